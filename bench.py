@@ -1,0 +1,308 @@
+#!/usr/bin/env python
+"""bench.py — Notebook reconciles/sec on B200 (BASELINE.json metric).
+
+A "step" is one pass of the GPU reconcile-generation path over one batch of
+synthetic Notebook CRs: for every Notebook, everything the reference's
+reconcilers compute for it that libnbrm implements (see STAGES below).  One
+Notebook processed = one reconcile.
+
+  value  reconciles/s with the batch already resident in HBM (kernels only)
+  e2e    reconciles/s through the C ABI with HOST buffers: pinned host ->
+         device copy of the batch, kernels, device -> host copy of every
+         generated object, all inside the timed region
+  --impl reference  the oracle (CPU restatement of the reference; the Go
+         reference cannot be built here) on all host cores, same workload
+
+Workload: BASELINE.json configs[1] (the ODH OAuth Notebook fixture, 100 per
+namespace), replicated to --batch Notebooks per GPU so that the batch is larger
+than the 126 MB L2; the literal 100-Notebook case is reported as latency in
+`config.literal_100`.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "Notebook reconciles/sec"
+UNIT = "reconciles/s"
+ENV = {"USE_ISTIO": "true", "ISTIO_GATEWAY": "kubeflow/kubeflow-gateway", "ISTIO_HOST": "*",
+       "CLUSTER_DOMAIN": "cluster.local"}
+STAGES = ["generateStatefulSet", "generateService", "generateVirtualService",
+          "SetControllerReference"]
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=262144, help="Notebooks per GPU per step")
+    ap.add_argument("--ref-sample", type=int, default=20000,
+                    help="Notebooks per step of the CPU reference arm")
+    return ap.parse_args()
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured"
+        except Exception:
+            pass
+    return 6650.0, "fallback"
+
+
+class ClockSampler(threading.Thread):
+    """Samples nvidia-smi clocks and throttle reasons while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index = index
+        self.samples = []
+        self.reasons = set()
+        self.stop_flag = threading.Event()
+
+    def run(self):
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        while not self.stop_flag.is_set():
+            try:
+                out = subprocess.run(
+                    ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                     "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                f = [x.strip() for x in out.strip().split(",")]
+                self.samples.append((float(f[0]), float(f[1])))
+                for nm, v in zip(names, f[2:6]):
+                    if v.lower().startswith("active"):
+                        self.reasons.add(nm)
+            except Exception:
+                pass
+            self.stop_flag.wait(0.1)
+
+    def result(self):
+        self.stop_flag.set()
+        self.join(timeout=10)
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": sorted(self.reasons)}
+        return {"sm_mhz": statistics.median(s[0] for s in self.samples),
+                "sm_max_mhz": max(s[1] for s in self.samples), "reasons": sorted(self.reasons),
+                "samples": len(self.samples)}
+
+
+def oracle_reconcile(nb):
+    """One reconcile's worth of pure work in the oracle (same STAGES)."""
+    from oracle import nbc
+    out = [nbc.generate_statefulset(nb, ENV), nbc.generate_service(nb, ENV),
+           nbc.generate_virtualservice(nb, ENV)]
+    for o in out:
+        nbc.set_controller_reference(nb, o)
+    return out
+
+
+def _oracle_chunk(docs):
+    """Worker: parse the Notebook JSON, run the oracle, serialise the objects
+    (the same bytes-in, bytes-out contract as the C ABI)."""
+    n = 0
+    for d in docs:
+        nb = json.loads(d)
+        for o in oracle_reconcile(nb):
+            n += len(json.dumps(o, separators=(",", ":")))
+    return n
+
+
+def cpu_baseline(docs, procs):
+    """Oracle timed on host cores over `docs`; returns reconciles/s."""
+    if procs <= 1:
+        t0 = time.perf_counter()
+        _oracle_chunk(docs)
+        return len(docs) / (time.perf_counter() - t0)
+    import multiprocessing as mp
+    chunks = [docs[i::procs] for i in range(procs)]
+    with mp.get_context("fork").Pool(procs) as pool:
+        pool.map(_oracle_chunk, [c[:8] for c in chunks])  # start the workers
+        t0 = time.perf_counter()
+        pool.map(_oracle_chunk, chunks)
+        dt = time.perf_counter() - t0
+    return len(docs) / dt
+
+
+def run_reference(args):
+    """--impl reference: the oracle on all host cores (rank 0 only)."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    import __graft_entry__ as graft
+    graft.load_pkg()
+    import importlib
+    wl = importlib.import_module(graft.PKG_NAME + ".workload")
+    cores = os.cpu_count() or 1
+    n = args.ref_sample
+    docs = [wl.dumps(nb) for nb in wl.corpus("c2", n)]
+    for _ in range(min(args.warmup, 1)):
+        cpu_baseline(docs[: max(n // 10, 1)], cores)
+    times = []
+    for _ in range(args.steps):
+        t0 = time.perf_counter()
+        cpu_baseline(docs, cores)
+        times.append(time.perf_counter() - t0)
+    dt = sum(times)
+    v = n * args.steps / dt
+    sample = "%d Notebooks/step (C2 OAuth fixture), JSON in -> oracle -> JSON out, %d processes" % (n, cores)
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
+        "data": "synthetic",
+        "config": {"workload": "configs[1] odh-notebook-controller OAuth Notebook fixture", "stages": STAGES,
+                   "batch_notebooks": n},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch
+    import __graft_entry__ as graft
+    pkg = graft.load_pkg()
+    import importlib
+    wl = importlib.import_module(graft.PKG_NAME + ".workload")
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if dist is not None:
+            dist.barrier(device_ids=[local])
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if dist is None:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    flags = pkg.GEN_ALL | pkg.GEN_OWNER_REF
+    B = args.batch
+    # weak scaling: every rank gets its own B Notebooks (independent keys, no collective)
+    nbs = wl.corpus("c2", B, start=rank * B)
+    raw = [wl.dumps(nb) for nb in nbs]
+    docs = pkg.Docs(raw, pinned=True)
+    ctx = pkg.Context(local, env=ENV)
+
+    # ---- value: inputs resident in HBM, kernels only
+    ctx.upload(0, docs)
+    for _ in range(args.warmup):
+        ctx.nbc_generate_resident(flags)
+    ctx.sync()
+    ctx.profile_enable(True)
+    sampler = ClockSampler(local)
+    sampler.start()
+    l0 = ctx.launch_count()
+    barrier()
+    ctx.timer_start()
+    for _ in range(args.steps):
+        ctx.nbc_generate_resident(flags)
+    ms = ctx.timer_stop()
+    barrier()
+    launches = ctx.launch_count() - l0
+    prof = ctx.profile_read()
+    ctx.profile_enable(False)
+    ms = max_over_ranks(ms)
+    value = world * B * args.steps / (ms / 1e3)
+
+    # ---- e2e: host buffers through the C ABI, copies inside the timed region
+    for _ in range(args.warmup):
+        res = ctx.nbc_generate(docs, flags, copy=False)
+    barrier()
+    ctx.timer_start()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        res = ctx.nbc_generate(docs, flags, copy=False)
+    ms_e2e_dev = ctx.timer_stop()
+    ms_e2e = 1e3 * (time.perf_counter() - t0)
+    barrier()
+    clocks = sampler.result()
+    ms_e2e = max_over_ranks(max(ms_e2e, ms_e2e_dev))
+    e2e_value = world * B * args.steps / (ms_e2e / 1e3)
+    h2d = docs.nbytes + docs.off.nbytes
+    d2h = int(res.off[-1]) + res.off.nbytes + res.status.nbytes
+    assert int(res.status.sum()) == 0
+
+    # ---- roofline of the dominant kernel (events inside the value loop)
+    peak, peak_kind = load_peaks()
+    emit_bytes = (prof.emit_bytes_read + prof.emit_bytes_written) / max(prof.emit_launches, 1)
+    plan_bytes = prof.plan_bytes_read / max(prof.plan_launches, 1)
+    kern = {"emit_objects": (prof.emit_ms / max(prof.emit_launches, 1), emit_bytes),
+            "nbc_generate_plan": (prof.plan_ms / max(prof.plan_launches, 1), plan_bytes)}
+    dom = max(kern, key=lambda k: kern[k][0])
+    dom_ms, dom_bytes = kern[dom]
+    achieved = dom_bytes / (dom_ms / 1e3) / 1e9 if dom_ms > 0 else 0.0
+    roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": None, "peak_kind": peak_kind,
+                "avg_launch_ms": dom_ms, "algorithmic_bytes_per_launch": dom_bytes,
+                "kernels_ms_per_step": {"plan": prof.plan_ms / args.steps, "scan": prof.scan_ms / args.steps,
+                                        "emit": prof.emit_ms / args.steps}}
+
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+
+    # literal configs[1]: 100 Notebooks, latency through the C ABI
+    small = pkg.Docs(raw[:100], pinned=True)
+    for _ in range(5):
+        ctx.nbc_generate(small, flags, copy=False)
+    lat = []
+    for _ in range(50):
+        t0 = time.perf_counter()
+        ctx.nbc_generate(small, flags, copy=False)
+        lat.append(1e3 * (time.perf_counter() - t0))
+    lat.sort()
+
+    # CPU baseline: the oracle, one core, bounded sample
+    cb_n = 4000
+    cb = cpu_baseline(raw[:cb_n], 1)
+
+    print(json.dumps({
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": "configs[1] odh-notebook-controller OAuth Notebook fixture x %d per GPU "
+                               "(100 per namespace)" % B,
+                   "stages": STAGES, "batch_notebooks": B, "l2": "batch larger than L2 (in %.0f MB, out %.0f MB)"
+                   % (docs.nbytes / 1e6, int(res.off[-1]) / 1e6),
+                   "literal_100": {"p50_ms": lat[len(lat) // 2], "p99_ms": lat[-1],
+                                   "reconciles_per_s": 100 / (lat[len(lat) // 2] / 1e3)}},
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "ms_per_step": ms_e2e / args.steps},
+        "gpu_launches": launches, "clocks": clocks, "roofline": roofline,
+        "cpu_baseline": {"value": cb, "unit": UNIT, "cores": 1, "kind": "port",
+                         "sample": "%d Notebooks of the same workload, JSON in -> oracle -> JSON out" % cb_n},
+    }))
+    ctx.close()
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,137 @@
+/* nbrm.h — C ABI of libnbrm, the B200 batch engine for the kubeflow-rm hot path.
+ *
+ * The reference (rhoai-rhtap/kubeflow-rm) is Go and exposes no in-process
+ * plugin or FFI interface: its drop-in surface is the CRDs and
+ * the webhooks.  This ABI is the seam a Go maintainer would bind with cgo (see
+ * INTEGRATION.md) to hand the pure, per-object work of a reconcile or
+ * admission pass to the GPU in batches.  Each entry point names the reference
+ * function(s) it replaces.  Paths are relative to components/ of the
+ * reference.
+ *
+ * Conventions
+ *   - A batch is n UTF-8 JSON documents packed back to back in `data`, with
+ *     n+1 byte offsets in `off` (document i is data[off[i] .. off[i+1])).
+ *   - All pointers in nbrm_docs are HOST pointers.  Pinned memory
+ *     (nbrm_host_alloc) makes the copies asynchronous; pageable memory works.
+ *   - Results point into context-owned pinned host memory and stay valid until
+ *     the next call on the same context.
+ *   - status[i] != 0 means input i was rejected the way the reference would
+ *     reject or crash on it (NBRM_E_*); its output objects have length 0.
+ *   - Return value: 0 ok; 1 ok but at least one status is non-zero; <0 the
+ *     call failed (nbrm_last_error says why).  There is no CPU fallback: every
+ *     entry point fails when no CUDA device is usable.
+ *   - A context is not thread-safe; use one per worker thread.  Calls on one
+ *     context run in order on its own CUDA stream.
+ *   - Limits: one batch holds < 4 GiB of input and < 4 GiB of output; one
+ *     document < 256 MiB.
+ */
+#ifndef NBRM_H_
+#define NBRM_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct nbrm_ctx nbrm_ctx;
+
+/* Per-document status codes. */
+enum {
+  NBRM_OK = 0,
+  NBRM_E_PARSE = 1,         /* not a JSON object / required object missing */
+  NBRM_E_NO_CONTAINERS = 2, /* reference panics: Containers[0], notebook_controller.go:455,489 */
+  NBRM_E_SEGS = 3,          /* object needs more template segments than the plan holds */
+  NBRM_E_PORTS_EMPTY = 4,   /* reference panics: Ports[0] on "ports":[], notebook_controller.go:491 */
+  NBRM_E_NIL_REPLICAS = 5,  /* reference panics: *Spec.Replicas, common/reconcilehelper/util.go:123 */
+  NBRM_E_DENIED = 6,        /* admission.Denied, odh-notebook-controller/controllers/notebook_webhook.go:274 */
+  NBRM_E_CONFLICT = 7,      /* PodDefault merge conflict, admission-webhook/main.go:671-679 */
+  NBRM_E_LIMIT = 8          /* a documented fixed limit of this library was exceeded */
+};
+
+/* The process environment and flags the reference reads while generating
+ * objects.  NULL means "unset" (os.LookupEnv reports absent).
+ *   notebook-controller/controllers/notebook_controller.go:213 (USE_ISTIO),
+ *   :475 (ADD_FSGROUP), :537 (CLUSTER_DOMAIN), :548 (ISTIO_HOST), :557 (ISTIO_GATEWAY);
+ *   odh-notebook-controller/main.go:63-72 (controller namespace), :80 (--oauth-proxy-image). */
+typedef struct nbrm_env {
+  const char* use_istio;
+  const char* istio_gateway;
+  const char* istio_host;
+  const char* cluster_domain;
+  const char* add_fsgroup;
+  const char* controller_namespace;
+  const char* oauth_proxy_image;
+} nbrm_env;
+
+typedef struct nbrm_docs {
+  const char* data;
+  const uint64_t* off; /* n + 1 entries */
+  uint64_t n;
+} nbrm_docs;
+
+typedef struct nbrm_out {
+  const char* data;
+  const uint64_t* off;    /* n + 1 entries */
+  uint64_t n;             /* number of output objects */
+  const uint32_t* status; /* one per INPUT document */
+  uint64_t n_status;
+} nbrm_out;
+
+/* Accumulated device time per kernel class since nbrm_profile_enable(ctx, 1),
+ * measured with CUDA events on the context's stream. */
+typedef struct nbrm_profile {
+  double plan_ms, scan_ms, emit_ms;
+  uint64_t plan_launches, scan_launches, emit_launches;
+  uint64_t emit_bytes_read, emit_bytes_written; /* algorithmic bytes of the emit kernel */
+  uint64_t plan_bytes_read;                     /* input bytes the plan kernels walked */
+} nbrm_profile;
+
+/* ---- context ---------------------------------------------------------- */
+int nbrm_ctx_create(int device, nbrm_ctx** ctx);
+void nbrm_ctx_destroy(nbrm_ctx* ctx);
+const char* nbrm_last_error(const nbrm_ctx* ctx);
+int nbrm_ctx_set_env(nbrm_ctx* ctx, const nbrm_env* env);
+int nbrm_sync(nbrm_ctx* ctx);
+
+/* Pinned host memory for inputs (optional). */
+void* nbrm_host_alloc(size_t bytes);
+void nbrm_host_free(void* p);
+
+/* Device timing of whatever runs on the context's stream between the calls. */
+int nbrm_timer_start(nbrm_ctx* ctx);
+int nbrm_timer_stop(nbrm_ctx* ctx, float* ms);
+int nbrm_profile_enable(nbrm_ctx* ctx, int on);
+int nbrm_profile_read(nbrm_ctx* ctx, nbrm_profile* out);
+/* Number of kernels this library has launched on the context so far. */
+uint64_t nbrm_launch_count(const nbrm_ctx* ctx);
+
+/* ---- resident inputs -------------------------------------------------- */
+/* Copy a batch into input slot 0..2 of the context; it stays in HBM until the
+ * slot is overwritten.  Slot meaning is per entry point. */
+int nbrm_upload(nbrm_ctx* ctx, int slot, const nbrm_docs* docs);
+/* Copy the result of the last *_resident call to host memory. */
+int nbrm_download(nbrm_ctx* ctx, nbrm_out* out);
+
+/* ---- notebook-controller generators ------------------------------------
+ * Replaces generateStatefulSet (notebook-controller/controllers/
+ * notebook_controller.go:408-484, with setPrefixEnvVar :392-406),
+ * generateService (:486-513), generateVirtualService (:519-619) and, with
+ * NBRM_GEN_OWNER_REF, the ctrl.SetControllerReference calls at :141,:183,:628.
+ * Input slot 0: Notebook CRs.  Output: 3 objects per Notebook, in the order
+ * StatefulSet, Service, VirtualService; an object not asked for has length 0. */
+enum {
+  NBRM_GEN_STS = 1,
+  NBRM_GEN_SVC = 2,
+  NBRM_GEN_VS = 4,
+  NBRM_GEN_OWNER_REF = 8,
+  NBRM_GEN_OWNER_V1 = 16 /* ownerReference apiVersion kubeflow.org/v1 (ODH) instead of v1beta1 */
+};
+int nbrm_nbc_generate(nbrm_ctx* ctx, const nbrm_docs* notebooks, uint32_t flags, nbrm_out* out);
+int nbrm_nbc_generate_resident(nbrm_ctx* ctx, uint32_t flags);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NBRM_H_ */

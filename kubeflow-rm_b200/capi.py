@@ -1,0 +1,228 @@
+"""ctypes binding of include/nbrm.h (libnbrm.so)."""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+
+GEN_STS, GEN_SVC, GEN_VS, GEN_OWNER_REF, GEN_OWNER_V1 = 1, 2, 4, 8, 16
+GEN_ALL = GEN_STS | GEN_SVC | GEN_VS
+
+STATUS_NAMES = {0: "OK", 1: "E_PARSE", 2: "E_NO_CONTAINERS", 3: "E_SEGS", 4: "E_PORTS_EMPTY",
+                5: "E_NIL_REPLICAS", 6: "E_DENIED", 7: "E_CONFLICT", 8: "E_LIMIT"}
+
+
+class NbrmError(RuntimeError):
+    pass
+
+
+class _Env(C.Structure):
+    _fields_ = [(k, C.c_char_p) for k in (
+        "use_istio", "istio_gateway", "istio_host", "cluster_domain", "add_fsgroup",
+        "controller_namespace", "oauth_proxy_image")]
+
+
+class _Docs(C.Structure):
+    _fields_ = [("data", C.c_void_p), ("off", C.c_void_p), ("n", C.c_uint64)]
+
+
+class _Out(C.Structure):
+    _fields_ = [("data", C.c_void_p), ("off", C.c_void_p), ("n", C.c_uint64),
+                ("status", C.c_void_p), ("n_status", C.c_uint64)]
+
+
+class Profile(C.Structure):
+    _fields_ = [("plan_ms", C.c_double), ("scan_ms", C.c_double), ("emit_ms", C.c_double),
+                ("plan_launches", C.c_uint64), ("scan_launches", C.c_uint64),
+                ("emit_launches", C.c_uint64), ("emit_bytes_read", C.c_uint64),
+                ("emit_bytes_written", C.c_uint64), ("plan_bytes_read", C.c_uint64)]
+
+
+# reference process environment (nbrm_env) key -> struct field
+ENV_FIELDS = {"USE_ISTIO": "use_istio", "ISTIO_GATEWAY": "istio_gateway", "ISTIO_HOST": "istio_host",
+              "CLUSTER_DOMAIN": "cluster_domain", "ADD_FSGROUP": "add_fsgroup",
+              "CONTROLLER_NAMESPACE": "controller_namespace", "OAUTH_PROXY_IMAGE": "oauth_proxy_image"}
+
+
+def lib_path():
+    return os.path.join(_HERE, "libnbrm.so")
+
+
+_lib = None
+
+
+def load_library():
+    """Load libnbrm.so; raise (never fall back) when it is missing."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    p = lib_path()
+    if not os.path.exists(p):
+        raise NbrmError("%s is not built: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                        "(there is no CPU fallback)" % p)
+    lib = C.CDLL(p)
+    lib.nbrm_ctx_create.argtypes = [C.c_int, C.POINTER(C.c_void_p)]
+    lib.nbrm_ctx_destroy.argtypes = [C.c_void_p]
+    lib.nbrm_ctx_destroy.restype = None
+    lib.nbrm_last_error.argtypes = [C.c_void_p]
+    lib.nbrm_last_error.restype = C.c_char_p
+    lib.nbrm_ctx_set_env.argtypes = [C.c_void_p, C.POINTER(_Env)]
+    lib.nbrm_sync.argtypes = [C.c_void_p]
+    lib.nbrm_host_alloc.argtypes = [C.c_size_t]
+    lib.nbrm_host_alloc.restype = C.c_void_p
+    lib.nbrm_host_free.argtypes = [C.c_void_p]
+    lib.nbrm_host_free.restype = None
+    lib.nbrm_timer_start.argtypes = [C.c_void_p]
+    lib.nbrm_timer_stop.argtypes = [C.c_void_p, C.POINTER(C.c_float)]
+    lib.nbrm_profile_enable.argtypes = [C.c_void_p, C.c_int]
+    lib.nbrm_profile_read.argtypes = [C.c_void_p, C.POINTER(Profile)]
+    lib.nbrm_launch_count.argtypes = [C.c_void_p]
+    lib.nbrm_launch_count.restype = C.c_uint64
+    lib.nbrm_upload.argtypes = [C.c_void_p, C.c_int, C.POINTER(_Docs)]
+    lib.nbrm_download.argtypes = [C.c_void_p, C.POINTER(_Out)]
+    lib.nbrm_nbc_generate.argtypes = [C.c_void_p, C.POINTER(_Docs), C.c_uint32, C.POINTER(_Out)]
+    lib.nbrm_nbc_generate_resident.argtypes = [C.c_void_p, C.c_uint32]
+    _lib = lib
+    return lib
+
+
+class Docs:
+    """A packed batch of JSON documents in host memory (optionally pinned)."""
+
+    def __init__(self, docs=None, pinned=False, data=None, off=None):
+        self._pin = []
+        if docs is not None:
+            lens = np.fromiter((len(d) for d in docs), dtype=np.uint64, count=len(docs))
+            off = np.zeros(len(docs) + 1, dtype=np.uint64)
+            np.cumsum(lens, out=off[1:])
+            data = np.frombuffer(b"".join(docs), dtype=np.uint8)
+        self.n = len(off) - 1
+        self.nbytes = int(off[-1]) if self.n else 0
+        if pinned:
+            lib = load_library()
+            self.data = self._pinned_copy(lib, np.ascontiguousarray(data, dtype=np.uint8))
+            self.off = self._pinned_copy(lib, np.ascontiguousarray(off, dtype=np.uint64))
+        else:
+            self.data = np.ascontiguousarray(data, dtype=np.uint8)
+            self.off = np.ascontiguousarray(off, dtype=np.uint64)
+
+    def _pinned_copy(self, lib, a):
+        nbytes = max(a.nbytes, 1)
+        p = lib.nbrm_host_alloc(nbytes)
+        if not p:
+            raise NbrmError("nbrm_host_alloc(%d) failed" % nbytes)
+        self._pin.append(p)
+        buf = (C.c_uint8 * nbytes).from_address(p)
+        out = np.frombuffer(buf, dtype=a.dtype, count=a.size)
+        out[...] = a
+        return out
+
+    def c_struct(self):
+        return _Docs(self.data.ctypes.data, self.off.ctypes.data, self.n)
+
+    def __del__(self):
+        if self._pin and _lib is not None:
+            for p in self._pin:
+                _lib.nbrm_host_free(p)
+            self._pin = []
+
+
+class Result:
+    """Copy-out view of an nbrm_out."""
+
+    def __init__(self, out, copy=True):
+        n = int(out.n)
+        off = np.frombuffer((C.c_uint64 * (n + 1)).from_address(out.off), dtype=np.uint64)
+        total = int(off[n]) if n else 0
+        data = np.frombuffer((C.c_uint8 * max(total, 1)).from_address(out.data), dtype=np.uint8,
+                             count=total)
+        ns = int(out.n_status)
+        st = np.frombuffer((C.c_uint32 * max(ns, 1)).from_address(out.status), dtype=np.uint32,
+                           count=ns)
+        self.off = off.copy() if copy else off
+        self.data = data.copy() if copy else data
+        self.status = st.copy() if copy else st
+        self.n = n
+
+    def doc(self, i):
+        return self.data[int(self.off[i]):int(self.off[i + 1])].tobytes()
+
+    def docs(self):
+        b = self.data.tobytes()
+        o = self.off
+        return [b[int(o[i]):int(o[i + 1])] for i in range(self.n)]
+
+
+class Context:
+    """One nbrm_ctx: a CUDA stream plus its device buffers on one GPU."""
+
+    def __init__(self, device=0, env=None):
+        self.lib = load_library()
+        h = C.c_void_p()
+        rc = self.lib.nbrm_ctx_create(device, C.byref(h))
+        if rc != 0 or not h:
+            raise NbrmError("nbrm_ctx_create(device=%d) failed (rc=%d): libnbrm needs a CUDA "
+                            "device, there is no CPU fallback" % (device, rc))
+        self.h = h
+        if env is not None:
+            self.set_env(env)
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.nbrm_ctx_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def _check(self, rc):
+        if rc < 0:
+            raise NbrmError(self.lib.nbrm_last_error(self.h).decode("utf-8", "replace"))
+        return rc
+
+    def set_env(self, env):
+        e = _Env()
+        for k, v in env.items():
+            setattr(e, ENV_FIELDS[k], None if v is None else v.encode())
+        self._check(self.lib.nbrm_ctx_set_env(self.h, C.byref(e)))
+
+    def sync(self):
+        self._check(self.lib.nbrm_sync(self.h))
+
+    def upload(self, slot, docs):
+        d = docs.c_struct()
+        self._check(self.lib.nbrm_upload(self.h, slot, C.byref(d)))
+
+    def download(self, copy=True):
+        o = _Out()
+        self._check(self.lib.nbrm_download(self.h, C.byref(o)))
+        return Result(o, copy)
+
+    def timer_start(self):
+        self._check(self.lib.nbrm_timer_start(self.h))
+
+    def timer_stop(self):
+        ms = C.c_float()
+        self._check(self.lib.nbrm_timer_stop(self.h, C.byref(ms)))
+        return ms.value
+
+    def profile_enable(self, on=True):
+        self._check(self.lib.nbrm_profile_enable(self.h, 1 if on else 0))
+
+    def profile_read(self):
+        p = Profile()
+        self._check(self.lib.nbrm_profile_read(self.h, C.byref(p)))
+        return p
+
+    def launch_count(self):
+        return int(self.lib.nbrm_launch_count(self.h))
+
+    # --- notebook-controller generators
+    def nbc_generate(self, docs, flags=GEN_ALL, copy=True):
+        d = docs.c_struct()
+        o = _Out()
+        self._check(self.lib.nbrm_nbc_generate(self.h, C.byref(d), flags, C.byref(o)))
+        return Result(o, copy)
+
+    def nbc_generate_resident(self, flags=GEN_ALL):
+        self._check(self.lib.nbrm_nbc_generate_resident(self.h, flags))

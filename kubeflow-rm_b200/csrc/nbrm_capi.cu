@@ -1,0 +1,454 @@
+// nbrm_capi.cu — the extern "C" surface declared in include/nbrm.h.
+#include <stdio.h>
+#include <string.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/nbrm.h"
+#include "nbrm_dev.h"
+#include "nbrm_pool.h"
+
+using namespace nbrm;
+
+namespace {
+
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  cudaError_t reserve(size_t n) {
+    if (n <= cap) return cudaSuccess;
+    size_t want = n + n / 4 + 256;
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+    cudaError_t e = cudaMalloc(&p, want);
+    if (e == cudaSuccess) cap = want;
+    return e;
+  }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+  }
+  template <typename T>
+  T* as() const {
+    return reinterpret_cast<T*>(p);
+  }
+};
+
+struct PinBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  cudaError_t reserve(size_t n) {
+    if (n <= cap) return cudaSuccess;
+    size_t want = n + n / 4 + 256;
+    if (p) cudaFreeHost(p);
+    p = nullptr;
+    cap = 0;
+    cudaError_t e = cudaHostAlloc(&p, want, cudaHostAllocDefault);
+    if (e == cudaSuccess) cap = want;
+    return e;
+  }
+  void release() {
+    if (p) cudaFreeHost(p);
+    p = nullptr;
+    cap = 0;
+  }
+};
+
+struct Slot {
+  DevBuf data, off;
+  uint32_t n = 0;
+  uint64_t bytes = 0;
+};
+
+enum KClass { K_PLAN = 0, K_SCAN = 1, K_EMIT = 2, K_COUNT = 3 };
+
+struct PendingEvent {
+  int cls;
+  cudaEvent_t a, b;
+};
+
+}  // namespace
+
+struct nbrm_ctx {
+  int device = 0;
+  int sm_count = 148;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t t0 = nullptr, t1 = nullptr;
+  std::string err;
+
+  // literal pool: fixed literals then the escaped environment strings
+  DevBuf pool;
+  EnvLits env;
+
+  Slot slot[3];
+  DevBuf segs, nseg, lens, status, aux, out_off, scan_tmp, out;
+  PinBuf h_out, h_off, h_status, h_total;
+
+  // last *_resident result
+  uint32_t res_n_in = 0, res_n_out = 0;
+  uint64_t res_bytes = 0;
+  bool res_valid = false;
+
+  bool prof = false;
+  std::vector<PendingEvent> pending;
+  std::vector<cudaEvent_t> free_events;
+  nbrm_profile acc;
+  uint64_t launches = 0;
+};
+
+namespace {
+
+int fail(nbrm_ctx* c, const char* what, cudaError_t e) {
+  char buf[512];
+  snprintf(buf, sizeof buf, "%s: %s", what, cudaGetErrorString(e));
+  c->err = buf;
+  return -1;
+}
+
+int fail_msg(nbrm_ctx* c, const char* what) {
+  c->err = what;
+  return -2;
+}
+
+#define CK(call)                                   \
+  do {                                             \
+    cudaError_t e_ = (call);                       \
+    if (e_ != cudaSuccess) return fail(c, #call, e_); \
+  } while (0)
+
+cudaEvent_t get_event(nbrm_ctx* c) {
+  if (!c->free_events.empty()) {
+    cudaEvent_t e = c->free_events.back();
+    c->free_events.pop_back();
+    return e;
+  }
+  cudaEvent_t e = nullptr;
+  cudaEventCreate(&e);
+  return e;
+}
+
+struct KScope {  // brackets one kernel class with events when profiling is on
+  nbrm_ctx* c;
+  PendingEvent pe;
+  bool on;
+  KScope(nbrm_ctx* c_, int cls, uint32_t n_launches) : c(c_), on(c_->prof) {
+    c->launches += n_launches;
+    if (!on) return;
+    pe.cls = cls;
+    pe.a = get_event(c);
+    pe.b = get_event(c);
+    cudaEventRecord(pe.a, c->stream);
+    if (cls == K_PLAN) c->acc.plan_launches += n_launches;
+    if (cls == K_SCAN) c->acc.scan_launches += n_launches;
+    if (cls == K_EMIT) c->acc.emit_launches += n_launches;
+  }
+  ~KScope() {
+    if (!on) return;
+    cudaEventRecord(pe.b, c->stream);
+    c->pending.push_back(pe);
+  }
+};
+
+int drain_profile(nbrm_ctx* c) {
+  if (c->pending.empty()) return 0;
+  CK(cudaStreamSynchronize(c->stream));
+  for (auto& pe : c->pending) {
+    float ms = 0;
+    cudaEventElapsedTime(&ms, pe.a, pe.b);
+    if (pe.cls == K_PLAN) c->acc.plan_ms += ms;
+    if (pe.cls == K_SCAN) c->acc.scan_ms += ms;
+    if (pe.cls == K_EMIT) c->acc.emit_ms += ms;
+    c->free_events.push_back(pe.a);
+    c->free_events.push_back(pe.b);
+  }
+  c->pending.clear();
+  return 0;
+}
+
+int build_pool(nbrm_ctx* c, const nbrm_env* env) {
+  std::string pool;
+  build_pool_host(env, pool, c->env);
+  CK(c->pool.reserve(pool.size()));
+  CK(cudaMemcpyAsync(c->pool.p, pool.data(), pool.size(), cudaMemcpyHostToDevice, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+int check_docs(nbrm_ctx* c, const nbrm_docs* d) {
+  if (!d || (d->n && (!d->data || !d->off))) return fail_msg(c, "nbrm_docs: null pointer");
+  if (d->n > 0x7fffffffull / 4) return fail_msg(c, "nbrm_docs: too many documents in one batch");
+  if (d->n) {
+    if (d->off[d->n] - d->off[0] >= 0xffffffffull - d->n * AUX_PAD)
+      return fail_msg(c, "nbrm_docs: batch holds 4 GiB or more; split it");
+  }
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int nbrm_ctx_create(int device, nbrm_ctx** out) {
+  if (!out) return -2;
+  *out = nullptr;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev <= 0) {
+    fprintf(stderr, "libnbrm: no usable CUDA device (%s); there is no CPU fallback\n",
+            e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+    return -1;
+  }
+  if (device < 0 || device >= ndev) return -2;
+  nbrm_ctx* c = new nbrm_ctx();
+  c->device = device;
+  memset(&c->acc, 0, sizeof c->acc);
+  if (cudaSetDevice(device) != cudaSuccess ||
+      cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaEventCreate(&c->t0) != cudaSuccess || cudaEventCreate(&c->t1) != cudaSuccess) {
+    fprintf(stderr, "libnbrm: cannot set up device %d: %s\n", device,
+            cudaGetErrorString(cudaGetLastError()));
+    delete c;
+    return -1;
+  }
+  cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device);
+  if (build_pool(c, nullptr) != 0) {
+    fprintf(stderr, "libnbrm: %s\n", c->err.c_str());
+    delete c;
+    return -1;
+  }
+  *out = c;
+  return 0;
+}
+
+void nbrm_ctx_destroy(nbrm_ctx* c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  cudaStreamSynchronize(c->stream);
+  for (auto& pe : c->pending) {
+    cudaEventDestroy(pe.a);
+    cudaEventDestroy(pe.b);
+  }
+  for (auto e : c->free_events) cudaEventDestroy(e);
+  for (auto& s : c->slot) {
+    s.data.release();
+    s.off.release();
+  }
+  DevBuf* bufs[] = {&c->pool, &c->segs, &c->nseg, &c->lens, &c->status,
+                    &c->aux,  &c->out_off, &c->scan_tmp, &c->out};
+  for (auto b : bufs) b->release();
+  PinBuf* pins[] = {&c->h_out, &c->h_off, &c->h_status, &c->h_total};
+  for (auto b : pins) b->release();
+  cudaEventDestroy(c->t0);
+  cudaEventDestroy(c->t1);
+  cudaStreamDestroy(c->stream);
+  delete c;
+}
+
+const char* nbrm_last_error(const nbrm_ctx* c) { return c ? c->err.c_str() : "null context"; }
+
+int nbrm_ctx_set_env(nbrm_ctx* c, const nbrm_env* env) {
+  if (!c) return -2;
+  CK(cudaSetDevice(c->device));
+  return build_pool(c, env);
+}
+
+int nbrm_sync(nbrm_ctx* c) {
+  if (!c) return -2;
+  CK(cudaStreamSynchronize(c->stream));
+  return 0;
+}
+
+void* nbrm_host_alloc(size_t bytes) {
+  void* p = nullptr;
+  if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess) return nullptr;
+  return p;
+}
+
+void nbrm_host_free(void* p) {
+  if (p) cudaFreeHost(p);
+}
+
+int nbrm_timer_start(nbrm_ctx* c) {
+  if (!c) return -2;
+  CK(cudaEventRecord(c->t0, c->stream));
+  return 0;
+}
+
+int nbrm_timer_stop(nbrm_ctx* c, float* ms) {
+  if (!c || !ms) return -2;
+  CK(cudaEventRecord(c->t1, c->stream));
+  CK(cudaEventSynchronize(c->t1));
+  CK(cudaEventElapsedTime(ms, c->t0, c->t1));
+  return 0;
+}
+
+int nbrm_profile_enable(nbrm_ctx* c, int on) {
+  if (!c) return -2;
+  if (drain_profile(c)) return -1;
+  c->prof = on != 0;
+  if (on) memset(&c->acc, 0, sizeof c->acc);
+  return 0;
+}
+
+int nbrm_profile_read(nbrm_ctx* c, nbrm_profile* out) {
+  if (!c || !out) return -2;
+  if (drain_profile(c)) return -1;
+  *out = c->acc;
+  return 0;
+}
+
+uint64_t nbrm_launch_count(const nbrm_ctx* c) { return c ? c->launches : 0; }
+
+int nbrm_upload(nbrm_ctx* c, int slot, const nbrm_docs* d) {
+  if (!c) return -2;
+  if (slot < 0 || slot > 2) return fail_msg(c, "nbrm_upload: slot must be 0..2");
+  if (int r = check_docs(c, d)) return r;
+  CK(cudaSetDevice(c->device));
+  Slot& s = c->slot[slot];
+  s.n = (uint32_t)d->n;
+  uint64_t base = d->n ? d->off[0] : 0;
+  if (base != 0) return fail_msg(c, "nbrm_docs: off[0] must be 0");
+  s.bytes = d->n ? d->off[d->n] : 0;
+  CK(s.data.reserve(s.bytes + 16));
+  CK(s.off.reserve((d->n + 1) * sizeof(uint64_t)));
+  if (s.bytes)
+    CK(cudaMemcpyAsync(s.data.p, d->data, s.bytes, cudaMemcpyHostToDevice, c->stream));
+  if (d->n) {
+    CK(cudaMemcpyAsync(s.off.p, d->off, (d->n + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice,
+                       c->stream));
+  } else {
+    CK(cudaMemsetAsync(s.off.p, 0, sizeof(uint64_t), c->stream));
+  }
+  c->res_valid = false;
+  return 0;
+}
+
+}  // extern "C"
+
+namespace {
+
+// plan -> scan -> (read total) -> emit, shared by every generator.
+struct Pipeline {
+  nbrm_ctx* c;
+  uint32_t n_in, n_out, cap;
+  PlanOut po;
+
+  int prepare(uint32_t n_in_, uint32_t out_per_doc, uint32_t cap_, uint64_t aux_bytes) {
+    n_in = n_in_;
+    n_out = n_in_ * out_per_doc;
+    cap = cap_;
+    CK(c->segs.reserve((size_t)n_out * cap * sizeof(Seg) + 16));
+    CK(c->nseg.reserve((size_t)n_out * 4 + 16));
+    CK(c->lens.reserve((size_t)n_out * 4 + 16));
+    CK(c->status.reserve((size_t)n_in * 4 + 16));
+    CK(c->aux.reserve(aux_bytes + 16));
+    CK(c->out_off.reserve(((size_t)n_out + 1) * 8));
+    CK(c->scan_tmp.reserve(scan_tmp_bytes(n_out)));
+    CK(c->h_total.reserve(8));
+    po.segs = c->segs.as<Seg>();
+    po.nseg = c->nseg.as<uint32_t>();
+    po.lens = c->lens.as<uint32_t>();
+    po.status = c->status.as<uint32_t>();
+    po.aux = c->aux.as<char>();
+    po.cap = cap;
+    return 0;
+  }
+
+  int finish(uint64_t plan_bytes) {
+    {
+      KScope k(c, K_SCAN, n_out ? 3 : 0);
+      launch_scan(po.lens, n_out, c->scan_tmp.as<uint64_t>(), c->out_off.as<uint64_t>(), c->stream);
+    }
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(c->h_total.p, c->out_off.as<uint64_t>() + n_out, 8, cudaMemcpyDeviceToHost,
+                       c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    uint64_t total = *reinterpret_cast<uint64_t*>(c->h_total.p);
+    if (total >= 0xffffffffull) return fail_msg(c, "output of this batch is 4 GiB or more; split it");
+    CK(c->out.reserve(total + 16));
+    SrcBases b;
+    b.p[SRC_IN0] = c->slot[0].data.as<char>();
+    b.p[SRC_IN1] = c->slot[1].data.as<char>();
+    b.p[SRC_IN2] = c->slot[2].data.as<char>();
+    b.p[SRC_POOL] = c->pool.as<char>();
+    b.p[SRC_AUX] = c->aux.as<char>();
+    {
+      KScope k(c, K_EMIT, n_out ? 1 : 0);
+      launch_emit(po.segs, po.nseg, c->out_off.as<uint64_t>(), n_out, cap, b, c->out.as<char>(),
+                  c->sm_count, c->stream);
+    }
+    CK(cudaGetLastError());
+    if (c->prof) {
+      c->acc.emit_bytes_read += total;
+      c->acc.emit_bytes_written += total;
+      c->acc.plan_bytes_read += plan_bytes;
+    }
+    c->res_n_in = n_in;
+    c->res_n_out = n_out;
+    c->res_bytes = total;
+    c->res_valid = true;
+    return 0;
+  }
+};
+
+}  // namespace
+
+extern "C" {
+
+int nbrm_download(nbrm_ctx* c, nbrm_out* out) {
+  if (!c || !out) return -2;
+  if (!c->res_valid) return fail_msg(c, "nbrm_download: no result on this context");
+  CK(cudaSetDevice(c->device));
+  CK(c->h_out.reserve(c->res_bytes + 16));
+  CK(c->h_off.reserve(((size_t)c->res_n_out + 1) * 8));
+  CK(c->h_status.reserve((size_t)c->res_n_in * 4 + 16));
+  if (c->res_bytes)
+    CK(cudaMemcpyAsync(c->h_out.p, c->out.p, c->res_bytes, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaMemcpyAsync(c->h_off.p, c->out_off.p, ((size_t)c->res_n_out + 1) * 8,
+                     cudaMemcpyDeviceToHost, c->stream));
+  if (c->res_n_in)
+    CK(cudaMemcpyAsync(c->h_status.p, c->status.p, (size_t)c->res_n_in * 4, cudaMemcpyDeviceToHost,
+                       c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  out->data = reinterpret_cast<const char*>(c->h_out.p);
+  out->off = reinterpret_cast<const uint64_t*>(c->h_off.p);
+  out->n = c->res_n_out;
+  out->status = reinterpret_cast<const uint32_t*>(c->h_status.p);
+  out->n_status = c->res_n_in;
+  const uint32_t* st = out->status;
+  for (uint32_t i = 0; i < c->res_n_in; ++i)
+    if (st[i]) return 1;
+  return 0;
+}
+
+int nbrm_nbc_generate_resident(nbrm_ctx* c, uint32_t flags) {
+  if (!c) return -2;
+  CK(cudaSetDevice(c->device));
+  Slot& s = c->slot[0];
+  Pipeline p;
+  p.c = c;
+  if (int r = p.prepare(s.n, NBC_OUT_PER_DOC, NBC_SEG_CAP, s.bytes + (uint64_t)s.n * AUX_PAD))
+    return r;
+  DevDocs nb;
+  nb.data = s.data.as<char>();
+  nb.off = s.off.as<uint64_t>();
+  nb.n = s.n;
+  {
+    KScope k(c, K_PLAN, s.n ? 1 : 0);
+    launch_nbc_generate_plan(nb, c->env, flags, p.po, c->stream);
+  }
+  CK(cudaGetLastError());
+  return p.finish(s.bytes);
+}
+
+int nbrm_nbc_generate(nbrm_ctx* c, const nbrm_docs* notebooks, uint32_t flags, nbrm_out* out) {
+  if (!c || !out) return -2;
+  if (int r = nbrm_upload(c, 0, notebooks)) return r;
+  if (int r = nbrm_nbc_generate_resident(c, flags)) return r;
+  return nbrm_download(c, out);
+}
+
+}  // extern "C"

@@ -1,0 +1,152 @@
+// nbrm_kernels.cu — the kernels every generator shares: exclusive scan of the
+// planned object lengths and the gather-copy that writes the packed output.
+#include "nbrm_dev.h"
+
+namespace nbrm {
+
+// ---------------------------------------------------------------- scan
+// lens[n] (u32) -> off[n+1] (u64), three small kernels: per-tile sums, a scan
+// of the tile sums by one block, per-tile scan plus the tile's prefix.
+
+static const int SCAN_THREADS = 256;
+static const int SCAN_ITEMS = 4;
+static const int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;  // 1024 lengths per block
+
+__device__ __forceinline__ uint64_t warp_incl_scan(uint64_t v, int lane) {
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    uint64_t t = __shfl_up_sync(0xffffffffu, v, d);
+    if (lane >= d) v += t;
+  }
+  return v;
+}
+
+// Inclusive scan across a 256-thread block; returns this thread's inclusive
+// value and the block total through `total`.
+__device__ __forceinline__ uint64_t block_incl_scan(uint64_t v, uint64_t* total) {
+  __shared__ uint64_t wsum[SCAN_THREADS / 32];
+  int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  uint64_t inc = warp_incl_scan(v, lane);
+  if (lane == 31) wsum[w] = inc;
+  __syncthreads();
+  if (w == 0) {
+    uint64_t s = lane < SCAN_THREADS / 32 ? wsum[lane] : 0;
+    s = warp_incl_scan(s, lane);
+    if (lane < SCAN_THREADS / 32) wsum[lane] = s;
+  }
+  __syncthreads();
+  uint64_t prefix = w ? wsum[w - 1] : 0;
+  *total = wsum[SCAN_THREADS / 32 - 1];
+  __syncthreads();
+  return inc + prefix;
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS) scan_tile_sums(const uint32_t* __restrict__ lens,
+                                                               uint32_t n,
+                                                               uint64_t* __restrict__ tile_sums) {
+  uint32_t base = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
+  uint64_t s = 0;
+#pragma unroll
+  for (int k = 0; k < SCAN_ITEMS; ++k)
+    if (base + k < n) s += lens[base + k];
+  uint64_t total;
+  block_incl_scan(s, &total);
+  if (threadIdx.x == 0) tile_sums[blockIdx.x] = total;
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS) scan_tile_prefix(uint64_t* __restrict__ tile_sums,
+                                                                 uint32_t n_tiles) {
+  __shared__ uint64_t carry_s;
+  if (threadIdx.x == 0) carry_s = 0;
+  __syncthreads();
+  for (uint32_t start = 0; start < n_tiles; start += SCAN_THREADS) {
+    uint32_t i = start + threadIdx.x;
+    uint64_t v = i < n_tiles ? tile_sums[i] : 0;
+    uint64_t total;
+    uint64_t inc = block_incl_scan(v, &total);
+    uint64_t carry = carry_s;
+    if (i < n_tiles) tile_sums[i] = carry + inc - v;  // exclusive
+    __syncthreads();
+    if (threadIdx.x == 0) carry_s = carry + total;
+    __syncthreads();
+  }
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS) scan_write_offsets(
+    const uint32_t* __restrict__ lens, uint32_t n, const uint64_t* __restrict__ tile_prefix,
+    uint64_t* __restrict__ off) {
+  uint32_t base = blockIdx.x * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
+  uint32_t v[SCAN_ITEMS];
+  uint64_t s = 0;
+#pragma unroll
+  for (int k = 0; k < SCAN_ITEMS; ++k) {
+    v[k] = base + k < n ? lens[base + k] : 0;
+    s += v[k];
+  }
+  uint64_t total;
+  uint64_t inc = block_incl_scan(s, &total);
+  uint64_t run = tile_prefix[blockIdx.x] + inc - s;
+#pragma unroll
+  for (int k = 0; k < SCAN_ITEMS; ++k) {
+    if (base + k < n) off[base + k] = run;
+    run += v[k];
+    if (base + k + 1 == n) off[n] = run;
+  }
+}
+
+void launch_scan(const uint32_t* lens, uint32_t n, uint64_t* tile_tmp, uint64_t* off,
+                 cudaStream_t st) {
+  if (n == 0) {
+    cudaMemsetAsync(off, 0, sizeof(uint64_t), st);
+    return;
+  }
+  uint32_t tiles = (n + SCAN_TILE - 1) / SCAN_TILE;
+  scan_tile_sums<<<tiles, SCAN_THREADS, 0, st>>>(lens, n, tile_tmp);
+  scan_tile_prefix<<<1, SCAN_THREADS, 0, st>>>(tile_tmp, tiles);
+  scan_write_offsets<<<tiles, SCAN_THREADS, 0, st>>>(lens, n, tile_tmp, off);
+}
+
+size_t scan_tmp_bytes(uint32_t n) {
+  return sizeof(uint64_t) * ((size_t)(n + SCAN_TILE - 1) / SCAN_TILE + 1);
+}
+
+// ---------------------------------------------------------------- emit
+// One warp per output object: read its segment list, copy each segment from
+// its source buffer to the packed output.  Lanes stride over the bytes of a
+// segment, so both the read and the write are contiguous per warp access.
+
+__global__ void __launch_bounds__(EMIT_THREADS) emit_objects(const Seg* __restrict__ segs,
+                                                            const uint32_t* __restrict__ nseg,
+                                                            const uint64_t* __restrict__ off,
+                                                            uint32_t n_out, uint32_t cap,
+                                                            SrcBases bases, char* __restrict__ out) {
+  const int lane = threadIdx.x & 31;
+  const uint32_t warps_per_block = EMIT_THREADS / 32;
+  uint32_t w = blockIdx.x * warps_per_block + (threadIdx.x >> 5);
+  const uint32_t stride = gridDim.x * warps_per_block;
+  for (; w < n_out; w += stride) {
+    const uint32_t ns = nseg[w];
+    if (!ns) continue;
+    const Seg* s = segs + (size_t)w * cap;
+    char* o = out + off[w];
+    for (uint32_t k = 0; k < ns; ++k) {
+      const Seg sg = s[k];
+      const uint32_t len = sg.len_src & SEG_LEN_MASK;
+      const char* src = bases.p[sg.len_src >> 28] + sg.off;
+      for (uint32_t j = lane; j < len; j += 32) o[j] = src[j];
+      o += len;
+    }
+  }
+}
+
+void launch_emit(const Seg* segs, const uint32_t* nseg, const uint64_t* off, uint32_t n_out,
+                 uint32_t cap, const SrcBases& bases, char* out, int sm_count, cudaStream_t st) {
+  if (!n_out) return;
+  uint32_t wpb = EMIT_THREADS / 32;
+  uint32_t blocks = (n_out + wpb - 1) / wpb;
+  uint32_t max_blocks = (uint32_t)sm_count * 8;
+  if (blocks > max_blocks) blocks = max_blocks;
+  emit_objects<<<blocks, EMIT_THREADS, 0, st>>>(segs, nseg, off, n_out, cap, bases, out);
+}
+
+}  // namespace nbrm

@@ -1,0 +1,474 @@
+// nbrm_nbc.cuh — planners for the notebook-controller generators.
+//
+// Reference behaviour (components/notebook-controller/controllers/
+// notebook_controller.go): generateStatefulSet :408-484, setPrefixEnvVar
+// :392-406, generateService :486-513, generateVirtualService :519-619,
+// ctrl.SetControllerReference at :141,:183,:628.
+#pragma once
+#include "nbrm_plan.cuh"
+
+namespace nbrm {
+
+enum GenFlags : uint32_t {
+  GEN_STS = 1u,
+  GEN_SVC = 2u,
+  GEN_VS = 4u,
+  GEN_OWNER_REF = 8u,      // add the controller ownerReference (Reconcile :141,:183,:628)
+  GEN_OWNER_V1 = 16u,      // ownerReference apiVersion kubeflow.org/v1 (ODH) instead of v1beta1
+};
+
+// Per-document slice of the aux arena: bytes a planner computes.
+struct Aux {
+  char* p;        // start of this document's slice
+  uint32_t abs;   // absolute offset of the slice in the aux arena
+  uint32_t cap;
+  uint32_t used;
+};
+
+// Spans of a Notebook every planner needs.
+struct NbView {
+  Span root, meta, name, ns, uid, labels, annotations, podspec, containers, c0;
+  uint32_t err;
+};
+
+NB_HD NbView view_notebook(const Doc& d) {
+  NbView v;
+  v.err = E_OK;
+  v.root = root(d);
+  v.meta = v.name = v.ns = v.uid = v.labels = v.annotations = mk(0, 0);
+  v.podspec = v.containers = v.c0 = mk(0, 0);
+  if (!is_object(d, v.root)) {
+    v.err = E_PARSE;
+    return v;
+  }
+  Span spec = mk(0, 0);
+  {
+    ObjIter it(d, v.root);
+    Member m;
+    while (it.next(d, m)) {
+      Span k = inner(m.key);
+      if (bytes_eq(d, k, "metadata")) v.meta = m.val;
+      else if (bytes_eq(d, k, "spec")) spec = m.val;
+    }
+  }
+  {
+    ObjIter it(d, v.meta);
+    Member m;
+    while (it.next(d, m)) {
+      Span k = inner(m.key);
+      if (bytes_eq(d, k, "name")) v.name = m.val;
+      else if (bytes_eq(d, k, "namespace")) v.ns = m.val;
+      else if (bytes_eq(d, k, "uid")) v.uid = m.val;
+      else if (bytes_eq(d, k, "labels")) v.labels = m.val;
+      else if (bytes_eq(d, k, "annotations")) v.annotations = m.val;
+    }
+  }
+  if (!is_string(d, v.name)) v.name = mk(0, 0);
+  if (!is_string(d, v.ns) || v.ns.len == 2) v.ns = mk(0, 0);
+  if (!is_string(d, v.uid)) v.uid = mk(0, 0);
+  Span tmpl = find(d, spec, "template");
+  v.podspec = find(d, tmpl, "spec");
+  v.containers = find(d, v.podspec, "containers");
+  if (is_array(d, v.containers)) {
+    ArrIter it(d, v.containers);
+    Span e;
+    if (it.next(d, e) && is_object(d, e)) v.c0 = e;
+  }
+  return v;
+}
+
+NB_HD void put_str(Planner& P, Span s) {
+  if (s.ok()) P.in(s);
+  else LIT(P, EMPTY_STR);
+}
+
+// "name":<name>[,"namespace":<ns>][,"ownerReferences":[...]]  (after the head literal)
+NB_HD void plan_meta_tail(Planner& P, const NbView& v, uint32_t flags) {
+  if (v.ns.ok()) {
+    LIT(P, NAMESPACE_KEY);
+    P.in(v.ns);
+  }
+  if (flags & GEN_OWNER_REF) {
+    if (flags & GEN_OWNER_V1) LIT(P, OWNER_V1);
+    else LIT(P, OWNER_V1BETA1);
+    put_str(P, v.name);
+    LIT(P, OWNER_UID);
+    put_str(P, v.uid);
+    LIT(P, OWNER_TAIL);
+  }
+}
+
+template <uint32_t N>
+NB_HD bool map_has(const Doc& d, Span map, const char (&key)[N]) {
+  return find(d, map, key).ok();
+}
+
+NB_HD bool env_has_nb_prefix(const Doc& d, Span env) {
+  ArrIter it(d, env);
+  Span e;
+  while (it.next(d, e)) {
+    if (str_eq(d, find(d, e, "name"), "NB_PREFIX")) return true;
+  }
+  return false;
+}
+
+NB_HD void plan_nb_prefix_elem(Planner& P, const NbView& v) {
+  LIT(P, NB_PREFIX_OPEN);
+  P.in(inner(v.ns));
+  LIT(P, SLASH);
+  P.in(inner(v.name));
+  LIT(P, NB_PREFIX_CLOSE);
+}
+
+// generateStatefulSet (+ SetControllerReference when asked).
+NB_HD void plan_statefulset(Planner& P, const Doc& d, const NbView& v, const EnvLits& env,
+                            uint32_t flags) {
+  LIT(P, STS_HEAD);
+  put_str(P, v.name);
+  plan_meta_tail(P, v, flags);
+  LIT(P, STS_SPEC_REPLICAS);
+  if (map_has(d, v.annotations, "kubeflow-resource-stopped")) LIT(P, ZERO);  // :410-412
+  else LIT(P, ONE);
+  LIT(P, STS_SELECTOR);
+  put_str(P, v.name);
+  LIT(P, STS_TEMPLATE_LABELS);
+  {  // :428-432 defaults, :441-444 Notebook labels win
+    Sep s;
+    if (!map_has(d, v.labels, "statefulset")) {
+      s.next(P);
+      LIT(P, LBL_STATEFULSET);
+      put_str(P, v.name);
+    }
+    if (!map_has(d, v.labels, "notebook-name")) {
+      s.next(P);
+      LIT(P, LBL_NOTEBOOK_NAME);
+      put_str(P, v.name);
+    }
+    if (!map_has(d, v.labels, "opendatahub.io/workbenches")) {
+      s.next(P);
+      LIT(P, LBL_WORKBENCH);
+    }
+    ObjIter it(d, v.labels);
+    Member m;
+    while (it.next(d, m)) s.in(P, d, m.all);
+  }
+  {  // :447-452 annotations whose key has neither "kubectl" nor "notebook"
+    Sep s;
+    ObjIter it(d, v.annotations);
+    Member m;
+    while (it.next(d, m)) {
+      Span k = inner(m.key);
+      if (bytes_contain(d, k, "kubectl") || bytes_contain(d, k, "notebook")) continue;
+      if (s.first) LIT(P, STS_ANNOTATIONS);
+      s.in(P, d, m.all);
+    }
+  }
+  LIT(P, STS_TEMPLATE_SPEC);
+  {  // PodSpec members, :435 deep copy with :454-482 edits
+    Sep ps;
+    bool has_sc = false;
+    ObjIter it(d, v.podspec);
+    Member m;
+    while (it.next(d, m)) {
+      Span k = inner(m.key);
+      if (bytes_eq(d, k, "containers")) {
+        ps.next(P);
+        LIT(P, KEY_CONTAINERS);
+        Sep cs;
+        bool has_wd = false, has_ports = false, has_env = false;
+        ObjIter ci(d, v.c0);
+        Member c;
+        while (ci.next(d, c)) {
+          Span ck = inner(c.key);
+          if (bytes_eq(d, ck, "workingDir")) {
+            if (is_nil(d, c.val) || c.val.len == 2) continue;  // "" -> default, :456
+            has_wd = true;
+          } else if (bytes_eq(d, ck, "ports")) {
+            if (is_nil(d, c.val)) continue;  // nil -> default, :459
+            has_ports = true;
+          } else if (bytes_eq(d, ck, "env")) {
+            if (is_nil(d, c.val)) continue;
+            has_env = true;
+            if (is_array(d, c.val) && !env_has_nb_prefix(d, c.val)) {  // :402-405
+              cs.next(P);
+              LIT(P, KEY_ENV_OPEN);
+              if (!is_empty_container(d, c.val)) {
+                P.in(mk(c.val.off + 1, c.val.len - 2));
+                LIT(P, COMMA);
+              }
+              plan_nb_prefix_elem(P, v);
+              continue;
+            }
+          }
+          cs.in(P, d, c.all);
+        }
+        if (!has_wd) {
+          cs.next(P);
+          LIT(P, KEY_WORKINGDIR_DEFAULT);
+        }
+        if (!has_ports) {
+          cs.next(P);
+          LIT(P, KEY_PORTS_DEFAULT);
+        }
+        if (!has_env) {
+          cs.next(P);
+          LIT(P, KEY_ENV_OPEN);
+          plan_nb_prefix_elem(P, v);
+        }
+        LIT(P, RBRACE);
+        // the other containers and the closing bracket, as they came
+        P.in(mk(v.c0.end(), v.containers.end() - v.c0.end()));
+        continue;
+      }
+      if (bytes_eq(d, k, "securityContext")) {
+        if (is_nil(d, m.val)) continue;  // nil pointer, :476
+        has_sc = true;
+      }
+      ps.in(P, d, m.all);
+    }
+    if (env.add_fsgroup && !has_sc) {  // :475-481
+      ps.next(P);
+      LIT(P, KEY_FSGROUP_DEFAULT);
+    }
+  }
+  LIT(P, STS_TAIL);
+}
+
+// generateService.
+NB_HD void plan_service(Planner& P, const Doc& d, const NbView& v, uint32_t flags) {
+  LIT(P, SVC_HEAD);
+  put_str(P, v.name);
+  plan_meta_tail(P, v, flags);
+  LIT(P, SVC_PORTS);
+  P.in(inner(v.name));
+  LIT(P, SVC_TARGETPORT);
+  Span ports = find(d, v.c0, "ports");
+  if (is_nil(d, ports)) {  // :490 nil test
+    LIT(P, PORT_8888);
+  } else {
+    ArrIter it(d, ports);
+    Span e;
+    if (!it.next(d, e)) {
+      P.err = E_PORTS_EMPTY;  // :491 would index an empty slice
+      return;
+    }
+    Span cp = find(d, e, "containerPort");
+    if (cp.ok() && !is_null(d, cp)) P.in(cp);
+    else LIT(P, ZERO);
+  }
+  LIT(P, SVC_SELECTOR);
+  put_str(P, v.name);
+  LIT(P, SVC_TAIL);
+}
+
+NB_HD int hexval(char c) {
+  if (c >= '0' && c <= '9') return c - '0';
+  if (c >= 'a' && c <= 'f') return c - 'a' + 10;
+  if (c >= 'A' && c <= 'F') return c - 'A' + 10;
+  return -1;
+}
+
+// Undo one level of JSON string escaping.  Returns bytes written, or
+// 0xffffffff when the escapes are malformed or the slice is too small.
+NB_HD uint32_t unescape(const Doc& d, Span s, char* out, uint32_t cap) {
+  uint32_t o = 0, i = s.off, e = s.end();
+  while (i < e) {
+    if (o + 4 > cap) return 0xffffffffu;
+    char c = d.p[i];
+    if (c != '\\') {
+      out[o++] = c;
+      ++i;
+      continue;
+    }
+    if (i + 1 >= e) return 0xffffffffu;
+    char x = d.p[i + 1];
+    i += 2;
+    switch (x) {
+      case '"': out[o++] = '"'; break;
+      case '\\': out[o++] = '\\'; break;
+      case '/': out[o++] = '/'; break;
+      case 'b': out[o++] = '\b'; break;
+      case 'f': out[o++] = '\f'; break;
+      case 'n': out[o++] = '\n'; break;
+      case 'r': out[o++] = '\r'; break;
+      case 't': out[o++] = '\t'; break;
+      case 'u': {
+        if (i + 4 > e) return 0xffffffffu;
+        uint32_t cp = 0;
+        for (int k = 0; k < 4; ++k) {
+          int h = hexval(d.p[i + k]);
+          if (h < 0) return 0xffffffffu;
+          cp = cp * 16 + (uint32_t)h;
+        }
+        i += 4;
+        if (cp >= 0xD800 && cp < 0xDC00 && i + 6 <= e && d.p[i] == '\\' && d.p[i + 1] == 'u') {
+          uint32_t lo = 0;
+          bool okh = true;
+          for (int k = 0; k < 4; ++k) {
+            int h = hexval(d.p[i + 2 + k]);
+            if (h < 0) okh = false;
+            lo = lo * 16 + (uint32_t)(h < 0 ? 0 : h);
+          }
+          if (okh && lo >= 0xDC00 && lo < 0xE000) {
+            cp = 0x10000 + ((cp - 0xD800) << 10) + (lo - 0xDC00);
+            i += 6;
+          }
+        }
+        if (cp >= 0xD800 && cp < 0xE000) cp = 0xFFFD;  // lone surrogate
+        if (cp < 0x80) {
+          out[o++] = (char)cp;
+        } else if (cp < 0x800) {
+          out[o++] = (char)(0xC0 | (cp >> 6));
+          out[o++] = (char)(0x80 | (cp & 0x3F));
+        } else if (cp < 0x10000) {
+          out[o++] = (char)(0xE0 | (cp >> 12));
+          out[o++] = (char)(0x80 | ((cp >> 6) & 0x3F));
+          out[o++] = (char)(0x80 | (cp & 0x3F));
+        } else {
+          out[o++] = (char)(0xF0 | (cp >> 18));
+          out[o++] = (char)(0x80 | ((cp >> 12) & 0x3F));
+          out[o++] = (char)(0x80 | ((cp >> 6) & 0x3F));
+          out[o++] = (char)(0x80 | (cp & 0x3F));
+        }
+        break;
+      }
+      default:
+        return 0xffffffffu;
+    }
+  }
+  return o;
+}
+
+// End index of the strictly valid JSON string starting at i, or 0.
+NB_HD uint32_t strict_string_end(const Doc& d, uint32_t i) {
+  if (i >= d.n || d.p[i] != '"') return 0;
+  uint32_t j = i + 1;
+  while (j < d.n) {
+    unsigned char c = (unsigned char)d.p[j];
+    if (c == '"') return j + 1;
+    if (c < 0x20) return 0;
+    if (c == '\\') {
+      if (j + 1 >= d.n) return 0;
+      char x = d.p[j + 1];
+      if (x == 'u') {
+        if (j + 6 > d.n) return 0;
+        for (int k = 2; k < 6; ++k)
+          if (hexval(d.p[j + k]) < 0) return 0;
+        j += 6;
+      } else if (x == '"' || x == '\\' || x == '/' || x == 'b' || x == 'f' || x == 'n' ||
+                 x == 'r' || x == 't') {
+        j += 2;
+      } else {
+        return 0;
+      }
+    } else {
+      ++j;
+    }
+  }
+  return 0;
+}
+
+// headers.request.set from the http-headers-request-set annotation (:566-579):
+// the annotation must decode to a flat object of strings (null counts as ""),
+// anything else gives the empty map.  Emits the members (no braces).
+NB_HD void plan_headers_set(Planner& P, const Doc& d, const NbView& v, Aux& aux) {
+  Span a = find(d, v.annotations, "notebooks.kubeflow.org/http-headers-request-set");
+  if (!is_string(d, a) || a.len == 2) return;
+  char* out = aux.p + aux.used;
+  uint32_t n = unescape(d, inner(a), out, aux.cap - aux.used);
+  if (n == 0xffffffffu) return;
+  Doc t;
+  t.p = out;
+  t.n = n;
+  // pass 1: validate strictly; pass 2: emit
+  for (int pass = 0; pass < 2; ++pass) {
+    uint32_t i = skip_ws(t, 0);
+    if (i >= t.n || t.p[i] != '{') return;
+    i = skip_ws(t, i + 1);
+    bool first = true;
+    if (i < t.n && t.p[i] == '}') {
+      ++i;
+    } else {
+      for (;;) {
+        uint32_t ke = strict_string_end(t, i);
+        if (!ke) return;
+        uint32_t ks = i;
+        i = skip_ws(t, ke);
+        if (i >= t.n || t.p[i] != ':') return;
+        i = skip_ws(t, i + 1);
+        uint32_t vs = i, ve;
+        bool isnull = false;
+        if (i + 4 <= t.n && t.p[i] == 'n' && t.p[i + 1] == 'u' && t.p[i + 2] == 'l' &&
+            t.p[i + 3] == 'l') {
+          ve = i + 4;
+          isnull = true;
+        } else {
+          ve = strict_string_end(t, i);
+          if (!ve) return;
+        }
+        if (pass == 1) {
+          if (!first) LIT(P, COMMA);
+          P.aux(aux.abs + aux.used + ks, ke - ks);
+          LIT(P, COLON);
+          if (isnull) LIT(P, EMPTY_STR);
+          else P.aux(aux.abs + aux.used + vs, ve - vs);
+        }
+        first = false;
+        i = skip_ws(t, ve);
+        if (i < t.n && t.p[i] == ',') {
+          i = skip_ws(t, i + 1);
+          continue;
+        }
+        if (i < t.n && t.p[i] == '}') {
+          ++i;
+          break;
+        }
+        return;
+      }
+    }
+    i = skip_ws(t, i);
+    if (i != t.n) return;
+  }
+  aux.used += n;
+}
+
+// generateVirtualService.
+NB_HD void plan_virtualservice(Planner& P, const Doc& d, const NbView& v, const EnvLits& env,
+                               uint32_t flags, Aux& aux) {
+  LIT(P, VS_HEAD);  // ... "name":"notebook-
+  P.in(inner(v.ns));
+  LIT(P, DASH);
+  P.in(inner(v.name));
+  LIT(P, QUOTE);
+  plan_meta_tail(P, v, flags);
+  LIT(P, VS_GATEWAYS);
+  P.pool(env.istio_gateway.off, env.istio_gateway.len);
+  LIT(P, VS_HOSTS);
+  P.pool(env.istio_host.off, env.istio_host.len);
+  LIT(P, VS_HTTP_SET);
+  plan_headers_set(P, d, v, aux);
+  LIT(P, VS_MATCH);
+  P.in(inner(v.ns));
+  LIT(P, SLASH);
+  P.in(inner(v.name));
+  LIT(P, VS_REWRITE);
+  Span rw = find(d, v.annotations, "notebooks.kubeflow.org/http-rewrite-uri");
+  if (is_string(d, rw) && rw.len > 2) {  // :533
+    P.in(rw);
+  } else {
+    LIT(P, VS_REWRITE_DEFAULT);
+    P.in(inner(v.ns));
+    LIT(P, SLASH);
+    P.in(inner(v.name));
+    LIT(P, SLASH_QUOTE);
+  }
+  LIT(P, VS_ROUTE);
+  P.in(inner(v.name));
+  LIT(P, DOT);
+  P.in(inner(v.ns));
+  LIT(P, DOT_SVC_DOT);
+  P.pool(env.cluster_domain.off, env.cluster_domain.len);
+  LIT(P, VS_TAIL);
+}
+
+}  // namespace nbrm

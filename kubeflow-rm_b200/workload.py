@@ -1,0 +1,183 @@
+"""Synthetic inputs for the parity tests and bench.py.
+
+All generators are deterministic in (seed, index).  Shapes follow the
+reference's own fixtures:
+  C1  the envtest Notebook of notebook-controller/controllers/
+      notebook_controller_bdd_test.go:46-57 (one busybox container)
+  C2  the OAuth Notebook of odh-notebook-controller/controllers/
+      notebook_controller_test.go:573-600
+  loadtest  notebook-controller/loadtest/jupyter_test.yaml
+Names are nb-%06d, namespaces ns-%03d with 100 Notebooks per namespace.
+"""
+import json
+import random
+
+SEED = 20261106
+
+
+def _meta(i, extra=None):
+    m = {"name": "nb-%06d" % i, "namespace": "ns-%03d" % (i // 100),
+         "uid": "%08x-0000-4000-8000-%012x" % (i & 0xffffffff, i),
+         "resourceVersion": str(1000 + i), "generation": 1,
+         "creationTimestamp": "2026-11-06T00:00:00Z"}
+    if extra:
+        m.update(extra)
+    return m
+
+
+def notebook_c1(i=0):
+    """C1: the envtest object (name/namespace varied by index)."""
+    if i == 0:
+        md = {"name": "test-notebook", "namespace": "default"}
+    else:
+        md = _meta(i)
+    return {"apiVersion": "kubeflow.org/v1beta1", "kind": "Notebook", "metadata": md,
+            "spec": {"template": {"spec": {"containers": [{"name": "busybox", "image": "busybox"}]}}}}
+
+
+def notebook_c2(i):
+    """C2: the ODH OAuth fixture, one per index."""
+    md = _meta(i)
+    name, ns = md["name"], md["namespace"]
+    md["labels"] = {"app.kubernetes.io/instance": name}
+    md["annotations"] = {
+        "notebooks.opendatahub.io/inject-oauth": "true",
+        "notebooks.opendatahub.io/foo": "bar",
+        "notebooks.opendatahub.io/oauth-logout-url":
+            "https://example.notebook-url/notebook/" + ns + "/" + name,
+    }
+    return {"apiVersion": "kubeflow.org/v1", "kind": "Notebook", "metadata": md,
+            "spec": {"template": {"spec": {
+                "containers": [{"name": name, "image": "registry.redhat.io/ubi8/ubi:latest"}],
+                "volumes": [{"name": "notebook-data",
+                             "persistentVolumeClaim": {"claimName": name + "-data"}}]}}}}
+
+
+def notebook_loadtest(i):
+    """notebook-controller/loadtest/jupyter_test.yaml with start_notebooks.py's renaming."""
+    md = _meta(i)
+    return {"apiVersion": "kubeflow.org/v1", "kind": "Notebook", "metadata": md,
+            "spec": {"template": {"spec": {
+                "serviceAccountName": "default-editor",
+                "volumes": [{"name": "test-vol", "persistentVolumeClaim": {"claimName": "test-pvc-%d" % i}},
+                            {"emptyDir": {"medium": "Memory"}, "name": "dshm"}],
+                "containers": [{
+                    "image": "gcr.io/kubeflow-images-public/tensorflow-1.14.0-notebook-cpu:v1.0.0",
+                    "name": "notebook",
+                    "resources": {"requests": {"cpu": "500m", "memory": "1Gi"}},
+                    "volumeMounts": [{"mountPath": "/home/jovyan", "name": "test-vol"},
+                                     {"mountPath": "/dev/shm", "name": "dshm"}]}]}}}}
+
+
+_LABEL_KEYS = ["app", "app.kubernetes.io/instance", "opendatahub.io/dashboard", "team", "tier",
+               "statefulset", "notebook-name", "opendatahub.io/workbenches", "access-ml-pipeline",
+               "opendatahub.io/odh-managed"]
+_ANN_KEYS = ["foo", "kubectl.kubernetes.io/last-applied-configuration",
+             "notebooks.opendatahub.io/inject-oauth", "opendatahub.io/username",
+             "openshift.io/display-name", "openshift.io/description",
+             "notebooks.kubeflow.org/last-activity", "kubeflow-resource-stopped",
+             "opendatahub.io/image-display-name", "notebooks.opendatahub.io/last-size-selection"]
+_WEIRD = ["", "x", "a\"b", "back\\slash", "uni\u00e9\u4e2d", "tab\there", "new\nline", "<&>",
+          "{\"k\":\"v\"}", "/some/path/", "sp ace", "\u0001ctl"]
+
+
+def notebook_fuzz(rng, i):
+    """A randomly shaped Notebook that walks every branch of the generators."""
+    nb = notebook_c2(i) if rng.random() < 0.5 else notebook_loadtest(i)
+    md = nb["metadata"]
+    if rng.random() < 0.05:
+        md.pop("namespace")
+    if rng.random() < 0.1:
+        md.pop("uid")
+    r = rng.random()
+    if r < 0.15:
+        md.pop("labels", None)
+    elif r < 0.25:
+        md["labels"] = {}
+    else:
+        md["labels"] = {k: rng.choice(_WEIRD[1:4] + ["true", "v1"])
+                        for k in rng.sample(_LABEL_KEYS, rng.randint(1, 6))}
+    r = rng.random()
+    if r < 0.15:
+        md.pop("annotations", None)
+    elif r < 0.25:
+        md["annotations"] = {}
+    else:
+        md["annotations"] = {k: rng.choice(_WEIRD + ["true", "2026-11-06T10:00:00Z"])
+                             for k in rng.sample(_ANN_KEYS, rng.randint(1, 6))}
+        if rng.random() < 0.4:
+            md["annotations"]["notebooks.kubeflow.org/http-rewrite-uri"] = rng.choice(["", "/", "/lab/x"])
+        if rng.random() < 0.5:
+            md["annotations"]["notebooks.kubeflow.org/http-headers-request-set"] = rng.choice([
+                "", "{}", "{\"X-RStudio-Root-Path\":\"/notebook/ns/nb/\"}",
+                "{\"A\":\"b\\\"q\",\"B\":null, \"C\" : \"\\u00e9\"}", "{\"A\":1}", "[1,2]", "null",
+                "not json", "{\"A\":\"b\"} trailing", " { \"A\" : \"b\" } ", "{\"A\":{\"n\":1}}",
+                "{\"A\":\"b\",}", "\"str\""])
+    spec = nb["spec"]["template"]["spec"]
+    c0 = spec["containers"][0]
+    r = rng.random()
+    if r < 0.2:
+        c0["workingDir"] = "/opt/app-root/src"
+    elif r < 0.3:
+        c0["workingDir"] = ""
+    r = rng.random()
+    if r < 0.25:
+        c0["ports"] = [{"containerPort": rng.choice([8888, 8080, 8787]), "name": "nb", "protocol": "TCP"}]
+    elif r < 0.3:
+        c0["ports"] = None
+    elif r < 0.33:
+        c0["ports"] = []
+    elif r < 0.36:
+        c0["ports"] = [{"name": "noport"}]
+    r = rng.random()
+    if r < 0.3:
+        c0["env"] = [{"name": "JUPYTER_NOTEBOOK_PORT", "value": "8888"},
+                     {"name": "NOTEBOOK_ARGS", "value": "--NotebookApp.token='' --x=\"y\""}]
+    elif r < 0.4:
+        c0["env"] = [{"name": "A", "value": "1"}, {"name": "NB_PREFIX", "value": "/custom"}]
+    elif r < 0.45:
+        c0["env"] = []
+    elif r < 0.5:
+        c0["env"] = None
+    r = rng.random()
+    if r < 0.15:
+        spec["securityContext"] = {"fsGroup": 1001, "runAsUser": 1001}
+    elif r < 0.2:
+        spec["securityContext"] = {}
+    elif r < 0.25:
+        spec["securityContext"] = None
+    if rng.random() < 0.3:
+        spec["containers"].append({"name": "sidecar", "image": "side:1", "args": ["--x", "[]{}\","]})
+    if rng.random() < 0.1:
+        spec["containers"] = []
+    if rng.random() < 0.03:
+        nb["spec"] = {}
+    if rng.random() < 0.2:
+        nb["status"] = {"conditions": [], "readyReplicas": 1, "containerState": {}}
+    return nb
+
+
+def dumps(tree, rng=None):
+    """JSON bytes; with an rng, sometimes pretty-printed or ASCII-escaped so the
+    walker sees whitespace and \\u escapes."""
+    if rng is not None:
+        r = rng.random()
+        if r < 0.15:
+            return json.dumps(tree, indent=2, ensure_ascii=False).encode()
+        if r < 0.3:
+            return json.dumps(tree, separators=(", ", ": "), ensure_ascii=True).encode()
+    return json.dumps(tree, separators=(",", ":"), ensure_ascii=False).encode()
+
+
+def corpus(kind, n, seed=SEED, start=0):
+    """n Notebook trees of one kind: 'c1', 'c2', 'loadtest' or 'fuzz'."""
+    if kind == "c1":
+        return [notebook_c1(start + i) for i in range(n)]
+    if kind == "c2":
+        return [notebook_c2(start + i) for i in range(n)]
+    if kind == "loadtest":
+        return [notebook_loadtest(start + i) for i in range(n)]
+    if kind == "fuzz":
+        rng = random.Random(seed + start)
+        return [notebook_fuzz(rng, start + i) for i in range(n)]
+    raise ValueError(kind)

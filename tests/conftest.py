@@ -1,0 +1,44 @@
+import os
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+
+import __graft_entry__ as graft  # noqa: E402
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+
+
+@pytest.fixture(scope="session")
+def pkg():
+    return graft.load_pkg()
+
+
+@pytest.fixture(scope="session")
+def wl(pkg):
+    import importlib
+    return importlib.import_module(graft.PKG_NAME + ".workload")
+
+
+@pytest.fixture(scope="session")
+def hostplan():
+    """The g++ build of the planner headers (tests/hostplan), built on demand."""
+    import subprocess
+    d = os.path.join(ROOT, "tests", "hostplan")
+    subprocess.run(["make", "-C", d], check=True, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)
+    import hostplan_binding
+    return hostplan_binding.HostPlan(os.path.join(d, "libhostplan.so"))
+
+
+@pytest.fixture(scope="session")
+def ctx(pkg):
+    """A libnbrm context on cuda:0; fails loudly (no fallback) without the library or a GPU."""
+    c = pkg.Context(0)
+    yield c
+    c.close()

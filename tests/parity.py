@@ -1,0 +1,41 @@
+"""Shared parity checkers: library output (GPU, or the CPU build of the
+planners) against the oracle, object by object, on canonical JSON."""
+import json
+
+from oracle import gojson, nbc
+
+
+def check_nbc_generate(nbs, outs, status, env, flags, owner_api="kubeflow.org/v1beta1"):
+    """nbs: Notebook trees; outs: 3 byte strings per Notebook; status: per Notebook."""
+    assert len(outs) == 3 * len(nbs)
+    n_checked = 0
+    for i, nb in enumerate(nbs):
+        gens = (nbc.generate_statefulset, nbc.generate_service, nbc.generate_virtualservice)
+        exp, panic = [], False
+        for k, g in enumerate(gens):
+            if not flags & (1 << k):
+                exp.append(None)
+                continue
+            try:
+                e = g(nb, env)
+            except nbc.ReferencePanic:
+                panic = True
+                break
+            if flags & 8:
+                nbc.set_controller_reference(nb, e, owner_api)
+            exp.append(e)
+        if panic:
+            assert status[i] != 0, "doc %d: reference panics, library accepted it" % i
+            assert all(len(outs[3 * i + k]) == 0 for k in range(3))
+            continue
+        assert status[i] == 0, "doc %d: status %d" % (i, status[i])
+        for k in range(3):
+            got = outs[3 * i + k]
+            if exp[k] is None:
+                assert got == b"", (i, k)
+                continue
+            tree = json.loads(got)
+            assert gojson.canon(tree) == gojson.canon(exp[k]), \
+                "doc %d object %d\n got %s\n exp %s" % (i, k, gojson.canon(tree), gojson.canon(exp[k]))
+            n_checked += 1
+    return n_checked
