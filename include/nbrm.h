@@ -131,6 +131,38 @@ enum {
 int nbrm_nbc_generate(nbrm_ctx* ctx, const nbrm_docs* notebooks, uint32_t flags, nbrm_out* out);
 int nbrm_nbc_generate_resident(nbrm_ctx* ctx, uint32_t flags);
 
+/* ---- offsets without allocation -----------------------------------------
+ * No counterpart in the reference: this entry point exists for embedders, not
+ * to replace a reference function.
+ *
+ * Exclusive prefix sum of n object lengths: d_off[i] = d_lens[0] + ... +
+ * d_lens[i-1], d_off[n] = total.  It is the offset step every generator above
+ * runs between planning and writing its objects, offered on its own for
+ * callers that lay out packed batches themselves but must not allocate device
+ * memory while doing so: an admission or reconcile worker that was given a
+ * fixed slice of a GPU shared with the users' notebook pods, where a
+ * cudaMalloc in the request path can fail under the neighbours' memory
+ * pressure and, even when it succeeds, stalls every stream on the device.
+ * This call uses no cudaMalloc/cudaFree and no allocating library routine; its
+ * only scratch is a 32 KiB array (4096 tile sums) that lives inside the loaded
+ * library on every GPU that loads it, until the process exits.
+ *
+ *   d_lens, d_off  DEVICE pointers owned by the caller (n and n+1 entries).
+ *   stream         a cudaStream_t (NULL = the default stream); the call only
+ *                  enqueues work, it does not wait for it.
+ *   err, err_cap   optional buffer for a message when the result is not 0.
+ *
+ * Limit: n <= NBRM_SCAN_NOALLOC_MAX_N (4 194 304); larger n is rejected with
+ * -3 and nothing is launched.  The device used is the calling thread's
+ * current device.  The first call on each device also looks up the scratch
+ * array's device address (cudaGetSymbolAddress); make that first call before
+ * starting any stream capture.  All calls on a device share the scratch, so
+ * two calls that can overlap on the GPU (different streams, no ordering
+ * between them) race: order them with an event or use one stream. */
+#define NBRM_SCAN_NOALLOC_MAX_N 4194304u
+int nbrm_scan_lengths_noalloc(const uint32_t* d_lens, uint64_t n, uint64_t* d_off, void* stream,
+                              char* err, size_t err_cap);
+
 #ifdef __cplusplus
 }
 #endif

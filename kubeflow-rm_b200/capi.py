@@ -83,8 +83,21 @@ def load_library():
     lib.nbrm_download.argtypes = [C.c_void_p, C.POINTER(_Out)]
     lib.nbrm_nbc_generate.argtypes = [C.c_void_p, C.POINTER(_Docs), C.c_uint32, C.POINTER(_Out)]
     lib.nbrm_nbc_generate_resident.argtypes = [C.c_void_p, C.c_uint32]
+    lib.nbrm_scan_lengths_noalloc.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p,
+                                              C.c_char_p, C.c_size_t]
     _lib = lib
     return lib
+
+
+SCAN_NOALLOC_MAX_N = 4194304
+
+
+def scan_lengths_noalloc(d_lens, n, d_off, stream=None):
+    """nbrm_scan_lengths_noalloc on raw DEVICE pointers (ints).  Returns (rc, message)."""
+    lib = load_library()
+    err = C.create_string_buffer(256)
+    rc = lib.nbrm_scan_lengths_noalloc(d_lens, n, d_off, stream, err, len(err))
+    return rc, err.value.decode("utf-8", "replace")
 
 
 class Docs:

@@ -1,5 +1,9 @@
 // nbrm_kernels.cu — the kernels every generator shares: exclusive scan of the
 // planned object lengths and the gather-copy that writes the packed output.
+#include <stdio.h>
+
+#include <mutex>
+
 #include "nbrm_dev.h"
 
 namespace nbrm {
@@ -150,3 +154,73 @@ void launch_emit(const Seg* segs, const uint32_t* nseg, const uint64_t* off, uin
 }
 
 }  // namespace nbrm
+
+// ---------------------------------------------------------------- scan without allocation
+// nbrm_scan_lengths_noalloc (include/nbrm.h): the same three scan kernels, with
+// the per-tile sums kept in a fixed array that is part of the loaded module
+// instead of a cudaMalloc'ed buffer.  4096 tiles x 8 B = 32 KiB per GPU, held
+// from module load until the process exits; one tile covers 1024 lengths, so
+// one call scans at most 4 194 304 lengths.
+//
+// In host code the name g_noalloc_tile_sums is only a handle for the symbol,
+// not an address a kernel can use: the device address is looked up once per
+// device with cudaGetSymbolAddress (below) and that pointer is what the
+// kernels get.
+//
+// All calls on a device share the one array.  Every slot a call reads (tiles
+// 0..t-1) is written by scan_tile_sums earlier in the same call, so nothing
+// has to start at zero and nothing is cleared; slots past t keep what an
+// earlier call left and are never read.  Two calls whose kernels can run at
+// the same time (different streams, no dependency between them) would
+// overwrite each other's tile sums: the caller must order them.
+static const uint32_t NOALLOC_MAX_TILES = 4096;
+static __device__ __align__(256) uint64_t g_noalloc_tile_sums[NOALLOC_MAX_TILES];
+
+namespace {
+const int NOALLOC_MAX_DEVICES = 64;
+uint64_t* g_noalloc_dev_ptr[NOALLOC_MAX_DEVICES];  // device address of the array, per device
+std::mutex g_noalloc_mu;
+
+int noalloc_fail(char* err, size_t cap, int rc, const char* what, const char* detail) {
+  if (err && cap)
+    snprintf(err, cap, "nbrm_scan_lengths_noalloc: %s%s%s", what, detail ? ": " : "",
+             detail ? detail : "");
+  return rc;
+}
+}  // namespace
+
+extern "C" int nbrm_scan_lengths_noalloc(const uint32_t* d_lens, uint64_t n, uint64_t* d_off,
+                                         void* stream, char* err, size_t err_cap) {
+  if (err && err_cap) err[0] = 0;
+  if (!d_off || (n && !d_lens)) return noalloc_fail(err, err_cap, -2, "null pointer", nullptr);
+  const uint64_t max_n = (uint64_t)NOALLOC_MAX_TILES * nbrm::SCAN_TILE;
+  if (n > max_n) {
+    char msg[128];
+    snprintf(msg, sizeof msg, "n = %llu but the fixed scratch covers at most %llu lengths per call",
+             (unsigned long long)n, (unsigned long long)max_n);
+    return noalloc_fail(err, err_cap, -3, "too many lengths", msg);
+  }
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return noalloc_fail(err, err_cap, -1, "cudaGetDevice", cudaGetErrorString(e));
+  if (dev < 0 || dev >= NOALLOC_MAX_DEVICES)
+    return noalloc_fail(err, err_cap, -2, "device ordinal out of range", nullptr);
+  uint64_t* tiles = nullptr;
+  {
+    // Set-up: once per device, done by the first call made with that device
+    // current (it is current here: cudaGetDevice just reported it).
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    if (!g_noalloc_dev_ptr[dev]) {
+      uint64_t* p = nullptr;
+      e = cudaGetSymbolAddress((void**)&p, g_noalloc_tile_sums);
+      if (e != cudaSuccess || !p)
+        return noalloc_fail(err, err_cap, -1, "cudaGetSymbolAddress", cudaGetErrorString(e));
+      g_noalloc_dev_ptr[dev] = p;
+    }
+    tiles = g_noalloc_dev_ptr[dev];
+  }
+  nbrm::launch_scan(d_lens, (uint32_t)n, tiles, d_off, (cudaStream_t)stream);
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return noalloc_fail(err, err_cap, -1, "kernel launch", cudaGetErrorString(e));
+  return 0;
+}
