@@ -111,6 +111,9 @@ uint64_t nbrm_launch_count(const nbrm_ctx* ctx);
 /* Copy a batch into input slot 0..2 of the context; it stays in HBM until the
  * slot is overwritten.  Slot meaning is per entry point. */
 int nbrm_upload(nbrm_ctx* ctx, int slot, const nbrm_docs* docs);
+/* Copy a raw side input (meaning per entry point, e.g. OAuth cookie seeds) to
+ * the device; bytes == 0 clears it. */
+int nbrm_upload_bytes(nbrm_ctx* ctx, const void* host, uint64_t bytes);
 /* Copy the result of the last *_resident call to host memory. */
 int nbrm_download(nbrm_ctx* ctx, nbrm_out* out);
 
@@ -130,6 +133,33 @@ enum {
 };
 int nbrm_nbc_generate(nbrm_ctx* ctx, const nbrm_docs* notebooks, uint32_t flags, nbrm_out* out);
 int nbrm_nbc_generate_resident(nbrm_ctx* ctx, uint32_t flags);
+
+/* ---- ODH reconcile generators -------------------------------------------
+ * Replaces, for a batch of Notebooks, the desired-object constructors that
+ * OpenshiftNotebookReconciler.Reconcile calls (odh-notebook-controller/
+ * controllers/notebook_controller.go:188-232):
+ *   NewNotebookNetworkPolicy  notebook_network.go:131-173
+ *   NewOAuthNetworkPolicy     notebook_network.go:176-210
+ *   NewNotebookRoute          notebook_route.go:34-62
+ *   NewNotebookOAuthRoute     notebook_oauth.go:253-259
+ *   NewNotebookServiceAccount notebook_oauth.go:49-64
+ *   NewNotebookOAuthService   notebook_oauth.go:116-140
+ *   NewNotebookOAuthSecret    notebook_oauth.go:190-210
+ *   NewRoleBinding            notebook_rbac.go:36-58 (as called at :144-153)
+ * and the decisions around them (OAuthInjectionIsEnabled :86, ServiceMeshIsEnabled
+ * :97).  Output: 7 objects per Notebook in the order ctrl NetworkPolicy, OAuth
+ * NetworkPolicy, Route (plain or OAuth), ServiceAccount, Service, Secret,
+ * RoleBinding; an object the reference would not build for that Notebook has
+ * length 0.  NBRM_GEN_OWNER_REF | NBRM_GEN_OWNER_V1 add the ownerReference the
+ * Reconcile* helpers set before Create.  NBRM_ODH_RBAC stands for
+ * SET_PIPELINE_RBAC=="true" with the Role present (notebook_rbac.go:61,144).
+ * seeds16: 16 bytes per Notebook from the caller's CSPRNG (the reference draws
+ * them with crypto/rand, notebook_oauth.go:192-193); the Secret's cookie is
+ * base64(base64(seed)).  NULL seeds give the all-zero seed: tests only. */
+enum { NBRM_ODH_RBAC = 32 };
+int nbrm_odh_generate(nbrm_ctx* ctx, const nbrm_docs* notebooks, const uint8_t* seeds16,
+                      uint32_t flags, nbrm_out* out);
+int nbrm_odh_generate_resident(nbrm_ctx* ctx, uint32_t flags);
 
 /* ---- offsets without allocation -----------------------------------------
  * No counterpart in the reference: this entry point exists for embedders, not

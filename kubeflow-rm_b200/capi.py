@@ -8,6 +8,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 
 GEN_STS, GEN_SVC, GEN_VS, GEN_OWNER_REF, GEN_OWNER_V1 = 1, 2, 4, 8, 16
 GEN_ALL = GEN_STS | GEN_SVC | GEN_VS
+ODH_RBAC = 32
 
 STATUS_NAMES = {0: "OK", 1: "E_PARSE", 2: "E_NO_CONTAINERS", 3: "E_SEGS", 4: "E_PORTS_EMPTY",
                 5: "E_NIL_REPLICAS", 6: "E_DENIED", 7: "E_CONFLICT", 8: "E_LIMIT"}
@@ -83,6 +84,9 @@ def load_library():
     lib.nbrm_download.argtypes = [C.c_void_p, C.POINTER(_Out)]
     lib.nbrm_nbc_generate.argtypes = [C.c_void_p, C.POINTER(_Docs), C.c_uint32, C.POINTER(_Out)]
     lib.nbrm_nbc_generate_resident.argtypes = [C.c_void_p, C.c_uint32]
+    lib.nbrm_upload_bytes.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
+    lib.nbrm_odh_generate.argtypes = [C.c_void_p, C.POINTER(_Docs), C.c_char_p, C.c_uint32, C.POINTER(_Out)]
+    lib.nbrm_odh_generate_resident.argtypes = [C.c_void_p, C.c_uint32]
     lib.nbrm_scan_lengths_noalloc.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p,
                                               C.c_char_p, C.c_size_t]
     _lib = lib
@@ -239,3 +243,16 @@ class Context:
 
     def nbc_generate_resident(self, flags=GEN_ALL):
         self._check(self.lib.nbrm_nbc_generate_resident(self.h, flags))
+
+    # --- ODH reconcile generators
+    def odh_generate(self, docs, seeds=None, flags=GEN_OWNER_REF | GEN_OWNER_V1, copy=True):
+        d = docs.c_struct()
+        o = _Out()
+        self._check(self.lib.nbrm_odh_generate(self.h, C.byref(d), seeds, flags, C.byref(o)))
+        return Result(o, copy)
+
+    def upload_bytes(self, data):
+        self._check(self.lib.nbrm_upload_bytes(self.h, data, len(data) if data else 0))
+
+    def odh_generate_resident(self, flags=GEN_OWNER_REF | GEN_OWNER_V1):
+        self._check(self.lib.nbrm_odh_generate_resident(self.h, flags))

@@ -84,7 +84,8 @@ struct nbrm_ctx {
   EnvLits env;
 
   Slot slot[3];
-  DevBuf segs, nseg, lens, status, aux, out_off, scan_tmp, out;
+  DevBuf segs, nseg, lens, status, aux, out_off, scan_tmp, out, extra;
+  uint64_t extra_bytes = 0;
   PinBuf h_out, h_off, h_status, h_total;
 
   // last *_resident result
@@ -237,7 +238,7 @@ void nbrm_ctx_destroy(nbrm_ctx* c) {
     s.off.release();
   }
   DevBuf* bufs[] = {&c->pool, &c->segs, &c->nseg, &c->lens, &c->status,
-                    &c->aux,  &c->out_off, &c->scan_tmp, &c->out};
+                    &c->aux,  &c->out_off, &c->scan_tmp, &c->out, &c->extra};
   for (auto b : bufs) b->release();
   PinBuf* pins[] = {&c->h_out, &c->h_off, &c->h_status, &c->h_total};
   for (auto b : pins) b->release();
@@ -331,68 +332,91 @@ int nbrm_upload(nbrm_ctx* c, int slot, const nbrm_docs* d) {
 namespace {
 
 // plan -> scan -> (read total) -> emit, shared by every generator.
-struct Pipeline {
-  nbrm_ctx* c;
-  uint32_t n_in, n_out, cap;
+// slots: bit k set = input slot k is read (all used slots must hold the same
+// number of documents; tuple i is document i of each).
+int run_generator(nbrm_ctx* c, int gen, uint32_t slots, uint32_t flags, const void* extra,
+                  uint64_t now) {
+  CK(cudaSetDevice(c->device));
+  uint32_t nobj = 0, cap = 0;
+  gen_shape(gen, &nobj, &cap);
+  uint32_t n = 0;
+  uint64_t in_bytes = 0;
+  bool first = true;
+  PlanIn in;
+  memset(&in, 0, sizeof in);
+  for (int k = 0; k < 3; ++k) {
+    if (!(slots & (1u << k))) continue;
+    Slot& s = c->slot[k];
+    if (!s.off.p) return fail_msg(c, "an input slot this entry point reads was never uploaded");
+    if (first) n = s.n;
+    else if (s.n != n) return fail_msg(c, "input slots hold different numbers of documents");
+    first = false;
+    in.slot[k].data = s.data.as<char>();
+    in.slot[k].off = s.off.as<uint64_t>();
+    in_bytes += s.bytes;
+  }
+  if (in_bytes + (uint64_t)n * AUX_PAD >= 0xffffffffull)
+    return fail_msg(c, "inputs of this batch total 4 GiB or more; split it");
+  in.n = n;
+  in.flags = flags;
+  in.env = c->env;
+  in.extra = extra;
+  in.now = now;
+  const uint32_t n_out = n * nobj;
+  CK(c->segs.reserve((size_t)n_out * cap * sizeof(Seg) + 16));
+  CK(c->nseg.reserve((size_t)n_out * 4 + 16));
+  CK(c->lens.reserve((size_t)n_out * 4 + 16));
+  CK(c->status.reserve((size_t)n * 4 + 16));
+  CK(c->aux.reserve(in_bytes + (uint64_t)n * AUX_PAD + 16));
+  CK(c->out_off.reserve(((size_t)n_out + 1) * 8));
+  CK(c->scan_tmp.reserve(scan_tmp_bytes(n_out)));
+  CK(c->h_total.reserve(8));
   PlanOut po;
-
-  int prepare(uint32_t n_in_, uint32_t out_per_doc, uint32_t cap_, uint64_t aux_bytes) {
-    n_in = n_in_;
-    n_out = n_in_ * out_per_doc;
-    cap = cap_;
-    CK(c->segs.reserve((size_t)n_out * cap * sizeof(Seg) + 16));
-    CK(c->nseg.reserve((size_t)n_out * 4 + 16));
-    CK(c->lens.reserve((size_t)n_out * 4 + 16));
-    CK(c->status.reserve((size_t)n_in * 4 + 16));
-    CK(c->aux.reserve(aux_bytes + 16));
-    CK(c->out_off.reserve(((size_t)n_out + 1) * 8));
-    CK(c->scan_tmp.reserve(scan_tmp_bytes(n_out)));
-    CK(c->h_total.reserve(8));
-    po.segs = c->segs.as<Seg>();
-    po.nseg = c->nseg.as<uint32_t>();
-    po.lens = c->lens.as<uint32_t>();
-    po.status = c->status.as<uint32_t>();
-    po.aux = c->aux.as<char>();
-    po.cap = cap;
-    return 0;
+  po.segs = c->segs.as<Seg>();
+  po.nseg = c->nseg.as<uint32_t>();
+  po.lens = c->lens.as<uint32_t>();
+  po.status = c->status.as<uint32_t>();
+  po.aux = c->aux.as<char>();
+  po.cap = cap;
+  {
+    KScope k(c, K_PLAN, n ? 1 : 0);
+    launch_plan(gen, in, po, c->stream);
   }
-
-  int finish(uint64_t plan_bytes) {
-    {
-      KScope k(c, K_SCAN, n_out ? 3 : 0);
-      launch_scan(po.lens, n_out, c->scan_tmp.as<uint64_t>(), c->out_off.as<uint64_t>(), c->stream);
-    }
-    CK(cudaGetLastError());
-    CK(cudaMemcpyAsync(c->h_total.p, c->out_off.as<uint64_t>() + n_out, 8, cudaMemcpyDeviceToHost,
-                       c->stream));
-    CK(cudaStreamSynchronize(c->stream));
-    uint64_t total = *reinterpret_cast<uint64_t*>(c->h_total.p);
-    if (total >= 0xffffffffull) return fail_msg(c, "output of this batch is 4 GiB or more; split it");
-    CK(c->out.reserve(total + 16));
-    SrcBases b;
-    b.p[SRC_IN0] = c->slot[0].data.as<char>();
-    b.p[SRC_IN1] = c->slot[1].data.as<char>();
-    b.p[SRC_IN2] = c->slot[2].data.as<char>();
-    b.p[SRC_POOL] = c->pool.as<char>();
-    b.p[SRC_AUX] = c->aux.as<char>();
-    {
-      KScope k(c, K_EMIT, n_out ? 1 : 0);
-      launch_emit(po.segs, po.nseg, c->out_off.as<uint64_t>(), n_out, cap, b, c->out.as<char>(),
-                  c->sm_count, c->stream);
-    }
-    CK(cudaGetLastError());
-    if (c->prof) {
-      c->acc.emit_bytes_read += total;
-      c->acc.emit_bytes_written += total;
-      c->acc.plan_bytes_read += plan_bytes;
-    }
-    c->res_n_in = n_in;
-    c->res_n_out = n_out;
-    c->res_bytes = total;
-    c->res_valid = true;
-    return 0;
+  CK(cudaGetLastError());
+  {
+    KScope k(c, K_SCAN, n_out ? 3 : 0);
+    launch_scan(po.lens, n_out, c->scan_tmp.as<uint64_t>(), c->out_off.as<uint64_t>(), c->stream);
   }
-};
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(c->h_total.p, c->out_off.as<uint64_t>() + n_out, 8, cudaMemcpyDeviceToHost,
+                     c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  uint64_t total = *reinterpret_cast<uint64_t*>(c->h_total.p);
+  if (total >= 0xffffffffull) return fail_msg(c, "output of this batch is 4 GiB or more; split it");
+  CK(c->out.reserve(total + 16));
+  SrcBases b;
+  b.p[SRC_IN0] = c->slot[0].data.as<char>();
+  b.p[SRC_IN1] = c->slot[1].data.as<char>();
+  b.p[SRC_IN2] = c->slot[2].data.as<char>();
+  b.p[SRC_POOL] = c->pool.as<char>();
+  b.p[SRC_AUX] = c->aux.as<char>();
+  {
+    KScope k(c, K_EMIT, n_out ? 1 : 0);
+    launch_emit(po.segs, po.nseg, c->out_off.as<uint64_t>(), n_out, cap, b, c->out.as<char>(),
+                c->sm_count, c->stream);
+  }
+  CK(cudaGetLastError());
+  if (c->prof) {
+    c->acc.emit_bytes_read += total;
+    c->acc.emit_bytes_written += total;
+    c->acc.plan_bytes_read += in_bytes;
+  }
+  c->res_n_in = n;
+  c->res_n_out = n_out;
+  c->res_bytes = total;
+  c->res_valid = true;
+  return 0;
+}
 
 }  // namespace
 
@@ -424,30 +448,44 @@ int nbrm_download(nbrm_ctx* c, nbrm_out* out) {
   return 0;
 }
 
+int nbrm_upload_bytes(nbrm_ctx* c, const void* host, uint64_t bytes) {
+  if (!c || (bytes && !host)) return -2;
+  CK(cudaSetDevice(c->device));
+  CK(c->extra.reserve(bytes + 16));
+  if (bytes) CK(cudaMemcpyAsync(c->extra.p, host, bytes, cudaMemcpyHostToDevice, c->stream));
+  c->extra_bytes = bytes;
+  return 0;
+}
+
 int nbrm_nbc_generate_resident(nbrm_ctx* c, uint32_t flags) {
   if (!c) return -2;
-  CK(cudaSetDevice(c->device));
-  Slot& s = c->slot[0];
-  Pipeline p;
-  p.c = c;
-  if (int r = p.prepare(s.n, NBC_OUT_PER_DOC, NBC_SEG_CAP, s.bytes + (uint64_t)s.n * AUX_PAD))
-    return r;
-  DevDocs nb;
-  nb.data = s.data.as<char>();
-  nb.off = s.off.as<uint64_t>();
-  nb.n = s.n;
-  {
-    KScope k(c, K_PLAN, s.n ? 1 : 0);
-    launch_nbc_generate_plan(nb, c->env, flags, p.po, c->stream);
-  }
-  CK(cudaGetLastError());
-  return p.finish(s.bytes);
+  return run_generator(c, GEN_ID_NBC, 1u, flags, nullptr, 0);
 }
 
 int nbrm_nbc_generate(nbrm_ctx* c, const nbrm_docs* notebooks, uint32_t flags, nbrm_out* out) {
   if (!c || !out) return -2;
   if (int r = nbrm_upload(c, 0, notebooks)) return r;
   if (int r = nbrm_nbc_generate_resident(c, flags)) return r;
+  return nbrm_download(c, out);
+}
+
+int nbrm_odh_generate_resident(nbrm_ctx* c, uint32_t flags) {
+  if (!c) return -2;
+  const void* seeds = nullptr;
+  if (c->extra_bytes) {
+    if (c->extra_bytes != (uint64_t)c->slot[0].n * 16)
+      return fail_msg(c, "nbrm_odh_generate: seeds must hold 16 bytes per Notebook");
+    seeds = c->extra.p;
+  }
+  return run_generator(c, GEN_ID_ODH, 1u, flags, seeds, 0);
+}
+
+int nbrm_odh_generate(nbrm_ctx* c, const nbrm_docs* notebooks, const uint8_t* seeds16,
+                      uint32_t flags, nbrm_out* out) {
+  if (!c || !out) return -2;
+  if (int r = nbrm_upload(c, 0, notebooks)) return r;
+  if (int r = nbrm_upload_bytes(c, seeds16, seeds16 ? notebooks->n * 16 : 0)) return r;
+  if (int r = nbrm_odh_generate_resident(c, flags)) return r;
   return nbrm_download(c, out);
 }
 

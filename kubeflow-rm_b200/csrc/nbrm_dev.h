@@ -18,17 +18,26 @@ struct SrcBases {
 
 // One batch of JSON documents resident in device memory.
 struct DevDocs {
-  const char* data;
+  const char* data;     // null when the slot is not used by the generator
   const uint64_t* off;  // n + 1 offsets into data
+};
+
+// What a plan kernel reads: tuple i = document i of every slot in use.
+struct PlanIn {
+  DevDocs slot[3];
   uint32_t n;
+  uint32_t flags;
+  EnvLits env;
+  const void* extra;  // generator-specific side input (device pointer) or null
+  uint64_t now;       // caller's clock, Unix seconds
 };
 
 // Where a plan kernel writes.
 struct PlanOut {
-  Seg* segs;          // n_out * cap
-  uint32_t* nseg;     // n_out
-  uint32_t* lens;     // n_out
-  uint32_t* status;   // one per input document
+  Seg* segs;          // n * NOBJ * cap
+  uint32_t* nseg;     // n * NOBJ
+  uint32_t* lens;     // n * NOBJ
+  uint32_t* status;   // one per input tuple
   char* aux;          // aux arena
   uint32_t cap;
 };
@@ -40,10 +49,9 @@ size_t scan_tmp_bytes(uint32_t n);
 void launch_emit(const Seg* segs, const uint32_t* nseg, const uint64_t* off, uint32_t n_out,
                  uint32_t cap, const SrcBases& bases, char* out, int sm_count, cudaStream_t st);
 
-// nbrm_nbc.cu — 3 output objects per Notebook: StatefulSet, Service, VirtualService
-static const uint32_t NBC_OUT_PER_DOC = 3;
-static const uint32_t NBC_SEG_CAP = 96;
-void launch_nbc_generate_plan(const DevDocs& nb, const EnvLits& env, uint32_t flags,
-                              const PlanOut& out, cudaStream_t st);
+// nbrm_plan_kernels.cu
+enum GenId { GEN_ID_NBC = 0, GEN_ID_ODH = 1 };
+void launch_plan(int gen, const PlanIn& in, const PlanOut& out, cudaStream_t st);
+void gen_shape(int gen, uint32_t* nobj, uint32_t* cap);
 
 }  // namespace nbrm

@@ -1,0 +1,65 @@
+// nbrm_gen.cuh — the frame every generator runs in: one input document (or one
+// aligned tuple of documents from up to three input arenas) in, a fixed number
+// of planned output objects out.  The same frame is instantiated by the plan
+// kernel (nbrm_plan_kernels.cu) and by the CPU test build of the planners.
+#pragma once
+#include "nbrm_plan.cuh"
+
+namespace nbrm {
+
+// Per-document slice of the aux arena: bytes a planner computes.
+struct Aux {
+  char* p;        // start of this document's slice
+  uint32_t abs;   // absolute offset of the slice in the aux arena
+  uint32_t cap;
+  uint32_t used;
+};
+
+// Where the objects planned for ONE input tuple go (already offset to its first object).
+struct ObjSink {
+  Seg* segs;       // n_obj * cap
+  uint32_t* nseg;  // n_obj
+  uint32_t* lens;  // n_obj
+  uint32_t cap;
+};
+
+// Everything a generator sees for one input tuple.
+struct DocCtx {
+  Doc d[3];          // document i of input slot 0..2 (n == 0 when the slot is unused or the doc is empty)
+  uint32_t base[3];  // its absolute offset in that slot's arena
+  Aux aux;
+  const EnvLits* env;
+  uint32_t flags;
+  uint32_t index;       // document index within the batch
+  const void* extra;    // generator-specific side input (device pointer), may be null
+  uint64_t now;         // caller-supplied clock, Unix seconds (generators that stamp times)
+};
+
+// Plans n_obj objects with plan_k(P, k).  One failing object voids the whole
+// tuple: all its objects get length 0 and the error is returned.
+template <class PlanK>
+NB_HD uint32_t plan_objects(const DocCtx& c, ObjSink s, uint32_t n_obj, uint32_t st, PlanK& plan_k) {
+  Planner P;
+  P.base[0] = c.base[0];
+  P.base[1] = c.base[1];
+  P.base[2] = c.base[2];
+  for (uint32_t k = 0; k < n_obj; ++k) {
+    P.begin(s.segs + (size_t)k * s.cap, s.cap);
+    P.err = E_OK;
+    if (!st) {
+      plan_k(P, k);
+      if (P.err) st = P.err;
+    }
+    s.nseg[k] = st ? 0 : P.n;
+    s.lens[k] = st ? 0 : P.total;
+  }
+  if (st) {
+    for (uint32_t k = 0; k < n_obj; ++k) {
+      s.nseg[k] = 0;
+      s.lens[k] = 0;
+    }
+  }
+  return st;
+}
+
+}  // namespace nbrm

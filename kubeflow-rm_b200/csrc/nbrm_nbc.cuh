@@ -5,7 +5,7 @@
 // :392-406, generateService :486-513, generateVirtualService :519-619,
 // ctrl.SetControllerReference at :141,:183,:628.
 #pragma once
-#include "nbrm_plan.cuh"
+#include "nbrm_gen.cuh"
 
 namespace nbrm {
 
@@ -15,14 +15,6 @@ enum GenFlags : uint32_t {
   GEN_VS = 4u,
   GEN_OWNER_REF = 8u,      // add the controller ownerReference (Reconcile :141,:183,:628)
   GEN_OWNER_V1 = 16u,      // ownerReference apiVersion kubeflow.org/v1 (ODH) instead of v1beta1
-};
-
-// Per-document slice of the aux arena: bytes a planner computes.
-struct Aux {
-  char* p;        // start of this document's slice
-  uint32_t abs;   // absolute offset of the slice in the aux arena
-  uint32_t cap;
-  uint32_t used;
 };
 
 // Spans of a Notebook every planner needs.
@@ -470,5 +462,28 @@ NB_HD void plan_virtualservice(Planner& P, const Doc& d, const NbView& v, const 
   P.pool(env.cluster_domain.off, env.cluster_domain.len);
   LIT(P, VS_TAIL);
 }
+
+// The notebook-controller generator: StatefulSet, Service, VirtualService.
+struct GenNbc {
+  static const uint32_t NOBJ = 3;
+  static const uint32_t CAP = 96;
+  struct K {
+    DocCtx& c;
+    const NbView& v;
+    NB_HD void operator()(Planner& P, uint32_t k) {
+      if (!(c.flags & (1u << k))) return;
+      if (k == 0) plan_statefulset(P, c.d[0], v, *c.env, c.flags);
+      else if (k == 1) plan_service(P, c.d[0], v, c.flags);
+      else plan_virtualservice(P, c.d[0], v, *c.env, c.flags, c.aux);
+    }
+  };
+  NB_HD static uint32_t run(DocCtx& c, ObjSink s) {
+    NbView v = view_notebook(c.d[0]);
+    uint32_t st = v.err;
+    if (!st && (!is_object(c.d[0], v.podspec) || !v.c0.ok())) st = E_NO_CONTAINERS;
+    K k{c, v};
+    return plan_objects(c, s, NOBJ, st, k);
+  }
+};
 
 }  // namespace nbrm

@@ -113,6 +113,16 @@ def notebook_fuzz(rng, i):
                 "{\"A\":\"b\\\"q\",\"B\":null, \"C\" : \"\\u00e9\"}", "{\"A\":1}", "[1,2]", "null",
                 "not json", "{\"A\":\"b\"} trailing", " { \"A\" : \"b\" } ", "{\"A\":{\"n\":1}}",
                 "{\"A\":\"b\",}", "\"str\""])
+    if md.get("annotations") is not None:
+        a = md["annotations"]
+        if rng.random() < 0.5:
+            a["notebooks.opendatahub.io/inject-oauth"] = rng.choice(
+                ["true", "false", "1", "T", "TRUE", "True", "t", "yes", "", "0", "tRuE"])
+        if rng.random() < 0.2:
+            a["opendatahub.io/service-mesh"] = rng.choice(["true", "false", "1", "nope"])
+        if rng.random() < 0.3:
+            a["notebooks.opendatahub.io/oauth-logout-url"] = rng.choice(
+                ["", "https://x.example/logout?a=b&c=\"d\"", "https://example/notebook/ns/nb"])
     spec = nb["spec"]["template"]["spec"]
     c0 = spec["containers"][0]
     r = rng.random()

@@ -171,7 +171,7 @@ def new_role_binding(nb, rolebinding_name, role_ref_kind, role_ref_name):
     name, ns = _name_ns(nb)
     return {"apiVersion": "rbac.authorization.k8s.io/v1", "kind": "RoleBinding",
             "metadata": _ometa(rolebinding_name, ns, {"notebook-name": name}),
-            "subjects": [{"kind": "ServiceAccount", "name": name, "namespace": ns}],
+            "subjects": [dict({"kind": "ServiceAccount", "name": name}, **({"namespace": ns} if ns else {}))],
             "roleRef": {"apiGroup": "rbac.authorization.k8s.io", "kind": role_ref_kind,
                         "name": role_ref_name}}
 
@@ -180,6 +180,42 @@ def elyra_role_binding(nb):
     """ReconcileRoleBindings, notebook_rbac.go:144-153."""
     name, _ = _name_ns(nb)
     return new_role_binding(nb, "elyra-pipelines-" + name, "Role", "ds-pipeline-user-access-dspa")
+
+
+ODH_SLOTS = ("ctrl_np", "oauth_np", "route", "service_account", "service", "secret", "rolebinding")
+
+
+def reconcile_objects(nb, ctrl_namespace, rbac=False, cookie_secret="", owner_ref=True):
+    """The desired objects OpenshiftNotebookReconciler.Reconcile builds for one
+    Notebook (notebook_controller.go:188-232), one slot per ODH_SLOTS entry,
+    None where the reference builds nothing:
+      ctrl NetworkPolicy always (:46 of notebook_network.go); OAuth NetworkPolicy
+      unless service mesh (:54-57); RoleBinding when SET_PIPELINE_RBAC is "true"
+      and the Role exists (`rbac`); without service mesh, OAuth on -> SA, Service,
+      Secret, OAuth Route, OAuth off -> plain Route.
+    Each object carries the controller ownerReference (apiVersion kubeflow.org/v1)
+    the Reconcile* helpers add before Create."""
+    from .nbc import set_controller_reference
+    m = meta(nb)
+    mesh = service_mesh_is_enabled(m)
+    oauth = oauth_injection_is_enabled(m)
+    out = [new_notebook_network_policy(nb, ctrl_namespace),
+           None if mesh else new_oauth_network_policy(nb),
+           None, None, None, None,
+           elyra_role_binding(nb) if rbac else None]
+    if not mesh:
+        if oauth:
+            out[2] = new_notebook_oauth_route(nb)
+            out[3] = new_notebook_service_account(nb)
+            out[4] = new_notebook_oauth_service(nb)
+            out[5] = new_notebook_oauth_secret(nb, cookie_secret)
+        else:
+            out[2] = new_notebook_route(nb)
+    if owner_ref:
+        for o in out:
+            if o is not None:
+                set_controller_reference(nb, o, "kubeflow.org/v1")
+    return out
 
 
 # ---------------------------------------------------------------- webhook mutations

@@ -11,6 +11,7 @@
 
 #include "../../include/nbrm.h"
 #include "../../kubeflow-rm_b200/csrc/nbrm_nbc.cuh"
+#include "../../kubeflow-rm_b200/csrc/nbrm_odh.cuh"
 #include "../../kubeflow-rm_b200/csrc/nbrm_pool.h"
 
 using namespace nbrm;
@@ -25,69 +26,86 @@ struct Out {
 };
 Out g_out;
 
-void emit(const std::vector<Seg>& segs, uint32_t n, const char* const bases[SRC_COUNT],
-          std::string& out) {
-  for (uint32_t k = 0; k < n; ++k) {
-    uint32_t len = segs[k].len_src & SEG_LEN_MASK;
-    out.append(bases[segs[k].len_src >> 28] + segs[k].off, len);
+template <class G>
+int run_host(const char* const data[3], const uint64_t* const off[3], uint64_t n, const nbrm_env* env,
+             uint32_t flags, const void* extra, uint64_t now) {
+  std::string pool;
+  EnvLits L;
+  build_pool_host(env, pool, L);
+  uint64_t total_in = 0;
+  for (int k = 0; k < 3; ++k)
+    if (data[k] && n) total_in += off[k][n];
+  std::vector<char> aux(total_in + n * AUX_PAD + 16);
+  g_out.data.clear();
+  g_out.off.assign(1, 0);
+  g_out.status.assign(n, 0);
+  const uint32_t cap = G::CAP;
+  std::vector<Seg> segs((size_t)G::NOBJ * cap);
+  std::vector<uint32_t> nseg(G::NOBJ), lens(G::NOBJ);
+  const char* bases[SRC_COUNT] = {data[0], data[1], data[2], pool.data(), aux.data()};
+  for (uint64_t i = 0; i < n; ++i) {
+    DocCtx c;
+    uint32_t aux_abs = (uint32_t)i * AUX_PAD, aux_cap = AUX_PAD;
+    for (int k = 0; k < 3; ++k) {
+      if (data[k]) {
+        c.d[k].p = data[k] + off[k][i];
+        c.d[k].n = (uint32_t)(off[k][i + 1] - off[k][i]);
+        c.base[k] = (uint32_t)off[k][i];
+        aux_abs += (uint32_t)off[k][i];
+        aux_cap += c.d[k].n;
+      } else {
+        c.d[k].p = nullptr;
+        c.d[k].n = 0;
+        c.base[k] = 0;
+      }
+    }
+    c.aux.abs = aux_abs;
+    c.aux.p = aux.data() + aux_abs;
+    c.aux.cap = aux_cap;
+    c.aux.used = 0;
+    c.env = &L;
+    c.flags = flags;
+    c.index = (uint32_t)i;
+    c.extra = extra;
+    c.now = now;
+    ObjSink s;
+    s.segs = segs.data();
+    s.nseg = nseg.data();
+    s.lens = lens.data();
+    s.cap = cap;
+    uint32_t st = G::run(c, s);
+    g_out.status[i] = st;
+    for (uint32_t k = 0; k < G::NOBJ; ++k) {
+      size_t before = g_out.data.size();
+      for (uint32_t j = 0; j < nseg[k]; ++j) {
+        const Seg& sg = segs[(size_t)k * cap + j];
+        g_out.data.append(bases[sg.len_src >> 28] + sg.off, sg.len_src & SEG_LEN_MASK);
+      }
+      if (g_out.data.size() - before != lens[k]) return -3;  // planned length must equal emitted bytes
+      g_out.off.push_back(g_out.data.size());
+    }
   }
+  return 0;
 }
 }  // namespace
 
 extern "C" {
 
-int hostplan_nbc_generate(const char* data, const uint64_t* off, uint64_t n, const nbrm_env* env,
-                          uint32_t flags, uint32_t cap, const char** out_data,
-                          const uint64_t** out_off, const uint32_t** out_status) {
-  std::string pool;
-  EnvLits L;
-  build_pool_host(env, pool, L);
-  uint64_t total_in = n ? off[n] : 0;
-  std::vector<char> aux(total_in + n * AUX_PAD + 16);
-  g_out.data.clear();
-  g_out.off.assign(1, 0);
-  g_out.status.assign(n, 0);
-  std::vector<Seg> segs(cap);
-  const char* bases[SRC_COUNT] = {data, nullptr, nullptr, pool.data(), aux.data()};
-  for (uint64_t i = 0; i < n; ++i) {
-    Doc d;
-    d.p = data + off[i];
-    d.n = (uint32_t)(off[i + 1] - off[i]);
-    NbView v = view_notebook(d);
-    uint32_t st = v.err;
-    if (!st && (!is_object(d, v.podspec) || !v.c0.ok())) st = E_NO_CONTAINERS;
-    Aux ax;
-    ax.abs = (uint32_t)off[i] + (uint32_t)i * AUX_PAD;
-    ax.p = aux.data() + ax.abs;
-    ax.cap = d.n + AUX_PAD;
-    ax.used = 0;
-    std::string objs[3];
-    for (uint32_t k = 0; k < 3; ++k) {
-      Planner P;
-      P.base[0] = (uint32_t)off[i];
-      P.base[1] = P.base[2] = 0;
-      P.begin(segs.data(), cap);
-      P.err = E_OK;
-      if (!st && (flags & (1u << k))) {
-        if (k == 0) plan_statefulset(P, d, v, L, flags);
-        else if (k == 1) plan_service(P, d, v, flags);
-        else plan_virtualservice(P, d, v, L, flags, ax);
-        if (P.err) st = P.err;
-        else {
-          emit(segs, P.n, bases, objs[k]);
-          if (objs[k].size() != P.total) return -3;
-        }
-      }
-    }
-    for (uint32_t k = 0; k < 3; ++k) {
-      if (!st) g_out.data += objs[k];
-      g_out.off.push_back(g_out.data.size());
-    }
-    g_out.status[i] = st;
+// gen: 0 notebook-controller (3 objects), 1 ODH reconcile (7 objects)
+int hostplan_run(int gen, const char* d0, const uint64_t* o0, const char* d1, const uint64_t* o1,
+                 const char* d2, const uint64_t* o2, uint64_t n, const nbrm_env* env, uint32_t flags,
+                 const void* extra, uint64_t now, uint32_t* nobj, const char** out_data,
+                 const uint64_t** out_off, const uint32_t** out_status) {
+  const char* data[3] = {d0, d1, d2};
+  const uint64_t* off[3] = {o0, o1, o2};
+  int rc = -9;
+  switch (gen) {
+    case 0: rc = run_host<GenNbc>(data, off, n, env, flags, extra, now); *nobj = GenNbc::NOBJ; break;
+    case 1: rc = run_host<GenOdh>(data, off, n, env, flags, extra, now); *nobj = GenOdh::NOBJ; break;
   }
   *out_data = g_out.data.data();
   *out_off = g_out.off.data();
   *out_status = g_out.status.data();
-  return 0;
+  return rc;
 }
 }

@@ -2,7 +2,7 @@
 planners) against the oracle, object by object, on canonical JSON."""
 import json
 
-from oracle import gojson, nbc
+from oracle import gojson, nbc, odh
 
 
 def check_nbc_generate(nbs, outs, status, env, flags, owner_api="kubeflow.org/v1beta1"):
@@ -33,6 +33,29 @@ def check_nbc_generate(nbs, outs, status, env, flags, owner_api="kubeflow.org/v1
             got = outs[3 * i + k]
             if exp[k] is None:
                 assert got == b"", (i, k)
+                continue
+            tree = json.loads(got)
+            assert gojson.canon(tree) == gojson.canon(exp[k]), \
+                "doc %d object %d\n got %s\n exp %s" % (i, k, gojson.canon(tree), gojson.canon(exp[k]))
+            n_checked += 1
+    return n_checked
+
+
+def check_odh_generate(nbs, outs, status, ctrl_ns, seeds, flags):
+    """outs: 7 byte strings per Notebook (oracle.odh.ODH_SLOTS order)."""
+    assert len(outs) == 7 * len(nbs)
+    n_checked = 0
+    for i, nb in enumerate(nbs):
+        cookie = odh.cookie_secret_from_seed(seeds[16 * i:16 * i + 16] if seeds else b"\0" * 16)
+        if not isinstance(nb, dict):
+            continue
+        exp = odh.reconcile_objects(nb, ctrl_ns, rbac=bool(flags & 32), cookie_secret=cookie,
+                                    owner_ref=bool(flags & 8))
+        assert status[i] == 0, (i, status[i])
+        for k in range(7):
+            got = outs[7 * i + k]
+            if exp[k] is None:
+                assert got == b"", (i, k, got)
                 continue
             tree = json.loads(got)
             assert gojson.canon(tree) == gojson.canon(exp[k]), \
