@@ -134,6 +134,36 @@ enum {
 int nbrm_nbc_generate(nbrm_ctx* ctx, const nbrm_docs* notebooks, uint32_t flags, nbrm_out* out);
 int nbrm_nbc_generate_resident(nbrm_ctx* ctx, uint32_t flags);
 
+/* ---- create-or-update decision ---------------------------------------------
+ * Replaces reconcilehelper.CopyStatefulSetFields / CopyServiceFields /
+ * CopyVirtualService (common/reconcilehelper/util.go:107-134, :166-195,
+ * :199-219), the template-label pre-copy of notebook_controller.go:165-169 and
+ * the NotFound -> Create / changed -> Update decision around them
+ * (notebook_controller.go:147-179, :189-210, :636-657).
+ * Input slot 0: desired objects; slot 1: found objects, pair i = document i of
+ * both, an empty found document = NotFound.  The object kind is read from the
+ * desired object's "kind".  Output, one object per pair: the desired object
+ * (the caller Creates it), or the found object with the owned fields copied
+ * over (the caller Updates it), or length 0 (nothing to do).  status
+ * NBRM_E_NIL_REPLICAS marks the pair the reference would crash on. */
+int nbrm_copy_fields(nbrm_ctx* ctx, const nbrm_docs* desired, const nbrm_docs* found, nbrm_out* out);
+int nbrm_copy_fields_resident(nbrm_ctx* ctx);
+/* Move the last result into an input slot without copying it (the slot's old
+ * contents are dropped).  Lets one generator's output feed the next on the device. */
+int nbrm_result_to_slot(nbrm_ctx* ctx, int slot);
+
+/* One notebook-controller reconcile pass for a batch, on the device end to end:
+ * nbrm_nbc_generate, then nbrm_copy_fields against the found objects
+ * (NotebookReconciler.Reconcile, notebook_controller.go:139-218, minus the
+ * client calls).  Slot 0: Notebooks; slot 1: found objects, 3 per Notebook in
+ * the order StatefulSet, Service, VirtualService (empty = NotFound); slot 2 is
+ * used for the desired objects.  Output: 3 objects per Notebook as
+ * nbrm_copy_fields gives them; in steady state every length is 0 and only the
+ * offsets travel back.  The status array then has one entry per object pair. */
+int nbrm_nbc_reconcile(nbrm_ctx* ctx, const nbrm_docs* notebooks, const nbrm_docs* found,
+                       uint32_t flags, nbrm_out* out);
+int nbrm_nbc_reconcile_resident(nbrm_ctx* ctx, uint32_t flags);
+
 /* ---- ODH reconcile generators -------------------------------------------
  * Replaces, for a batch of Notebooks, the desired-object constructors that
  * OpenshiftNotebookReconciler.Reconcile calls (odh-notebook-controller/

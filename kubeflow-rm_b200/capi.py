@@ -87,6 +87,12 @@ def load_library():
     lib.nbrm_upload_bytes.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64]
     lib.nbrm_odh_generate.argtypes = [C.c_void_p, C.POINTER(_Docs), C.c_char_p, C.c_uint32, C.POINTER(_Out)]
     lib.nbrm_odh_generate_resident.argtypes = [C.c_void_p, C.c_uint32]
+    lib.nbrm_result_to_slot.argtypes = [C.c_void_p, C.c_int]
+    lib.nbrm_copy_fields.argtypes = [C.c_void_p, C.POINTER(_Docs), C.POINTER(_Docs), C.POINTER(_Out)]
+    lib.nbrm_copy_fields_resident.argtypes = [C.c_void_p]
+    lib.nbrm_nbc_reconcile.argtypes = [C.c_void_p, C.POINTER(_Docs), C.POINTER(_Docs), C.c_uint32,
+                                       C.POINTER(_Out)]
+    lib.nbrm_nbc_reconcile_resident.argtypes = [C.c_void_p, C.c_uint32]
     lib.nbrm_scan_lengths_noalloc.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p,
                                               C.c_char_p, C.c_size_t]
     _lib = lib
@@ -256,3 +262,23 @@ class Context:
 
     def odh_generate_resident(self, flags=GEN_OWNER_REF | GEN_OWNER_V1):
         self._check(self.lib.nbrm_odh_generate_resident(self.h, flags))
+
+    # --- create-or-update decision / fused reconcile
+    def result_to_slot(self, slot):
+        self._check(self.lib.nbrm_result_to_slot(self.h, slot))
+
+    def copy_fields(self, desired, found, copy=True):
+        d, f, o = desired.c_struct(), found.c_struct(), _Out()
+        self._check(self.lib.nbrm_copy_fields(self.h, C.byref(d), C.byref(f), C.byref(o)))
+        return Result(o, copy)
+
+    def copy_fields_resident(self):
+        self._check(self.lib.nbrm_copy_fields_resident(self.h))
+
+    def nbc_reconcile(self, notebooks, found, flags=GEN_ALL | GEN_OWNER_REF, copy=True):
+        d, f, o = notebooks.c_struct(), found.c_struct(), _Out()
+        self._check(self.lib.nbrm_nbc_reconcile(self.h, C.byref(d), C.byref(f), flags, C.byref(o)))
+        return Result(o, copy)
+
+    def nbc_reconcile_resident(self, flags=GEN_ALL | GEN_OWNER_REF):
+        self._check(self.lib.nbrm_nbc_reconcile_resident(self.h, flags))

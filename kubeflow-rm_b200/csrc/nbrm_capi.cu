@@ -3,6 +3,7 @@
 #include <string.h>
 
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "../../include/nbrm.h"
@@ -332,9 +333,9 @@ int nbrm_upload(nbrm_ctx* c, int slot, const nbrm_docs* d) {
 namespace {
 
 // plan -> scan -> (read total) -> emit, shared by every generator.
-// slots: bit k set = input slot k is read (all used slots must hold the same
-// number of documents; tuple i is document i of each).
-int run_generator(nbrm_ctx* c, int gen, uint32_t slots, uint32_t flags, const void* extra,
+// map[k] = the context slot that feeds generator input k, or -1 (all used slots
+// must hold the same number of documents; tuple i is document i of each).
+int run_generator(nbrm_ctx* c, int gen, const int (&map)[3], uint32_t flags, const void* extra,
                   uint64_t now) {
   CK(cudaSetDevice(c->device));
   uint32_t nobj = 0, cap = 0;
@@ -345,8 +346,8 @@ int run_generator(nbrm_ctx* c, int gen, uint32_t slots, uint32_t flags, const vo
   PlanIn in;
   memset(&in, 0, sizeof in);
   for (int k = 0; k < 3; ++k) {
-    if (!(slots & (1u << k))) continue;
-    Slot& s = c->slot[k];
+    if (map[k] < 0) continue;
+    Slot& s = c->slot[map[k]];
     if (!s.off.p) return fail_msg(c, "an input slot this entry point reads was never uploaded");
     if (first) n = s.n;
     else if (s.n != n) return fail_msg(c, "input slots hold different numbers of documents");
@@ -395,9 +396,9 @@ int run_generator(nbrm_ctx* c, int gen, uint32_t slots, uint32_t flags, const vo
   if (total >= 0xffffffffull) return fail_msg(c, "output of this batch is 4 GiB or more; split it");
   CK(c->out.reserve(total + 16));
   SrcBases b;
-  b.p[SRC_IN0] = c->slot[0].data.as<char>();
-  b.p[SRC_IN1] = c->slot[1].data.as<char>();
-  b.p[SRC_IN2] = c->slot[2].data.as<char>();
+  b.p[SRC_IN0] = map[0] >= 0 ? c->slot[map[0]].data.as<char>() : nullptr;
+  b.p[SRC_IN1] = map[1] >= 0 ? c->slot[map[1]].data.as<char>() : nullptr;
+  b.p[SRC_IN2] = map[2] >= 0 ? c->slot[map[2]].data.as<char>() : nullptr;
   b.p[SRC_POOL] = c->pool.as<char>();
   b.p[SRC_AUX] = c->aux.as<char>();
   {
@@ -459,7 +460,7 @@ int nbrm_upload_bytes(nbrm_ctx* c, const void* host, uint64_t bytes) {
 
 int nbrm_nbc_generate_resident(nbrm_ctx* c, uint32_t flags) {
   if (!c) return -2;
-  return run_generator(c, GEN_ID_NBC, 1u, flags, nullptr, 0);
+  return run_generator(c, GEN_ID_NBC, {0, -1, -1}, flags, nullptr, 0);
 }
 
 int nbrm_nbc_generate(nbrm_ctx* c, const nbrm_docs* notebooks, uint32_t flags, nbrm_out* out) {
@@ -477,7 +478,7 @@ int nbrm_odh_generate_resident(nbrm_ctx* c, uint32_t flags) {
       return fail_msg(c, "nbrm_odh_generate: seeds must hold 16 bytes per Notebook");
     seeds = c->extra.p;
   }
-  return run_generator(c, GEN_ID_ODH, 1u, flags, seeds, 0);
+  return run_generator(c, GEN_ID_ODH, {0, -1, -1}, flags, seeds, 0);
 }
 
 int nbrm_odh_generate(nbrm_ctx* c, const nbrm_docs* notebooks, const uint8_t* seeds16,
@@ -486,6 +487,48 @@ int nbrm_odh_generate(nbrm_ctx* c, const nbrm_docs* notebooks, const uint8_t* se
   if (int r = nbrm_upload(c, 0, notebooks)) return r;
   if (int r = nbrm_upload_bytes(c, seeds16, seeds16 ? notebooks->n * 16 : 0)) return r;
   if (int r = nbrm_odh_generate_resident(c, flags)) return r;
+  return nbrm_download(c, out);
+}
+
+int nbrm_result_to_slot(nbrm_ctx* c, int slot) {
+  if (!c) return -2;
+  if (slot < 0 || slot > 2) return fail_msg(c, "nbrm_result_to_slot: slot must be 0..2");
+  if (!c->res_valid) return fail_msg(c, "nbrm_result_to_slot: no result on this context");
+  Slot& s = c->slot[slot];
+  std::swap(s.data, c->out);
+  std::swap(s.off, c->out_off);
+  s.n = c->res_n_out;
+  s.bytes = c->res_bytes;
+  c->res_valid = false;
+  return 0;
+}
+
+int nbrm_copy_fields_resident(nbrm_ctx* c) {
+  if (!c) return -2;
+  return run_generator(c, GEN_ID_COPY, {0, 1, -1}, 0, nullptr, 0);
+}
+
+int nbrm_copy_fields(nbrm_ctx* c, const nbrm_docs* desired, const nbrm_docs* found, nbrm_out* out) {
+  if (!c || !out) return -2;
+  if (int r = nbrm_upload(c, 0, desired)) return r;
+  if (int r = nbrm_upload(c, 1, found)) return r;
+  if (int r = nbrm_copy_fields_resident(c)) return r;
+  return nbrm_download(c, out);
+}
+
+int nbrm_nbc_reconcile_resident(nbrm_ctx* c, uint32_t flags) {
+  if (!c) return -2;
+  if (int r = run_generator(c, GEN_ID_NBC, {0, -1, -1}, flags, nullptr, 0)) return r;
+  if (int r = nbrm_result_to_slot(c, 2)) return r;  // desired objects become input slot 2
+  return run_generator(c, GEN_ID_COPY, {2, 1, -1}, 0, nullptr, 0);
+}
+
+int nbrm_nbc_reconcile(nbrm_ctx* c, const nbrm_docs* notebooks, const nbrm_docs* found,
+                       uint32_t flags, nbrm_out* out) {
+  if (!c || !out) return -2;
+  if (int r = nbrm_upload(c, 0, notebooks)) return r;
+  if (int r = nbrm_upload(c, 1, found)) return r;
+  if (int r = nbrm_nbc_reconcile_resident(c, flags)) return r;
   return nbrm_download(c, out);
 }
 

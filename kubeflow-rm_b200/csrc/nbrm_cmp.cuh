@@ -1,0 +1,504 @@
+// nbrm_cmp.cuh — "does the found object need an update, and what is written
+// back": the reconcilehelper Copy*Fields functions on JSON text.
+//
+// Reference: components/common/reconcilehelper/util.go — CopyStatefulSetFields
+// :107-134, CopyServiceFields :166-195, CopyVirtualService :199-219; the
+// template-label pre-copy of notebook_controller.go:165-169; and the
+// create-or-update decision around them (notebook_controller.go:147-179,
+// :189-210, :636-657).
+//
+// Input slot 0 holds the desired objects ("from"), slot 1 the found objects
+// ("to", an empty document = NotFound), tuple i pairs document i of both.
+// Output: one object per pair —
+//   found missing            -> the desired object as is   (caller Creates it)
+//   update required          -> the found object with the owned fields copied
+//                               over                       (caller Updates it)
+//   nothing to do            -> length 0
+#pragma once
+#include "nbrm_gen.cuh"
+
+namespace nbrm {
+
+// ---------------------------------------------------------------- DeepEqual on JSON text
+// reflect.DeepEqual of two decoded values, restated on the encoded text:
+// objects compare by key (order-free), a member whose value is null counts as
+// absent (Go nil), arrays compare element by element, strings compare decoded
+// (escapes and raw UTF-8 alike), numbers and literals compare as tokens.
+
+// Decoding cursor over the inside of a JSON string: yields Unicode code points
+// (escapes and raw UTF-8 both decoded), -1 at the end.
+struct StrCur {
+  uint32_t i, end;
+  NB_HD static int hex4(const Doc& d, uint32_t at, uint32_t end) {
+    if (at + 4 > end) return -1;
+    int v = 0;
+    for (int k = 0; k < 4; ++k) {
+      char h = d.p[at + k];
+      int hv = (h >= '0' && h <= '9') ? h - '0'
+               : (h >= 'a' && h <= 'f') ? h - 'a' + 10
+               : (h >= 'A' && h <= 'F') ? h - 'A' + 10 : -1;
+      if (hv < 0) return -1;
+      v = v * 16 + hv;
+    }
+    return v;
+  }
+  NB_HD int next(const Doc& d) {
+    if (i >= end) return -1;
+    unsigned char c = (unsigned char)d.p[i];
+    if (c == '\\') {
+      if (i + 1 >= end) {
+        i = end;
+        return 0xFFFD;
+      }
+      char x = d.p[i + 1];
+      i += 2;
+      switch (x) {
+        case 'b': return '\b';
+        case 'f': return '\f';
+        case 'n': return '\n';
+        case 'r': return '\r';
+        case 't': return '\t';
+        case 'u': {
+          int v = hex4(d, i, end);
+          if (v < 0) {
+            i = end;
+            return 0xFFFD;
+          }
+          i += 4;
+          if (v >= 0xD800 && v < 0xDC00 && i + 6 <= end && d.p[i] == '\\' && d.p[i + 1] == 'u') {
+            int lo = hex4(d, i + 2, end);
+            if (lo >= 0xDC00 && lo < 0xE000) {
+              i += 6;
+              return 0x10000 + ((v - 0xD800) << 10) + (lo - 0xDC00);
+            }
+          }
+          if (v >= 0xD800 && v < 0xE000) return 0xFFFD;
+          return v;
+        }
+        default: return (unsigned char)x;  // \" \\ \/
+      }
+    }
+    if (c < 0x80) {
+      ++i;
+      return c;
+    }
+    int need = (c >= 0xF0) ? 3 : (c >= 0xE0) ? 2 : (c >= 0xC0) ? 1 : 0;
+    int v = (need == 3) ? (c & 0x07) : (need == 2) ? (c & 0x0F) : (need == 1) ? (c & 0x1F) : 0xFFFD;
+    ++i;
+    for (int k = 0; k < need && i < end; ++k, ++i) v = (v << 6) | ((unsigned char)d.p[i] & 0x3F);
+    return v;
+  }
+};
+
+NB_HD bool str_equal(const Doc& a, Span x, const Doc& b, Span y) {
+  if (spans_eq(a, x, b, y)) return true;
+  StrCur ca, cb;
+  Span ix = inner(x), iy = inner(y);
+  ca.i = ix.off;
+  ca.end = ix.end();
+  cb.i = iy.off;
+  cb.end = iy.end();
+  for (;;) {
+    int u = ca.next(a), v = cb.next(b);
+    if (u != v) return false;
+    if (u == -1) return true;
+  }
+}
+
+NB_HD uint32_t count_members(const Doc& d, Span obj) {  // null-valued members do not count
+  ObjIter it(d, obj);
+  Member m;
+  uint32_t n = 0;
+  while (it.next(d, m))
+    if (!is_null(d, m.val)) ++n;
+  return n;
+}
+
+// obj[key] where key is a span of another document (decoded compare).
+NB_HD Span find_key(const Doc& d, Span obj, const Doc& kd, Span key) {
+  ObjIter it(d, obj);
+  Member m;
+  while (it.next(d, m))
+    if (str_equal(d, m.key, kd, key)) return m.val;
+  return mk(0, 0);
+}
+
+static const int EQ_MAX_DEPTH = 24;
+
+struct EqFrame {
+  uint32_t ai, aend;  // cursor in A's container
+  uint32_t bi, bend;  // cursor in B's array (arrays) / B's object span (objects)
+  uint32_t is_obj;
+};
+
+// nil (absent / null) on both sides is equal; nil vs anything else is not.
+NB_HD bool json_equal(const Doc& a, Span x, const Doc& b, Span y) {
+  const bool xn = is_nil(a, x), yn = is_nil(b, y);
+  if (xn || yn) return xn && yn;
+  EqFrame st[EQ_MAX_DEPTH];
+  int sp = 0;
+  // compare one pair of values; containers are pushed
+  Span cx = x, cy = y;
+  bool have = true;
+  for (;;) {
+    if (have) {
+      char ta = a.p[cx.off], tb = b.p[cy.off];
+      if (ta == '"') {
+        if (tb != '"' || !str_equal(a, cx, b, cy)) return false;
+      } else if (ta == '{') {
+        if (tb != '{' || count_members(a, cx) != count_members(b, cy)) return false;
+        if (sp >= EQ_MAX_DEPTH) return false;
+        st[sp].ai = cx.off + 1;
+        st[sp].aend = cx.end() - 1;
+        st[sp].bi = cy.off;
+        st[sp].bend = cy.end();
+        st[sp].is_obj = 1;
+        ++sp;
+      } else if (ta == '[') {
+        if (tb != '[') return false;
+        if (sp >= EQ_MAX_DEPTH) return false;
+        st[sp].ai = cx.off + 1;
+        st[sp].aend = cx.end() - 1;
+        st[sp].bi = cy.off + 1;
+        st[sp].bend = cy.end() - 1;
+        st[sp].is_obj = 0;
+        ++sp;
+      } else {
+        if (!spans_eq(a, cx, b, cy)) return false;
+      }
+      have = false;
+    }
+    if (sp == 0) return true;
+    EqFrame& f = st[sp - 1];
+    if (f.is_obj) {
+      ObjIter it(a, mk(0, 0));
+      it.i = f.ai;
+      it.end = f.aend;
+      Member m;
+      bool got = false;
+      while (it.next(a, m)) {
+        if (is_null(a, m.val)) continue;
+        got = true;
+        break;
+      }
+      f.ai = it.i;
+      if (!got) {
+        --sp;
+        continue;
+      }
+      Span bv = find_key(b, mk(f.bi, f.bend - f.bi), a, m.key);
+      if (is_nil(b, bv)) return false;
+      cx = m.val;
+      cy = bv;
+      have = true;
+    } else {
+      ArrIter ia(a, mk(0, 0)), ib(b, mk(0, 0));
+      ia.i = f.ai;
+      ia.end = f.aend;
+      ib.i = f.bi;
+      ib.end = f.bend;
+      Span ea, eb;
+      bool ga = ia.next(a, ea), gb = ib.next(b, eb);
+      f.ai = ia.i;
+      f.bi = ib.i;
+      if (ga != gb) return false;
+      if (!ga) {
+        --sp;
+        continue;
+      }
+      cx = ea;
+      cy = eb;
+      have = true;
+    }
+  }
+}
+
+// ---------------------------------------------------------------- Copy*Fields
+
+// util.go:109-121: for k, v := range to.<field> { if from.<field>[k] != v { requireUpdate } }
+NB_HD bool map_field_differs(const Doc& from, Span fmap, const Doc& to, Span tmap) {
+  ObjIter it(to, tmap);
+  Member m;
+  while (it.next(to, m)) {
+    if (!is_string(to, m.val)) continue;
+    Span fv = find_key(from, fmap, to, m.key);
+    if (is_string(from, fv)) {
+      if (!str_equal(from, fv, to, m.val)) return true;
+    } else if (m.val.len > 2) {
+      return true;  // missing in from reads as "" there
+    }
+  }
+  return false;
+}
+
+struct ObjView {
+  Span root, meta, labels, annotations, spec;
+};
+
+NB_HD ObjView view_object(const Doc& d) {
+  ObjView v;
+  v.root = root(d);
+  v.meta = find(d, v.root, "metadata");
+  v.labels = find(d, v.meta, "labels");
+  v.annotations = find(d, v.meta, "annotations");
+  v.spec = find(d, v.root, "spec");
+  return v;
+}
+
+// "metadata":{...to's members without labels/annotations..., from's labels/annotations}
+NB_HD void plan_merged_metadata(Planner& P, const Doc& from, const ObjView& fv, const Doc& to,
+                                const ObjView& tv, const Member& meta_member) {
+  P.in(mk(meta_member.key.off, meta_member.val.off - meta_member.key.off), 1);  // "metadata":
+  LIT(P, LBRACE);
+  Sep s;
+  ObjIter it(to, tv.meta);
+  Member m;
+  while (it.next(to, m)) {
+    Span k = inner(m.key);
+    if (bytes_eq(to, k, "labels") || bytes_eq(to, k, "annotations")) continue;
+    s.in(P, to, m.all, 1);
+  }
+  if (!is_nil(from, fv.labels)) {  // to.Labels = from.Labels (:114)
+    s.next(P);
+    LIT(P, KEY_LABELS);
+    P.in(fv.labels, 0);
+  }
+  if (!is_nil(from, fv.annotations)) {  // :121
+    s.next(P);
+    LIT(P, KEY_ANNOTATIONS);
+    P.in(fv.annotations, 0);
+  }
+  LIT(P, RBRACE);
+}
+
+template <uint32_t N>
+NB_HD bool kind_is(const Doc& d, Span rootv, const char (&k)[N]) {
+  return str_eq(d, find(d, rootv, "kind"), k);
+}
+
+// The planner for one (desired, found) pair.
+NB_HD void plan_copy_fields(Planner& P, const Doc& from, const Doc& to) {
+  if (to.n == 0 || !is_object(to, root(to))) {  // NotFound -> Create(desired)
+    P.in(root(from), 0);
+    return;
+  }
+  ObjView fv = view_object(from), tv = view_object(to);
+  if (!is_object(from, fv.root)) {
+    P.err = E_PARSE;
+    return;
+  }
+  bool require = map_field_differs(from, fv.labels, to, tv.labels);        // util.go:109-113
+  require |= map_field_differs(from, fv.annotations, to, tv.annotations);  // :116-120
+
+  if (kind_is(from, fv.root, "VirtualService")) {  // CopyVirtualService, util.go:199-219
+    if (!is_object(from, fv.spec)) return;         // :200-206 from has no spec map: false
+    bool upd = !is_object(to, tv.spec) || !json_equal(from, fv.spec, to, tv.spec);
+    if (!upd) return;
+    LIT(P, LBRACE);
+    Sep s;
+    ObjIter it(to, tv.root);
+    Member m;
+    while (it.next(to, m)) {
+      if (bytes_eq(to, inner(m.key), "spec")) continue;
+      s.in(P, to, m.all, 1);
+    }
+    s.next(P);
+    LIT(P, KEY_SPEC);
+    P.in(fv.spec, 0);
+    LIT(P, RBRACE);
+    return;
+  }
+
+  if (kind_is(from, fv.root, "Service")) {  // CopyServiceFields, util.go:166-195
+    Span fsel = find(from, fv.spec, "selector"), fports = find(from, fv.spec, "ports");
+    Span tsel = find(to, tv.spec, "selector"), tports = find(to, tv.spec, "ports");
+    if (!json_equal(from, fsel, to, tsel)) require = true;      // :184
+    if (!json_equal(from, fports, to, tports)) require = true;  // :189
+    if (!require) return;
+    LIT(P, LBRACE);
+    Sep s;
+    bool had_spec = false;
+    ObjIter it(to, tv.root);
+    Member m;
+    while (it.next(to, m)) {
+      Span k = inner(m.key);
+      if (bytes_eq(to, k, "metadata")) {
+        s.next(P);
+        plan_merged_metadata(P, from, fv, to, tv, m);
+      } else if (bytes_eq(to, k, "spec") && is_object(to, m.val)) {
+        had_spec = true;
+        s.next(P);
+        LIT(P, KEY_SPEC);
+        LIT(P, LBRACE);
+        Sep ss;
+        ObjIter si(to, m.val);
+        Member sm;
+        while (si.next(to, sm)) {
+          Span sk = inner(sm.key);
+          if (bytes_eq(to, sk, "selector") || bytes_eq(to, sk, "ports")) continue;
+          ss.in(P, to, sm.all, 1);
+        }
+        if (!is_nil(from, fsel)) {
+          ss.next(P);
+          LIT(P, KEY_SELECTOR);
+          P.in(fsel, 0);
+        }
+        if (!is_nil(from, fports)) {
+          ss.next(P);
+          LIT(P, KEY_PORTS);
+          P.in(fports, 0);
+        }
+        LIT(P, RBRACE);
+      } else {
+        s.in(P, to, m.all, 1);
+      }
+    }
+    if (!had_spec) {
+      s.next(P);
+      LIT(P, KEY_SPEC);
+      LIT(P, LBRACE);
+      Sep ss;
+      if (!is_nil(from, fsel)) {
+        ss.next(P);
+        LIT(P, KEY_SELECTOR);
+        P.in(fsel, 0);
+      }
+      if (!is_nil(from, fports)) {
+        ss.next(P);
+        LIT(P, KEY_PORTS);
+        P.in(fports, 0);
+      }
+      LIT(P, RBRACE);
+    }
+    LIT(P, RBRACE);
+    return;
+  }
+
+  // StatefulSet: notebook_controller.go:165-169 then CopyStatefulSetFields, util.go:107-134
+  Span frep = find(from, fv.spec, "replicas"), trep = find(to, tv.spec, "replicas");
+  if (is_nil(from, frep) || is_nil(to, trep)) {
+    P.err = E_NIL_REPLICAS;  // util.go:123 dereferences both
+    return;
+  }
+  Span ftmpl = find(from, fv.spec, "template"), ttmpl = find(to, tv.spec, "template");
+  Span ftmeta = find(from, ftmpl, "metadata"), ttmeta = find(to, ttmpl, "metadata");
+  Span ftlabels = find(from, ftmeta, "labels"), ttlabels = find(to, ttmeta, "labels");
+  Span fpod = find(from, ftmpl, "spec"), tpod = find(to, ttmpl, "spec");
+  const bool replicas_differ = !spans_eq(from, frep, to, trep);
+  // pre-copy: template labels follow only when the replica counts differ
+  const bool copy_tlabels = replicas_differ && !json_equal(from, ftlabels, to, ttlabels);
+  if (replicas_differ) require = true;                      // :123-126
+  if (!json_equal(from, fpod, to, tpod)) require = true;    // :128-130
+  if (!require) return;
+
+  LIT(P, LBRACE);
+  Sep s;
+  ObjIter it(to, tv.root);
+  Member m;
+  while (it.next(to, m)) {
+    Span k = inner(m.key);
+    if (bytes_eq(to, k, "metadata")) {
+      s.next(P);
+      plan_merged_metadata(P, from, fv, to, tv, m);
+    } else if (bytes_eq(to, k, "spec")) {
+      s.next(P);
+      LIT(P, KEY_SPEC);
+      LIT(P, LBRACE);
+      Sep ss;
+      ObjIter si(to, m.val);
+      Member sm;
+      while (si.next(to, sm)) {
+        Span sk = inner(sm.key);
+        if (bytes_eq(to, sk, "replicas")) {
+          ss.next(P);
+          LIT(P, KEY_REPLICAS);
+          P.in(frep, 0);
+        } else if (bytes_eq(to, sk, "template")) {
+          ss.next(P);
+          LIT(P, KEY_TEMPLATE);
+          LIT(P, LBRACE);
+          Sep ts;
+          bool had_meta = false;
+          ObjIter ti(to, sm.val);
+          Member tm;
+          while (ti.next(to, tm)) {
+            Span tk = inner(tm.key);
+            if (bytes_eq(to, tk, "spec")) continue;  // replaced below
+            if (bytes_eq(to, tk, "metadata") && copy_tlabels) {
+              had_meta = true;
+              ts.next(P);
+              LIT(P, KEY_METADATA);
+              LIT(P, LBRACE);
+              Sep ms;
+              ObjIter mi(to, tm.val);
+              Member mm;
+              while (mi.next(to, mm)) {
+                if (bytes_eq(to, inner(mm.key), "labels")) continue;
+                ms.in(P, to, mm.all, 1);
+              }
+              if (!is_nil(from, ftlabels)) {
+                ms.next(P);
+                LIT(P, KEY_LABELS);
+                P.in(ftlabels, 0);
+              }
+              LIT(P, RBRACE);
+              continue;
+            }
+            if (bytes_eq(to, tk, "metadata")) had_meta = true;
+            ts.in(P, to, tm.all, 1);
+          }
+          if (!had_meta && copy_tlabels && !is_nil(from, ftlabels)) {
+            ts.next(P);
+            LIT(P, KEY_METADATA);
+            LIT(P, LBRACE);
+            LIT(P, KEY_LABELS);
+            P.in(ftlabels, 0);
+            LIT(P, RBRACE);
+          }
+          if (!is_nil(from, fpod)) {  // to.Spec.Template.Spec = from.Spec.Template.Spec (:131)
+            ts.next(P);
+            LIT(P, KEY_SPEC);
+            P.in(fpod, 0);
+          }
+          LIT(P, RBRACE);
+        } else {
+          ss.in(P, to, sm.all, 1);
+        }
+      }
+      if (!ttmpl.ok() && !is_nil(from, fpod)) {  // found had no template at all
+        ss.next(P);
+        LIT(P, KEY_TEMPLATE);
+        LIT(P, LBRACE);
+        LIT(P, KEY_SPEC);
+        P.in(fpod, 0);
+        LIT(P, RBRACE);
+      }
+      LIT(P, RBRACE);
+    } else {
+      s.in(P, to, m.all, 1);
+    }
+  }
+  LIT(P, RBRACE);
+}
+
+// The compare generator: slot 0 desired, slot 1 found, one output per pair.
+struct GenCopyFields {
+  static const uint32_t NOBJ = 1;
+  static const uint32_t CAP = 48;
+  struct K {
+    DocCtx& c;
+    NB_HD void operator()(Planner& P, uint32_t) { plan_copy_fields(P, c.d[0], c.d[1]); }
+  };
+  NB_HD static uint32_t run(DocCtx& c, ObjSink s) {
+    K k{c};
+    uint32_t st = E_OK;
+    if (c.d[0].n == 0) {  // nothing desired (the generator rejected the Notebook): nothing to do
+      s.nseg[0] = 0;
+      s.lens[0] = 0;
+      return E_OK;
+    }
+    return plan_objects(c, s, NOBJ, st, k);
+  }
+};
+
+}  // namespace nbrm

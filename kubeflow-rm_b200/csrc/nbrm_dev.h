@@ -50,7 +50,7 @@ void launch_emit(const Seg* segs, const uint32_t* nseg, const uint64_t* off, uin
                  uint32_t cap, const SrcBases& bases, char* out, int sm_count, cudaStream_t st);
 
 // nbrm_plan_kernels.cu
-enum GenId { GEN_ID_NBC = 0, GEN_ID_ODH = 1 };
+enum GenId { GEN_ID_NBC = 0, GEN_ID_ODH = 1, GEN_ID_COPY = 2 };
 void launch_plan(int gen, const PlanIn& in, const PlanOut& out, cudaStream_t st);
 void gen_shape(int gen, uint32_t* nobj, uint32_t* cap);
 

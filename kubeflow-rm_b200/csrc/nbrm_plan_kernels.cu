@@ -2,6 +2,7 @@
 #include "nbrm_dev.h"
 #include "nbrm_nbc.cuh"
 #include "nbrm_odh.cuh"
+#include "nbrm_cmp.cuh"
 
 namespace nbrm {
 
@@ -57,6 +58,7 @@ void launch_plan(int gen, const PlanIn& in, const PlanOut& out, cudaStream_t st)
   switch (gen) {
     case GEN_ID_NBC: launch<GenNbc>(in, out, st); break;
     case GEN_ID_ODH: launch<GenOdh>(in, out, st); break;
+    case GEN_ID_COPY: launch<GenCopyFields>(in, out, st); break;
   }
 }
 
@@ -64,6 +66,7 @@ void gen_shape(int gen, uint32_t* nobj, uint32_t* cap) {
   switch (gen) {
     case GEN_ID_NBC: *nobj = GenNbc::NOBJ; *cap = GenNbc::CAP; break;
     case GEN_ID_ODH: *nobj = GenOdh::NOBJ; *cap = GenOdh::CAP; break;
+    case GEN_ID_COPY: *nobj = GenCopyFields::NOBJ; *cap = GenCopyFields::CAP; break;
     default: *nobj = 0; *cap = 0;
   }
 }

@@ -191,3 +191,69 @@ def corpus(kind, n, seed=SEED, start=0):
         rng = random.Random(seed + start)
         return [notebook_fuzz(rng, start + i) for i in range(n)]
     raise ValueError(kind)
+
+
+def found_variant(rng, desired):
+    """A "found" object for `desired` as an API server might return it: None
+    (NotFound), the same object with server-side metadata and status, or a copy
+    that differs in an owned or an unowned field.  Used by the Copy*Fields
+    parity tests (reference: common/reconcilehelper/util.go:107-219)."""
+    import copy
+    r = rng.random()
+    if r < 0.12:
+        return None
+    f = copy.deepcopy(desired)
+    md = f.setdefault("metadata", {})
+    md.update({"uid": "f-%d" % rng.randrange(10**6), "resourceVersion": str(rng.randrange(10**6)),
+               "creationTimestamp": "2026-11-06T00:00:00Z"})
+    kind = desired.get("kind")
+    if kind == "StatefulSet":
+        f["status"] = {"replicas": 1, "readyReplicas": rng.randint(0, 1)}
+        f["spec"]["serviceName"] = ""
+        f["spec"]["podManagementPolicy"] = "OrderedReady"
+    elif kind == "Service":
+        f["spec"]["clusterIP"] = "10.0.%d.%d" % (rng.randrange(256), rng.randrange(256))
+        f["spec"]["sessionAffinity"] = "None"
+        f["status"] = {"loadBalancer": {}}
+    r = rng.random()
+    if r < 0.35:
+        pass                                             # unchanged: no update expected
+    elif r < 0.45:
+        md["labels"] = {"added-by": rng.choice(["someone", ""])}
+    elif r < 0.5:
+        md["annotations"] = {"note": "x", "empty": ""}
+    elif r < 0.6 and kind == "StatefulSet":
+        f["spec"]["replicas"] = 1 - f["spec"]["replicas"]
+        if rng.random() < 0.5:
+            f["spec"]["template"]["metadata"]["labels"]["extra"] = "1"
+    elif r < 0.75 and kind == "StatefulSet":
+        ps = f["spec"]["template"]["spec"]
+        ps["dnsPolicy"] = "ClusterFirst"                 # server-side defaulting
+        ps["containers"][0]["terminationMessagePath"] = "/dev/termination-log"
+    elif r < 0.8 and kind == "StatefulSet":
+        f["spec"]["template"]["spec"]["containers"][0]["image"] = "other:latest"
+    elif r < 0.85 and kind == "StatefulSet":
+        f["spec"]["template"]["metadata"]["labels"]["drift"] = "1"   # not owned unless replicas differ
+    elif r < 0.7 and kind == "Service":
+        f["spec"]["ports"][0]["targetPort"] = 9999
+    elif r < 0.8 and kind == "Service":
+        f["spec"]["selector"] = {"statefulset": "someone-else"}
+    elif r < 0.85 and kind == "Service":
+        f["spec"]["ports"][0]["nodePort"] = None          # null member = nil: still equal
+    elif r < 0.7 and kind == "VirtualService":
+        f["spec"]["hosts"] = ["other.example.com"]
+    elif r < 0.8 and kind == "VirtualService":
+        f["spec"]["http"][0]["timeout"] = "300s"
+    elif r < 0.85 and kind == "VirtualService":
+        del f["spec"]
+    if rng.random() < 0.3:                                # key order must not matter
+        def shuffle(x):
+            if isinstance(x, dict):
+                ks = list(x)
+                rng.shuffle(ks)
+                return {k: shuffle(x[k]) for k in ks}
+            if isinstance(x, list):
+                return [shuffle(v) for v in x]
+            return x
+        f = shuffle(f)
+    return f

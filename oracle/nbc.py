@@ -39,9 +39,12 @@ def json_equal(a, b):
     if type(a) is not type(b):
         return False
     if isinstance(a, dict):
-        if a.keys() != b.keys():
+        # a member whose value is null is a nil field after decoding: same as absent
+        ka = {k for k, v in a.items() if v is not None}
+        kb = {k for k, v in b.items() if v is not None}
+        if ka != kb:
             return False
-        return all(json_equal(a[k], b[k]) for k in a)
+        return all(json_equal(a[k], b[k]) for k in ka)
     if isinstance(a, list):
         return len(a) == len(b) and all(json_equal(x, y) for x, y in zip(a, b))
     return a == b
@@ -304,6 +307,27 @@ def precopy_template_labels(desired, found):
                 ft.pop("labels", None)
             else:
                 ft["labels"] = deepcopy(dl)
+
+
+def create_or_update(desired, found):
+    """The create-or-update decision of Reconcile for one owned object
+    (notebook_controller.go:147-179 StatefulSet, :189-210 Service, :636-657
+    VirtualService).  found is None for NotFound.
+
+    Returns the object the reference would send: `desired` itself (Create), the
+    found object with the owned fields copied over (Update), or None."""
+    if found is None:
+        return deepcopy(desired)
+    to = deepcopy(found)
+    kind = desired.get("kind")
+    if kind == "VirtualService":
+        require = copy_virtualservice(desired, to)
+    elif kind == "Service":
+        require = copy_service_fields(desired, to)
+    else:
+        precopy_template_labels(desired, to)
+        require = copy_statefulset_fields(desired, to)
+    return to if require else None
 
 
 # ---------------------------------------------------------------- status mirroring

@@ -12,6 +12,7 @@
 #include "../../include/nbrm.h"
 #include "../../kubeflow-rm_b200/csrc/nbrm_nbc.cuh"
 #include "../../kubeflow-rm_b200/csrc/nbrm_odh.cuh"
+#include "../../kubeflow-rm_b200/csrc/nbrm_cmp.cuh"
 #include "../../kubeflow-rm_b200/csrc/nbrm_pool.h"
 
 using namespace nbrm;
@@ -102,6 +103,7 @@ int hostplan_run(int gen, const char* d0, const uint64_t* o0, const char* d1, co
   switch (gen) {
     case 0: rc = run_host<GenNbc>(data, off, n, env, flags, extra, now); *nobj = GenNbc::NOBJ; break;
     case 1: rc = run_host<GenOdh>(data, off, n, env, flags, extra, now); *nobj = GenOdh::NOBJ; break;
+    case 2: rc = run_host<GenCopyFields>(data, off, n, env, flags, extra, now); *nobj = GenCopyFields::NOBJ; break;
   }
   *out_data = g_out.data.data();
   *out_off = g_out.off.data();

@@ -4,7 +4,7 @@ import ctypes as C
 
 import numpy as np
 
-GEN_NBC, GEN_ODH = 0, 1
+GEN_NBC, GEN_ODH, GEN_COPY = 0, 1, 2
 
 
 def _pack(docs_list):
@@ -62,3 +62,9 @@ class HostPlan:
         if not docs_list:
             return [], np.zeros(0, dtype=np.uint32)
         return self.run(GEN_ODH, [docs_list], env, flags, extra=seeds)
+
+    def copy_fields(self, desired_list, found_list):
+        """found_list entries may be b"" (NotFound)."""
+        if not desired_list:
+            return [], np.zeros(0, dtype=np.uint32)
+        return self.run(GEN_COPY, [desired_list, found_list])

@@ -62,3 +62,31 @@ def check_odh_generate(nbs, outs, status, ctrl_ns, seeds, flags):
                 "doc %d object %d\n got %s\n exp %s" % (i, k, gojson.canon(tree), gojson.canon(exp[k]))
             n_checked += 1
     return n_checked
+
+
+def check_copy_fields(desired, found, outs, status):
+    """desired/found: trees (found None = NotFound, desired None = nothing desired)."""
+    n_update = n_create = n_none = 0
+    for i, (d, f) in enumerate(zip(desired, found)):
+        if d is None:
+            assert outs[i] == b"" and status[i] == 0
+            continue
+        try:
+            exp = nbc.create_or_update(d, f)
+        except nbc.ReferencePanic:
+            assert status[i] == 5 and outs[i] == b"", i
+            continue
+        assert status[i] == 0, (i, status[i])
+        if exp is None:
+            assert outs[i] == b"", "pair %d: update not expected, got %s" % (i, outs[i])
+            n_none += 1
+            continue
+        assert outs[i] != b"", "pair %d: expected %s" % (i, gojson.canon(exp))
+        tree = json.loads(outs[i])
+        assert gojson.canon(tree) == gojson.canon(exp), \
+            "pair %d\n got %s\n exp %s" % (i, gojson.canon(tree), gojson.canon(exp))
+        if f is None:
+            n_create += 1
+        else:
+            n_update += 1
+    return n_create, n_update, n_none
