@@ -33,7 +33,7 @@ struct StrCur {
     if (at + 4 > end) return -1;
     int v = 0;
     for (int k = 0; k < 4; ++k) {
-      char h = d.p[at + k];
+      char h = d.at(at + k);
       int hv = (h >= '0' && h <= '9') ? h - '0'
                : (h >= 'a' && h <= 'f') ? h - 'a' + 10
                : (h >= 'A' && h <= 'F') ? h - 'A' + 10 : -1;
@@ -44,13 +44,13 @@ struct StrCur {
   }
   NB_HD int next(const Doc& d) {
     if (i >= end) return -1;
-    unsigned char c = (unsigned char)d.p[i];
+    unsigned char c = (unsigned char)d.at(i);
     if (c == '\\') {
       if (i + 1 >= end) {
         i = end;
         return 0xFFFD;
       }
-      char x = d.p[i + 1];
+      char x = d.at(i + 1);
       i += 2;
       switch (x) {
         case 'b': return '\b';
@@ -65,7 +65,7 @@ struct StrCur {
             return 0xFFFD;
           }
           i += 4;
-          if (v >= 0xD800 && v < 0xDC00 && i + 6 <= end && d.p[i] == '\\' && d.p[i + 1] == 'u') {
+          if (v >= 0xD800 && v < 0xDC00 && i + 6 <= end && d.at(i) == '\\' && d.at(i + 1) == 'u') {
             int lo = hex4(d, i + 2, end);
             if (lo >= 0xDC00 && lo < 0xE000) {
               i += 6;
@@ -85,7 +85,7 @@ struct StrCur {
     int need = (c >= 0xF0) ? 3 : (c >= 0xE0) ? 2 : (c >= 0xC0) ? 1 : 0;
     int v = (need == 3) ? (c & 0x07) : (need == 2) ? (c & 0x0F) : (need == 1) ? (c & 0x1F) : 0xFFFD;
     ++i;
-    for (int k = 0; k < need && i < end; ++k, ++i) v = (v << 6) | ((unsigned char)d.p[i] & 0x3F);
+    for (int k = 0; k < need && i < end; ++k, ++i) v = (v << 6) | ((unsigned char)d.at(i) & 0x3F);
     return v;
   }
 };
@@ -142,7 +142,7 @@ NB_HD bool json_equal(const Doc& a, Span x, const Doc& b, Span y) {
   bool have = true;
   for (;;) {
     if (have) {
-      char ta = a.p[cx.off], tb = b.p[cy.off];
+      char ta = a.at(cx.off), tb = b.at(cy.off);
       if (ta == '"') {
         if (tb != '"' || !str_equal(a, cx, b, cy)) return false;
       } else if (ta == '{') {
@@ -238,10 +238,10 @@ struct ObjView {
 NB_HD ObjView view_object(const Doc& d) {
   ObjView v;
   v.root = root(d);
-  v.meta = find(d, v.root, "metadata");
-  v.labels = find(d, v.meta, "labels");
-  v.annotations = find(d, v.meta, "annotations");
-  v.spec = find(d, v.root, "spec");
+  v.meta = FIND(d, v.root, "metadata");
+  v.labels = FIND(d, v.meta, "labels");
+  v.annotations = FIND(d, v.meta, "annotations");
+  v.spec = FIND(d, v.root, "spec");
   return v;
 }
 
@@ -254,8 +254,7 @@ NB_HD void plan_merged_metadata(Planner& P, const Doc& from, const ObjView& fv, 
   ObjIter it(to, tv.meta);
   Member m;
   while (it.next(to, m)) {
-    Span k = inner(m.key);
-    if (bytes_eq(to, k, "labels") || bytes_eq(to, k, "annotations")) continue;
+    if (KEY_IS(to, m, "labels") || KEY_IS(to, m, "annotations")) continue;
     s.in(P, to, m.all, 1);
   }
   if (!is_nil(from, fv.labels)) {  // to.Labels = from.Labels (:114)
@@ -273,7 +272,7 @@ NB_HD void plan_merged_metadata(Planner& P, const Doc& from, const ObjView& fv, 
 
 template <uint32_t N>
 NB_HD bool kind_is(const Doc& d, Span rootv, const char (&k)[N]) {
-  return str_eq(d, find(d, rootv, "kind"), k);
+  return str_eq(d, FIND(d, rootv, "kind"), k);
 }
 
 // The planner for one (desired, found) pair.
@@ -299,7 +298,7 @@ NB_HD void plan_copy_fields(Planner& P, const Doc& from, const Doc& to) {
     ObjIter it(to, tv.root);
     Member m;
     while (it.next(to, m)) {
-      if (bytes_eq(to, inner(m.key), "spec")) continue;
+      if (KEY_IS(to, m, "spec")) continue;
       s.in(P, to, m.all, 1);
     }
     s.next(P);
@@ -310,8 +309,8 @@ NB_HD void plan_copy_fields(Planner& P, const Doc& from, const Doc& to) {
   }
 
   if (kind_is(from, fv.root, "Service")) {  // CopyServiceFields, util.go:166-195
-    Span fsel = find(from, fv.spec, "selector"), fports = find(from, fv.spec, "ports");
-    Span tsel = find(to, tv.spec, "selector"), tports = find(to, tv.spec, "ports");
+    Span fsel = FIND(from, fv.spec, "selector"), fports = FIND(from, fv.spec, "ports");
+    Span tsel = FIND(to, tv.spec, "selector"), tports = FIND(to, tv.spec, "ports");
     if (!json_equal(from, fsel, to, tsel)) require = true;      // :184
     if (!json_equal(from, fports, to, tports)) require = true;  // :189
     if (!require) return;
@@ -321,11 +320,10 @@ NB_HD void plan_copy_fields(Planner& P, const Doc& from, const Doc& to) {
     ObjIter it(to, tv.root);
     Member m;
     while (it.next(to, m)) {
-      Span k = inner(m.key);
-      if (bytes_eq(to, k, "metadata")) {
+      if (KEY_IS(to, m, "metadata")) {
         s.next(P);
         plan_merged_metadata(P, from, fv, to, tv, m);
-      } else if (bytes_eq(to, k, "spec") && is_object(to, m.val)) {
+      } else if (KEY_IS(to, m, "spec") && is_object(to, m.val)) {
         had_spec = true;
         s.next(P);
         LIT(P, KEY_SPEC);
@@ -334,8 +332,7 @@ NB_HD void plan_copy_fields(Planner& P, const Doc& from, const Doc& to) {
         ObjIter si(to, m.val);
         Member sm;
         while (si.next(to, sm)) {
-          Span sk = inner(sm.key);
-          if (bytes_eq(to, sk, "selector") || bytes_eq(to, sk, "ports")) continue;
+          if (KEY_IS(to, sm, "selector") || KEY_IS(to, sm, "ports")) continue;
           ss.in(P, to, sm.all, 1);
         }
         if (!is_nil(from, fsel)) {
@@ -375,15 +372,15 @@ NB_HD void plan_copy_fields(Planner& P, const Doc& from, const Doc& to) {
   }
 
   // StatefulSet: notebook_controller.go:165-169 then CopyStatefulSetFields, util.go:107-134
-  Span frep = find(from, fv.spec, "replicas"), trep = find(to, tv.spec, "replicas");
+  Span frep = FIND(from, fv.spec, "replicas"), trep = FIND(to, tv.spec, "replicas");
   if (is_nil(from, frep) || is_nil(to, trep)) {
     P.err = E_NIL_REPLICAS;  // util.go:123 dereferences both
     return;
   }
-  Span ftmpl = find(from, fv.spec, "template"), ttmpl = find(to, tv.spec, "template");
-  Span ftmeta = find(from, ftmpl, "metadata"), ttmeta = find(to, ttmpl, "metadata");
-  Span ftlabels = find(from, ftmeta, "labels"), ttlabels = find(to, ttmeta, "labels");
-  Span fpod = find(from, ftmpl, "spec"), tpod = find(to, ttmpl, "spec");
+  Span ftmpl = FIND(from, fv.spec, "template"), ttmpl = FIND(to, tv.spec, "template");
+  Span ftmeta = FIND(from, ftmpl, "metadata"), ttmeta = FIND(to, ttmpl, "metadata");
+  Span ftlabels = FIND(from, ftmeta, "labels"), ttlabels = FIND(to, ttmeta, "labels");
+  Span fpod = FIND(from, ftmpl, "spec"), tpod = FIND(to, ttmpl, "spec");
   const bool replicas_differ = !spans_eq(from, frep, to, trep);
   // pre-copy: template labels follow only when the replica counts differ
   const bool copy_tlabels = replicas_differ && !json_equal(from, ftlabels, to, ttlabels);
@@ -396,11 +393,10 @@ NB_HD void plan_copy_fields(Planner& P, const Doc& from, const Doc& to) {
   ObjIter it(to, tv.root);
   Member m;
   while (it.next(to, m)) {
-    Span k = inner(m.key);
-    if (bytes_eq(to, k, "metadata")) {
+    if (KEY_IS(to, m, "metadata")) {
       s.next(P);
       plan_merged_metadata(P, from, fv, to, tv, m);
-    } else if (bytes_eq(to, k, "spec")) {
+    } else if (KEY_IS(to, m, "spec")) {
       s.next(P);
       LIT(P, KEY_SPEC);
       LIT(P, LBRACE);
@@ -408,12 +404,11 @@ NB_HD void plan_copy_fields(Planner& P, const Doc& from, const Doc& to) {
       ObjIter si(to, m.val);
       Member sm;
       while (si.next(to, sm)) {
-        Span sk = inner(sm.key);
-        if (bytes_eq(to, sk, "replicas")) {
+        if (KEY_IS(to, sm, "replicas")) {
           ss.next(P);
           LIT(P, KEY_REPLICAS);
           P.in(frep, 0);
-        } else if (bytes_eq(to, sk, "template")) {
+        } else if (KEY_IS(to, sm, "template")) {
           ss.next(P);
           LIT(P, KEY_TEMPLATE);
           LIT(P, LBRACE);
@@ -422,9 +417,8 @@ NB_HD void plan_copy_fields(Planner& P, const Doc& from, const Doc& to) {
           ObjIter ti(to, sm.val);
           Member tm;
           while (ti.next(to, tm)) {
-            Span tk = inner(tm.key);
-            if (bytes_eq(to, tk, "spec")) continue;  // replaced below
-            if (bytes_eq(to, tk, "metadata") && copy_tlabels) {
+            if (KEY_IS(to, tm, "spec")) continue;  // replaced below
+            if (KEY_IS(to, tm, "metadata") && copy_tlabels) {
               had_meta = true;
               ts.next(P);
               LIT(P, KEY_METADATA);
@@ -433,7 +427,7 @@ NB_HD void plan_copy_fields(Planner& P, const Doc& from, const Doc& to) {
               ObjIter mi(to, tm.val);
               Member mm;
               while (mi.next(to, mm)) {
-                if (bytes_eq(to, inner(mm.key), "labels")) continue;
+                if (KEY_IS(to, mm, "labels")) continue;
                 ms.in(P, to, mm.all, 1);
               }
               if (!is_nil(from, ftlabels)) {
@@ -444,7 +438,7 @@ NB_HD void plan_copy_fields(Planner& P, const Doc& from, const Doc& to) {
               LIT(P, RBRACE);
               continue;
             }
-            if (bytes_eq(to, tk, "metadata")) had_meta = true;
+            if (KEY_IS(to, tm, "metadata")) had_meta = true;
             ts.in(P, to, tm.all, 1);
           }
           if (!had_meta && copy_tlabels && !is_nil(from, ftlabels)) {

@@ -46,12 +46,13 @@ struct PlanOut {
 void launch_scan(const uint32_t* lens, uint32_t n, uint64_t* tile_tmp, uint64_t* off,
                  cudaStream_t st);
 size_t scan_tmp_bytes(uint32_t n);
-void launch_emit(const Seg* segs, const uint32_t* nseg, const uint64_t* off, uint32_t n_out,
-                 uint32_t cap, const SrcBases& bases, char* out, int sm_count, cudaStream_t st);
+void launch_emit(const Seg* segs, const uint32_t* nseg, const uint32_t* lens, const uint64_t* off,
+                 uint32_t n_out, uint32_t cap, uint32_t nobj, const SrcBases& bases, char* out,
+                 int sm_count, cudaStream_t st);
 
 // nbrm_plan_kernels.cu
 enum GenId { GEN_ID_NBC = 0, GEN_ID_ODH = 1, GEN_ID_COPY = 2 };
-void launch_plan(int gen, const PlanIn& in, const PlanOut& out, cudaStream_t st);
+void launch_plan(int gen, const PlanIn& in, const PlanOut& out, uint64_t in_bytes, cudaStream_t st);
 void gen_shape(int gen, uint32_t* nobj, uint32_t* cap);
 
 }  // namespace nbrm

@@ -48,6 +48,7 @@ NB_HD uint32_t plan_objects(const DocCtx& c, ObjSink s, uint32_t n_obj, uint32_t
     P.err = E_OK;
     if (!st) {
       plan_k(P, k);
+      P.finish();
       if (P.err) st = P.err;
     }
     s.nseg[k] = st ? 0 : P.n;

@@ -115,22 +115,121 @@ size_t scan_tmp_bytes(uint32_t n) {
 }
 
 // ---------------------------------------------------------------- emit
-// One warp per output object: read its segment list, copy each segment from
-// its source buffer to the packed output.  Lanes stride over the bytes of a
-// segment, so both the read and the write are contiguous per warp access.
+// Gather-copy of every planned object into the packed output.
+//
+// Objects here are a few hundred bytes assembled from segments of a few dozen
+// bytes (template text alternating with names), so a warp spread over one
+// object idles most of its lanes on per-segment bookkeeping.  emit_objects
+// therefore gives each object to ONE thread, and makes the 32 lanes of a warp
+// work on the same object kind of 32 consecutive input documents (objects are
+// stored document-major, nobj per document), so that the lanes run the same
+// segment structure in lockstep.  A thread reads each source through aligned
+// 16-byte blocks and writes its object through aligned 8-byte words; only the
+// bytes before the first and after the last aligned word are stored singly,
+// because those words are shared with the neighbouring objects.
+//
+// Objects longer than BIG_OBJECT bytes (a Notebook with a huge annotation) are
+// left to emit_big_objects, which spreads a warp over each of them.
+
+static const uint32_t BIG_OBJECT = 16384;
+
+struct Writer {
+  char* o;
+  unsigned long long acc;
+  uint32_t fill;  // bytes in acc
+  uint32_t head;  // single bytes still to store before o is 8-byte aligned
+  __device__ __forceinline__ void init(char* p) {
+    o = p;
+    acc = 0;
+    fill = 0;
+    head = (uint32_t)((8u - ((uint32_t)(unsigned long long)p & 7u)) & 7u);
+  }
+  // append the nb (1..4) low bytes of v
+  __device__ __forceinline__ void put(uint32_t v, uint32_t nb) {
+    while (head && nb) {
+      *o++ = (char)v;
+      v >>= 8;
+      --nb;
+      --head;
+    }
+    if (!nb) return;
+    if (nb < 4) v &= (1u << (8u * nb)) - 1u;
+    acc |= (unsigned long long)v << (8u * fill);
+    fill += nb;
+    if (fill >= 8) {
+      *reinterpret_cast<unsigned long long*>(o) = acc;
+      o += 8;
+      fill -= 8;
+      acc = fill ? ((unsigned long long)v >> (8u * (nb - fill))) : 0ull;
+    }
+  }
+  __device__ __forceinline__ void finish() {
+    for (uint32_t k = 0; k < fill; ++k) o[k] = (char)(acc >> (8u * k));
+  }
+};
+
+__device__ __forceinline__ void copy_segment(const char* src, uint32_t len, Writer& W) {
+  unsigned long long a = (unsigned long long)src;
+  while (len) {
+    const uint4 w = *reinterpret_cast<const uint4*>(a & ~15ull);
+    const uint32_t k = (uint32_t)a & 15u;
+    const uint32_t avail = min(16u - k, len);
+    uint32_t done = 0;
+    while (done < avail) {
+      const uint32_t kk = k + done;
+      const uint32_t word = (kk & 8u) ? ((kk & 4u) ? w.w : w.z) : ((kk & 4u) ? w.y : w.x);
+      const uint32_t sh = kk & 3u;
+      const uint32_t nb = min(4u - sh, avail - done);
+      W.put(word >> (8u * sh), nb);
+      done += nb;
+    }
+    a += avail;
+    len -= avail;
+  }
+}
 
 __global__ void __launch_bounds__(EMIT_THREADS) emit_objects(const Seg* __restrict__ segs,
                                                             const uint32_t* __restrict__ nseg,
+                                                            const uint32_t* __restrict__ lens,
                                                             const uint64_t* __restrict__ off,
                                                             uint32_t n_out, uint32_t cap,
-                                                            SrcBases bases, char* __restrict__ out) {
+                                                            uint32_t nobj, SrcBases bases,
+                                                            char* __restrict__ out) {
+  // thread -> object: lanes of a warp take the same kind k of 32 consecutive documents
+  const uint32_t t = blockIdx.x * EMIT_THREADS + threadIdx.x;
+  const uint32_t per_group = 32u * nobj;
+  const uint32_t group = t / per_group, r = t - group * per_group;
+  const uint32_t k = r >> 5, lane = r & 31u;
+  const uint32_t obj = (group * 32u + lane) * nobj + k;
+  if (obj >= n_out) return;
+  const uint32_t ns = nseg[obj];
+  if (!ns || lens[obj] > BIG_OBJECT) return;
+  const Seg* s = segs + (size_t)obj * cap;
+  Writer W;
+  W.init(out + off[obj]);
+  for (uint32_t j = 0; j < ns; ++j) {
+    const Seg sg = s[j];
+    copy_segment(bases.p[sg.len_src >> 28] + sg.off, sg.len_src & SEG_LEN_MASK, W);
+  }
+  W.finish();
+}
+
+// One warp per object, lanes stride over each segment's bytes; only for the
+// rare objects emit_objects skips.
+__global__ void __launch_bounds__(EMIT_THREADS) emit_big_objects(const Seg* __restrict__ segs,
+                                                                const uint32_t* __restrict__ nseg,
+                                                                const uint32_t* __restrict__ lens,
+                                                                const uint64_t* __restrict__ off,
+                                                                uint32_t n_out, uint32_t cap,
+                                                                SrcBases bases,
+                                                                char* __restrict__ out) {
   const int lane = threadIdx.x & 31;
   const uint32_t warps_per_block = EMIT_THREADS / 32;
   uint32_t w = blockIdx.x * warps_per_block + (threadIdx.x >> 5);
   const uint32_t stride = gridDim.x * warps_per_block;
   for (; w < n_out; w += stride) {
+    if (lens[w] <= BIG_OBJECT) continue;
     const uint32_t ns = nseg[w];
-    if (!ns) continue;
     const Seg* s = segs + (size_t)w * cap;
     char* o = out + off[w];
     for (uint32_t k = 0; k < ns; ++k) {
@@ -143,14 +242,20 @@ __global__ void __launch_bounds__(EMIT_THREADS) emit_objects(const Seg* __restri
   }
 }
 
-void launch_emit(const Seg* segs, const uint32_t* nseg, const uint64_t* off, uint32_t n_out,
-                 uint32_t cap, const SrcBases& bases, char* out, int sm_count, cudaStream_t st) {
+void launch_emit(const Seg* segs, const uint32_t* nseg, const uint32_t* lens, const uint64_t* off,
+                 uint32_t n_out, uint32_t cap, uint32_t nobj, const SrcBases& bases, char* out,
+                 int sm_count, cudaStream_t st) {
   if (!n_out) return;
+  // round the thread count up to whole (32 * nobj) groups
+  const uint32_t per_group = 32u * nobj;
+  const uint64_t threads = (uint64_t)((n_out / nobj + 31u) / 32u) * per_group;
+  const uint32_t blocks = (uint32_t)((threads + EMIT_THREADS - 1) / EMIT_THREADS);
+  emit_objects<<<blocks, EMIT_THREADS, 0, st>>>(segs, nseg, lens, off, n_out, cap, nobj, bases, out);
   uint32_t wpb = EMIT_THREADS / 32;
-  uint32_t blocks = (n_out + wpb - 1) / wpb;
+  uint32_t big_blocks = (n_out + wpb - 1) / wpb;
   uint32_t max_blocks = (uint32_t)sm_count * 8;
-  if (blocks > max_blocks) blocks = max_blocks;
-  emit_objects<<<blocks, EMIT_THREADS, 0, st>>>(segs, nseg, off, n_out, cap, bases, out);
+  if (big_blocks > max_blocks) big_blocks = max_blocks;
+  emit_big_objects<<<big_blocks, EMIT_THREADS, 0, st>>>(segs, nseg, lens, off, n_out, cap, bases, out);
 }
 
 }  // namespace nbrm

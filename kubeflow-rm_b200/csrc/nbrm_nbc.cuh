@@ -20,52 +20,139 @@ enum GenFlags : uint32_t {
 // Spans of a Notebook every planner needs.
 struct NbView {
   Span root, meta, name, ns, uid, labels, annotations, podspec, containers, c0;
+  // annotation values every generator asks for, found in ONE pass over the map
+  Span a_stopped;   // kubeflow-resource-stopped (present when .ok())
+  Span a_rewrite;   // notebooks.kubeflow.org/http-rewrite-uri
+  Span a_headers;   // notebooks.kubeflow.org/http-headers-request-set
+  Span a_oauth;     // notebooks.opendatahub.io/inject-oauth
+  Span a_mesh;      // opendatahub.io/service-mesh
+  Span a_logout;    // notebooks.opendatahub.io/oauth-logout-url
+  Span a_restart;   // notebooks.opendatahub.io/notebook-restart
+  bool l_statefulset, l_notebook_name, l_workbench;  // labels that override a default
   uint32_t err;
 };
 
+// One descent through the Notebook: every byte is read once (plus the values
+// that are walked again by the planners that copy them).
 NB_HD NbView view_notebook(const Doc& d) {
   NbView v;
   v.err = E_OK;
-  v.root = root(d);
-  v.meta = v.name = v.ns = v.uid = v.labels = v.annotations = mk(0, 0);
+  v.root = v.meta = v.name = v.ns = v.uid = v.labels = v.annotations = mk(0, 0);
   v.podspec = v.containers = v.c0 = mk(0, 0);
-  if (!is_object(d, v.root)) {
+  v.a_stopped = v.a_rewrite = v.a_headers = v.a_oauth = v.a_mesh = v.a_logout = v.a_restart = mk(0, 0);
+  v.l_statefulset = v.l_notebook_name = v.l_workbench = false;
+  Cursor c;
+  c.i = skip_ws(d, 0);
+  const uint32_t rs = c.i;
+  if (!obj_enter(d, c)) {
     v.err = E_PARSE;
     return v;
   }
-  Span spec = mk(0, 0);
-  {
-    ObjIter it(d, v.root);
-    Member m;
-    while (it.next(d, m)) {
-      Span k = inner(m.key);
-      if (bytes_eq(d, k, "metadata")) v.meta = m.val;
-      else if (bytes_eq(d, k, "spec")) spec = m.val;
+  Member m;
+  while (obj_key(d, c, m)) {
+    if (KEY_IS(d, m, "metadata")) {
+      const uint32_t s0 = c.i;
+      if (!obj_enter(d, c)) {
+        val_skip(d, c);
+        continue;
+      }
+      Member mm;
+      while (obj_key(d, c, mm)) {
+        if (KEY_IS(d, mm, "name")) {
+          v.name = val_skip(d, c);
+        } else if (KEY_IS(d, mm, "namespace")) {
+          v.ns = val_skip(d, c);
+        } else if (KEY_IS(d, mm, "uid")) {
+          v.uid = val_skip(d, c);
+        } else if (KEY_IS(d, mm, "labels")) {
+          const uint32_t l0 = c.i;
+          if (!obj_enter(d, c)) {
+            val_skip(d, c);
+            continue;
+          }
+          Member lm;
+          while (obj_key(d, c, lm)) {
+            if (KEY_IS(d, lm, "statefulset")) v.l_statefulset = true;
+            else if (KEY_IS(d, lm, "notebook-name")) v.l_notebook_name = true;
+            else if (KEY_IS(d, lm, "opendatahub.io/workbenches")) v.l_workbench = true;
+            val_skip(d, c);
+          }
+          v.labels = mk(l0, c.i - l0);
+        } else if (KEY_IS(d, mm, "annotations")) {
+          const uint32_t a0 = c.i;
+          if (!obj_enter(d, c)) {
+            val_skip(d, c);
+            continue;
+          }
+          Member am;
+          while (obj_key(d, c, am)) {
+            const Span val = val_skip(d, c);
+            if (KEY_IS(d, am, "kubeflow-resource-stopped")) v.a_stopped = val;
+            else if (KEY_IS(d, am, "notebooks.kubeflow.org/http-rewrite-uri")) v.a_rewrite = val;
+            else if (KEY_IS(d, am, "notebooks.kubeflow.org/http-headers-request-set")) v.a_headers = val;
+            else if (KEY_IS(d, am, "notebooks.opendatahub.io/inject-oauth")) v.a_oauth = val;
+            else if (KEY_IS(d, am, "opendatahub.io/service-mesh")) v.a_mesh = val;
+            else if (KEY_IS(d, am, "notebooks.opendatahub.io/oauth-logout-url")) v.a_logout = val;
+            else if (KEY_IS(d, am, "notebooks.opendatahub.io/notebook-restart")) v.a_restart = val;
+          }
+          v.annotations = mk(a0, c.i - a0);
+        } else {
+          val_skip(d, c);
+        }
+      }
+      v.meta = mk(s0, c.i - s0);
+    } else if (KEY_IS(d, m, "spec")) {
+      if (!obj_enter(d, c)) {
+        val_skip(d, c);
+        continue;
+      }
+      Member sm;
+      while (obj_key(d, c, sm)) {
+        if (!KEY_IS(d, sm, "template") || !obj_enter(d, c)) {
+          val_skip(d, c);
+          continue;
+        }
+        Member tm;
+        while (obj_key(d, c, tm)) {
+          if (!KEY_IS(d, tm, "spec")) {
+            val_skip(d, c);
+            continue;
+          }
+          const uint32_t p0 = c.i;
+          if (!obj_enter(d, c)) {
+            val_skip(d, c);
+            continue;
+          }
+          Member pm;
+          while (obj_key(d, c, pm)) {
+            if (!KEY_IS(d, pm, "containers")) {
+              val_skip(d, c);
+              continue;
+            }
+            const uint32_t k0 = c.i;
+            if (!arr_enter(d, c)) {
+              val_skip(d, c);
+              continue;
+            }
+            bool first = true;
+            while (arr_elem(d, c)) {
+              const Span e = val_skip(d, c);
+              if (first && is_object(d, e)) v.c0 = e;
+              first = false;
+            }
+            v.containers = mk(k0, c.i - k0);
+          }
+          v.podspec = mk(p0, c.i - p0);
+        }
+      }
+    } else {
+      val_skip(d, c);
     }
   }
-  {
-    ObjIter it(d, v.meta);
-    Member m;
-    while (it.next(d, m)) {
-      Span k = inner(m.key);
-      if (bytes_eq(d, k, "name")) v.name = m.val;
-      else if (bytes_eq(d, k, "namespace")) v.ns = m.val;
-      else if (bytes_eq(d, k, "uid")) v.uid = m.val;
-      else if (bytes_eq(d, k, "labels")) v.labels = m.val;
-      else if (bytes_eq(d, k, "annotations")) v.annotations = m.val;
-    }
-  }
+  v.root = mk(rs, c.i - rs);
   if (!is_string(d, v.name)) v.name = mk(0, 0);
   if (!is_string(d, v.ns) || v.ns.len == 2) v.ns = mk(0, 0);
   if (!is_string(d, v.uid)) v.uid = mk(0, 0);
-  Span tmpl = find(d, spec, "template");
-  v.podspec = find(d, tmpl, "spec");
-  v.containers = find(d, v.podspec, "containers");
-  if (is_array(d, v.containers)) {
-    ArrIter it(d, v.containers);
-    Span e;
-    if (it.next(d, e) && is_object(d, e)) v.c0 = e;
-  }
   return v;
 }
 
@@ -90,16 +177,25 @@ NB_HD void plan_meta_tail(Planner& P, const NbView& v, uint32_t flags) {
   }
 }
 
-template <uint32_t N>
-NB_HD bool map_has(const Doc& d, Span map, const char (&key)[N]) {
-  return find(d, map, key).ok();
+// strings.Contains(k, "kubectl") || strings.Contains(k, "notebook") (:449) in one
+// pass over the key: the last eight bytes ride in a 64-bit register.
+NB_HD bool key_has_kubectl_or_notebook(const Doc& d, Span k) {
+  const unsigned long long NOTEBOOK = 0x6e6f7465626f6f6bull;  // "notebook"
+  const unsigned long long KUBECTL = 0x006b75626563746cull;   // "kubectl"
+  unsigned long long roll = 0;
+  for (uint32_t j = 0; j < k.len; ++j) {
+    roll = (roll << 8) | (unsigned char)d.at(k.off + j);
+    if (j >= 7 && roll == NOTEBOOK) return true;
+    if (j >= 6 && (roll & 0x00ffffffffffffffull) == KUBECTL) return true;
+  }
+  return false;
 }
 
 NB_HD bool env_has_nb_prefix(const Doc& d, Span env) {
   ArrIter it(d, env);
   Span e;
   while (it.next(d, e)) {
-    if (str_eq(d, find(d, e, "name"), "NB_PREFIX")) return true;
+    if (str_eq(d, FIND(d, e, "name"), "NB_PREFIX")) return true;
   }
   return false;
 }
@@ -119,24 +215,24 @@ NB_HD void plan_statefulset(Planner& P, const Doc& d, const NbView& v, const Env
   put_str(P, v.name);
   plan_meta_tail(P, v, flags);
   LIT(P, STS_SPEC_REPLICAS);
-  if (map_has(d, v.annotations, "kubeflow-resource-stopped")) LIT(P, ZERO);  // :410-412
+  if (v.a_stopped.ok()) LIT(P, ZERO);  // :410-412 metav1.HasAnnotation: presence only
   else LIT(P, ONE);
   LIT(P, STS_SELECTOR);
   put_str(P, v.name);
   LIT(P, STS_TEMPLATE_LABELS);
   {  // :428-432 defaults, :441-444 Notebook labels win
     Sep s;
-    if (!map_has(d, v.labels, "statefulset")) {
+    if (!v.l_statefulset) {
       s.next(P);
       LIT(P, LBL_STATEFULSET);
       put_str(P, v.name);
     }
-    if (!map_has(d, v.labels, "notebook-name")) {
+    if (!v.l_notebook_name) {
       s.next(P);
       LIT(P, LBL_NOTEBOOK_NAME);
       put_str(P, v.name);
     }
-    if (!map_has(d, v.labels, "opendatahub.io/workbenches")) {
+    if (!v.l_workbench) {
       s.next(P);
       LIT(P, LBL_WORKBENCH);
     }
@@ -149,8 +245,7 @@ NB_HD void plan_statefulset(Planner& P, const Doc& d, const NbView& v, const Env
     ObjIter it(d, v.annotations);
     Member m;
     while (it.next(d, m)) {
-      Span k = inner(m.key);
-      if (bytes_contain(d, k, "kubectl") || bytes_contain(d, k, "notebook")) continue;
+      if (key_has_kubectl_or_notebook(d, inner(m.key))) continue;
       if (s.first) LIT(P, STS_ANNOTATIONS);
       s.in(P, d, m.all);
     }
@@ -162,8 +257,7 @@ NB_HD void plan_statefulset(Planner& P, const Doc& d, const NbView& v, const Env
     ObjIter it(d, v.podspec);
     Member m;
     while (it.next(d, m)) {
-      Span k = inner(m.key);
-      if (bytes_eq(d, k, "containers")) {
+      if (KEY_IS(d, m, "containers")) {
         ps.next(P);
         LIT(P, KEY_CONTAINERS);
         Sep cs;
@@ -171,14 +265,13 @@ NB_HD void plan_statefulset(Planner& P, const Doc& d, const NbView& v, const Env
         ObjIter ci(d, v.c0);
         Member c;
         while (ci.next(d, c)) {
-          Span ck = inner(c.key);
-          if (bytes_eq(d, ck, "workingDir")) {
+          if (KEY_IS(d, c, "workingDir")) {
             if (is_nil(d, c.val) || c.val.len == 2) continue;  // "" -> default, :456
             has_wd = true;
-          } else if (bytes_eq(d, ck, "ports")) {
+          } else if (KEY_IS(d, c, "ports")) {
             if (is_nil(d, c.val)) continue;  // nil -> default, :459
             has_ports = true;
-          } else if (bytes_eq(d, ck, "env")) {
+          } else if (KEY_IS(d, c, "env")) {
             if (is_nil(d, c.val)) continue;
             has_env = true;
             if (is_array(d, c.val) && !env_has_nb_prefix(d, c.val)) {  // :402-405
@@ -212,7 +305,7 @@ NB_HD void plan_statefulset(Planner& P, const Doc& d, const NbView& v, const Env
         P.in(mk(v.c0.end(), v.containers.end() - v.c0.end()));
         continue;
       }
-      if (bytes_eq(d, k, "securityContext")) {
+      if (KEY_IS(d, m, "securityContext")) {
         if (is_nil(d, m.val)) continue;  // nil pointer, :476
         has_sc = true;
       }
@@ -234,7 +327,7 @@ NB_HD void plan_service(Planner& P, const Doc& d, const NbView& v, uint32_t flag
   LIT(P, SVC_PORTS);
   P.in(inner(v.name));
   LIT(P, SVC_TARGETPORT);
-  Span ports = find(d, v.c0, "ports");
+  Span ports = FIND(d, v.c0, "ports");
   if (is_nil(d, ports)) {  // :490 nil test
     LIT(P, PORT_8888);
   } else {
@@ -244,7 +337,7 @@ NB_HD void plan_service(Planner& P, const Doc& d, const NbView& v, uint32_t flag
       P.err = E_PORTS_EMPTY;  // :491 would index an empty slice
       return;
     }
-    Span cp = find(d, e, "containerPort");
+    Span cp = FIND(d, e, "containerPort");
     if (cp.ok() && !is_null(d, cp)) P.in(cp);
     else LIT(P, ZERO);
   }
@@ -266,14 +359,14 @@ NB_HD uint32_t unescape(const Doc& d, Span s, char* out, uint32_t cap) {
   uint32_t o = 0, i = s.off, e = s.end();
   while (i < e) {
     if (o + 4 > cap) return 0xffffffffu;
-    char c = d.p[i];
+    char c = d.at(i);
     if (c != '\\') {
       out[o++] = c;
       ++i;
       continue;
     }
     if (i + 1 >= e) return 0xffffffffu;
-    char x = d.p[i + 1];
+    char x = d.at(i + 1);
     i += 2;
     switch (x) {
       case '"': out[o++] = '"'; break;
@@ -288,16 +381,16 @@ NB_HD uint32_t unescape(const Doc& d, Span s, char* out, uint32_t cap) {
         if (i + 4 > e) return 0xffffffffu;
         uint32_t cp = 0;
         for (int k = 0; k < 4; ++k) {
-          int h = hexval(d.p[i + k]);
+          int h = hexval(d.at(i + k));
           if (h < 0) return 0xffffffffu;
           cp = cp * 16 + (uint32_t)h;
         }
         i += 4;
-        if (cp >= 0xD800 && cp < 0xDC00 && i + 6 <= e && d.p[i] == '\\' && d.p[i + 1] == 'u') {
+        if (cp >= 0xD800 && cp < 0xDC00 && i + 6 <= e && d.at(i) == '\\' && d.at(i + 1) == 'u') {
           uint32_t lo = 0;
           bool okh = true;
           for (int k = 0; k < 4; ++k) {
-            int h = hexval(d.p[i + 2 + k]);
+            int h = hexval(d.at(i + 2 + k));
             if (h < 0) okh = false;
             lo = lo * 16 + (uint32_t)(h < 0 ? 0 : h);
           }
@@ -333,19 +426,19 @@ NB_HD uint32_t unescape(const Doc& d, Span s, char* out, uint32_t cap) {
 
 // End index of the strictly valid JSON string starting at i, or 0.
 NB_HD uint32_t strict_string_end(const Doc& d, uint32_t i) {
-  if (i >= d.n || d.p[i] != '"') return 0;
+  if (i >= d.n || d.at(i) != '"') return 0;
   uint32_t j = i + 1;
   while (j < d.n) {
-    unsigned char c = (unsigned char)d.p[j];
+    unsigned char c = (unsigned char)d.at(j);
     if (c == '"') return j + 1;
     if (c < 0x20) return 0;
     if (c == '\\') {
       if (j + 1 >= d.n) return 0;
-      char x = d.p[j + 1];
+      char x = d.at(j + 1);
       if (x == 'u') {
         if (j + 6 > d.n) return 0;
         for (int k = 2; k < 6; ++k)
-          if (hexval(d.p[j + k]) < 0) return 0;
+          if (hexval(d.at(j + k)) < 0) return 0;
         j += 6;
       } else if (x == '"' || x == '\\' || x == '/' || x == 'b' || x == 'f' || x == 'n' ||
                  x == 'r' || x == 't') {
@@ -364,7 +457,7 @@ NB_HD uint32_t strict_string_end(const Doc& d, uint32_t i) {
 // the annotation must decode to a flat object of strings (null counts as ""),
 // anything else gives the empty map.  Emits the members (no braces).
 NB_HD void plan_headers_set(Planner& P, const Doc& d, const NbView& v, Aux& aux) {
-  Span a = find(d, v.annotations, "notebooks.kubeflow.org/http-headers-request-set");
+  Span a = v.a_headers;
   if (!is_string(d, a) || a.len == 2) return;
   char* out = aux.p + aux.used;
   uint32_t n = unescape(d, inner(a), out, aux.cap - aux.used);
@@ -375,10 +468,10 @@ NB_HD void plan_headers_set(Planner& P, const Doc& d, const NbView& v, Aux& aux)
   // pass 1: validate strictly; pass 2: emit
   for (int pass = 0; pass < 2; ++pass) {
     uint32_t i = skip_ws(t, 0);
-    if (i >= t.n || t.p[i] != '{') return;
+    if (i >= t.n || t.at(i) != '{') return;
     i = skip_ws(t, i + 1);
     bool first = true;
-    if (i < t.n && t.p[i] == '}') {
+    if (i < t.n && t.at(i) == '}') {
       ++i;
     } else {
       for (;;) {
@@ -386,12 +479,12 @@ NB_HD void plan_headers_set(Planner& P, const Doc& d, const NbView& v, Aux& aux)
         if (!ke) return;
         uint32_t ks = i;
         i = skip_ws(t, ke);
-        if (i >= t.n || t.p[i] != ':') return;
+        if (i >= t.n || t.at(i) != ':') return;
         i = skip_ws(t, i + 1);
         uint32_t vs = i, ve;
         bool isnull = false;
-        if (i + 4 <= t.n && t.p[i] == 'n' && t.p[i + 1] == 'u' && t.p[i + 2] == 'l' &&
-            t.p[i + 3] == 'l') {
+        if (i + 4 <= t.n && t.at(i) == 'n' && t.at(i + 1) == 'u' && t.at(i + 2) == 'l' &&
+            t.at(i + 3) == 'l') {
           ve = i + 4;
           isnull = true;
         } else {
@@ -407,11 +500,11 @@ NB_HD void plan_headers_set(Planner& P, const Doc& d, const NbView& v, Aux& aux)
         }
         first = false;
         i = skip_ws(t, ve);
-        if (i < t.n && t.p[i] == ',') {
+        if (i < t.n && t.at(i) == ',') {
           i = skip_ws(t, i + 1);
           continue;
         }
-        if (i < t.n && t.p[i] == '}') {
+        if (i < t.n && t.at(i) == '}') {
           ++i;
           break;
         }
@@ -444,7 +537,7 @@ NB_HD void plan_virtualservice(Planner& P, const Doc& d, const NbView& v, const 
   LIT(P, SLASH);
   P.in(inner(v.name));
   LIT(P, VS_REWRITE);
-  Span rw = find(d, v.annotations, "notebooks.kubeflow.org/http-rewrite-uri");
+  Span rw = v.a_rewrite;
   if (is_string(d, rw) && rw.len > 2) {  // :533
     P.in(rw);
   } else {

@@ -29,10 +29,10 @@ NB_HD bool annotation_true(const Doc& d, Span v) {
 }
 
 NB_HD bool oauth_enabled(const Doc& d, const NbView& v) {
-  return annotation_true(d, find(d, v.annotations, "notebooks.opendatahub.io/inject-oauth"));
+  return annotation_true(d, v.a_oauth);
 }
 NB_HD bool mesh_enabled(const Doc& d, const NbView& v) {
-  return annotation_true(d, find(d, v.annotations, "opendatahub.io/service-mesh"));
+  return annotation_true(d, v.a_mesh);
 }
 
 NB_HD void plan_labels_notebook_name(Planner& P, const NbView& v) {

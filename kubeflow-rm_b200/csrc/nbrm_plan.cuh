@@ -41,35 +41,50 @@ static const uint32_t SEG_LEN_MASK = 0x0fffffffu;
 struct Planner {
   Seg* segs;
   uint32_t cap;
-  uint32_t n;
+  uint32_t n;      // segments already written to segs[]
   uint32_t total;
   uint32_t err;
   uint32_t base[3];  // absolute offset of this thread's document inside input arena k
+  // the segment being built lives in registers until the next one starts:
+  // consecutive pieces of the same source merge without touching memory
+  uint32_t cur_off, cur_len, cur_src;
 
   NB_HD void begin(Seg* s, uint32_t c) {
     segs = s;
     cap = c;
     n = 0;
     total = 0;
+    cur_len = 0;
+    cur_off = 0;
+    cur_src = 0;
   }
-  NB_HD void put(uint32_t src, uint32_t off, uint32_t len) {
-    if (!len) return;
-    total += len;
-    if (n) {
-      Seg& p = segs[n - 1];
-      uint32_t plen = p.len_src & SEG_LEN_MASK;
-      if ((p.len_src >> 28) == src && p.off + plen == off && plen + len <= SEG_LEN_MASK) {
-        p.len_src += len;
-        return;
-      }
-    }
+  NB_HD void flush() {
+    if (!cur_len) return;
     if (n < cap) {
-      segs[n].off = off;
-      segs[n].len_src = (src << 28) | len;
+      segs[n].off = cur_off;
+      segs[n].len_src = (cur_src << 28) | cur_len;
       ++n;
     } else {
       err = E_SEGS;
     }
+    cur_len = 0;
+  }
+  NB_HD void put(uint32_t src, uint32_t off, uint32_t len) {
+    if (!len) return;
+    total += len;
+    if (cur_len && cur_src == src && cur_off + cur_len == off && cur_len + len <= SEG_LEN_MASK) {
+      cur_len += len;
+      return;
+    }
+    flush();
+    cur_src = src;
+    cur_off = off;
+    cur_len = len;
+  }
+  // number of segments once the open one is written
+  NB_HD uint32_t finish() {
+    flush();
+    return n;
   }
   NB_HD void in(Span s, uint32_t k = 0) { put(k, base[k] + s.off, s.len); }
   NB_HD void pool(uint32_t off, uint32_t len) { put(SRC_POOL, off, len); }
@@ -116,14 +131,11 @@ struct Sep {
   // previous copied bytes and the input already has the comma, the comma is
   // taken from the input so the run stays one segment.
   NB_HD void in(Planner& P, const Doc& d, Span s, uint32_t k = 0) {
-    if (!first && P.n && s.off > 0 && d.p[s.off - 1] == ',') {
-      Seg& p = P.segs[P.n - 1];
-      uint32_t plen = p.len_src & SEG_LEN_MASK;
-      if ((p.len_src >> 28) == k && p.off + plen == P.base[k] + s.off - 1) {
-        p.len_src += 1 + s.len;
-        P.total += 1 + s.len;
-        return;
-      }
+    if (!first && P.cur_len && P.cur_src == k && s.off > 0 &&
+        P.cur_off + P.cur_len == P.base[k] + s.off - 1 && d.at(s.off - 1) == ',') {
+      P.cur_len += 1 + s.len;
+      P.total += 1 + s.len;
+      return;
     }
     next(P);
     P.in(s, k);

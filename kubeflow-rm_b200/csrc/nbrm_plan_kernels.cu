@@ -9,17 +9,59 @@ namespace nbrm {
 // One input tuple per thread (document i of every input slot in use).  Writes,
 // for each of G::NOBJ output objects, the segment list, its byte length and the
 // segment count; plus one status word per tuple.
+//
+// The documents of a block's tuples are contiguous in each input arena, so the
+// block first copies that range of every slot into shared memory with aligned
+// 16-byte loads (coalesced, each input byte read from HBM once) and the
+// planners then walk shared memory.  Walking global memory directly makes every
+// byte access of a warp touch 32 different cache lines, which is what bounded
+// the first version of this kernel.  A block whose documents do not fit (a
+// Notebook with a huge annotation) walks global memory instead.
+extern __shared__ __align__(16) char plan_smem[];
+
 template <class G>
-__global__ void __launch_bounds__(PLAN_THREADS) plan_kernel(PlanIn in, PlanOut out) {
-  uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+__global__ void plan_kernel(PlanIn in, PlanOut out, uint32_t smem_cap) {
+  const uint32_t b0 = blockIdx.x * blockDim.x;
+  const uint32_t b1 = min(b0 + blockDim.x, in.n);
+  const uint32_t i = b0 + threadIdx.x;
+
+  // the block's byte range in every slot, widened to 16-byte boundaries
+  uint64_t g0[3], a0[3];
+  uint32_t soff[3], total = 0;
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    g0[k] = a0[k] = 0;
+    soff[k] = total;
+    if (in.slot[k].data) {
+      g0[k] = in.slot[k].off[b0];
+      const uint64_t g1 = in.slot[k].off[b1];
+      a0[k] = g0[k] & ~15ull;
+      const uint64_t a1 = (g1 + 15ull) & ~15ull;
+      const uint64_t bytes = a1 - a0[k];
+      total = bytes > 0xffffffffull - total ? 0xffffffffu : total + (uint32_t)bytes;
+    }
+  }
+  const bool staged = total <= smem_cap;
+  if (staged) {
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      if (!in.slot[k].data) continue;
+      const uint32_t chunks = ((k < 2 ? soff[k + 1] : total) - soff[k]) >> 4;
+      const uint4* src = reinterpret_cast<const uint4*>(in.slot[k].data + a0[k]);
+      uint4* dst = reinterpret_cast<uint4*>(plan_smem + soff[k]);
+      for (uint32_t c = threadIdx.x; c < chunks; c += blockDim.x) dst[c] = src[c];
+    }
+  }
+  __syncthreads();
   if (i >= in.n) return;
+
   DocCtx c;
   uint32_t aux_abs = i * AUX_PAD, aux_cap = AUX_PAD;
 #pragma unroll
   for (int k = 0; k < 3; ++k) {
     if (in.slot[k].data) {
       const uint64_t o0 = in.slot[k].off[i], o1 = in.slot[k].off[i + 1];
-      c.d[k].p = in.slot[k].data + o0;
+      c.d[k].p = staged ? plan_smem + soff[k] + (uint32_t)(o0 - a0[k]) : in.slot[k].data + o0;
       c.d[k].n = (uint32_t)(o1 - o0);
       c.base[k] = (uint32_t)o0;
       aux_abs += (uint32_t)o0;
@@ -47,18 +89,29 @@ __global__ void __launch_bounds__(PLAN_THREADS) plan_kernel(PlanIn in, PlanOut o
   out.status[i] = G::run(c, s);
 }
 
+static const uint32_t PLAN_SMEM = 100 * 1024;  // two blocks per SM
+
 template <class G>
-static void launch(const PlanIn& in, const PlanOut& out, cudaStream_t st) {
+static void launch(const PlanIn& in, const PlanOut& out, uint64_t in_bytes, cudaStream_t st) {
   if (!in.n) return;
-  uint32_t blocks = (in.n + PLAN_THREADS - 1) / PLAN_THREADS;
-  plan_kernel<G><<<blocks, PLAN_THREADS, 0, st>>>(in, out);
+  static bool configured = false;  // per instantiation; set once per process and device set
+  if (!configured) {
+    cudaFuncSetAttribute(plan_kernel<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PLAN_SMEM);
+    configured = true;
+  }
+  // as many tuples per block as fit the staging area on average, 32..128
+  const uint64_t avg = in_bytes / in.n + 48;
+  uint32_t threads = 128;
+  while (threads > 32 && (uint64_t)threads * avg > PLAN_SMEM) threads >>= 1;
+  uint32_t blocks = (in.n + threads - 1) / threads;
+  plan_kernel<G><<<blocks, threads, PLAN_SMEM, st>>>(in, out, PLAN_SMEM);
 }
 
-void launch_plan(int gen, const PlanIn& in, const PlanOut& out, cudaStream_t st) {
+void launch_plan(int gen, const PlanIn& in, const PlanOut& out, uint64_t in_bytes, cudaStream_t st) {
   switch (gen) {
-    case GEN_ID_NBC: launch<GenNbc>(in, out, st); break;
-    case GEN_ID_ODH: launch<GenOdh>(in, out, st); break;
-    case GEN_ID_COPY: launch<GenCopyFields>(in, out, st); break;
+    case GEN_ID_NBC: launch<GenNbc>(in, out, in_bytes, st); break;
+    case GEN_ID_ODH: launch<GenOdh>(in, out, in_bytes, st); break;
+    case GEN_ID_COPY: launch<GenCopyFields>(in, out, in_bytes, st); break;
   }
 }
 
