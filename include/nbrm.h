@@ -75,8 +75,9 @@ typedef struct nbrm_out {
   const char* data;
   const uint64_t* off;    /* n + 1 entries */
   uint64_t n;             /* number of output objects */
-  const uint32_t* status; /* one per INPUT document */
+  const uint32_t* status; /* one per INPUT document (tuple) */
   uint64_t n_status;
+  const uint32_t* result; /* one per input tuple; meaning per entry point, 0 when unused */
 } nbrm_out;
 
 /* Accumulated device time per kernel class since nbrm_profile_enable(ctx, 1),
@@ -163,6 +164,42 @@ int nbrm_result_to_slot(nbrm_ctx* ctx, int slot);
 int nbrm_nbc_reconcile(nbrm_ctx* ctx, const nbrm_docs* notebooks, const nbrm_docs* found,
                        uint32_t flags, nbrm_out* out);
 int nbrm_nbc_reconcile_resident(nbrm_ctx* ctx, uint32_t flags);
+
+/* ---- Notebook status mirroring --------------------------------------------
+ * Replaces createNotebookStatus and PodCondToNotebookCond (notebook-controller/
+ * controllers/notebook_controller.go:290-349, :351-390).  Slot 0: Notebooks,
+ * slot 1: their StatefulSets, slot 2: their Pods "<name>-0"; an empty document
+ * = not found.  Output: one NotebookStatus object per Notebook (what the
+ * reference assigns to nb.Status before Status().Update, :286-287).
+ * now_unix stands for metav1.Now() (:377,:386), in Unix seconds. */
+int nbrm_notebook_status(nbrm_ctx* ctx, const nbrm_docs* notebooks, const nbrm_docs* statefulsets,
+                         const nbrm_docs* pods, uint64_t now_unix, nbrm_out* out);
+int nbrm_notebook_status_resident(nbrm_ctx* ctx, uint64_t now_unix);
+
+/* ---- idle culling ---------------------------------------------------------
+ * Replaces the pure part of CullingReconciler.Reconcile (notebook-controller/
+ * controllers/culling_controller.go:85-169) and its helpers
+ * cullingCheckPeriodHasPassed :173, notebookIsIdle :186, allKernelsAreIdle :281,
+ * getNotebookRecentTime :295, compareAnnotationTimeToResource :337,
+ * updateTimestampFrom{Kernels,Terminals}Activity :357,:390,
+ * updateLastCullingCheckTimestampAnnotation :416, annotationsExist :426,
+ * initializeAnnotations :435, removeAnnotations :444, setStopAnnotation :461,
+ * StopAnnotationIsSet :480.  The HTTP GETs to the notebook server stay with
+ * the caller: slot 1 / slot 2 hold the bodies of /api/kernels and
+ * /api/terminals per Notebook (empty document = the GET failed), pod_exists one
+ * byte per Notebook (NULL = every Pod exists).  cull_idle_minutes and
+ * check_period_minutes are CULL_IDLE_TIME and IDLENESS_CHECK_PERIOD (:511-544).
+ * Output: the Notebook to Update, length 0 when the pass changes nothing;
+ * result[i] = outcome | updates << 8 with outcome 1 culling annotations
+ * removed because the Notebook is stopped, 2 removed because the Pod is gone,
+ * 3 check period not over (requeue), 4 checked and still active, 5 culled
+ * (stop annotation set); updates = number of r.Update calls the reference
+ * makes on that path. */
+int nbrm_culling_pass(nbrm_ctx* ctx, const nbrm_docs* notebooks, const nbrm_docs* kernels,
+                      const nbrm_docs* terminals, const uint8_t* pod_exists, uint64_t now_unix,
+                      int32_t cull_idle_minutes, int32_t check_period_minutes, nbrm_out* out);
+int nbrm_culling_pass_resident(nbrm_ctx* ctx, uint64_t now_unix, int32_t cull_idle_minutes,
+                               int32_t check_period_minutes);
 
 /* ---- ODH reconcile generators -------------------------------------------
  * Replaces, for a batch of Notebooks, the desired-object constructors that

@@ -30,7 +30,7 @@ class _Docs(C.Structure):
 
 class _Out(C.Structure):
     _fields_ = [("data", C.c_void_p), ("off", C.c_void_p), ("n", C.c_uint64),
-                ("status", C.c_void_p), ("n_status", C.c_uint64)]
+                ("status", C.c_void_p), ("n_status", C.c_uint64), ("result", C.c_void_p)]
 
 
 class Profile(C.Structure):
@@ -93,6 +93,12 @@ def load_library():
     lib.nbrm_nbc_reconcile.argtypes = [C.c_void_p, C.POINTER(_Docs), C.POINTER(_Docs), C.c_uint32,
                                        C.POINTER(_Out)]
     lib.nbrm_nbc_reconcile_resident.argtypes = [C.c_void_p, C.c_uint32]
+    lib.nbrm_notebook_status.argtypes = [C.c_void_p, C.POINTER(_Docs), C.POINTER(_Docs), C.POINTER(_Docs),
+                                         C.c_uint64, C.POINTER(_Out)]
+    lib.nbrm_notebook_status_resident.argtypes = [C.c_void_p, C.c_uint64]
+    lib.nbrm_culling_pass.argtypes = [C.c_void_p, C.POINTER(_Docs), C.POINTER(_Docs), C.POINTER(_Docs),
+                                      C.c_char_p, C.c_uint64, C.c_int32, C.c_int32, C.POINTER(_Out)]
+    lib.nbrm_culling_pass_resident.argtypes = [C.c_void_p, C.c_uint64, C.c_int32, C.c_int32]
     lib.nbrm_scan_lengths_noalloc.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p,
                                               C.c_char_p, C.c_size_t]
     _lib = lib
@@ -163,6 +169,9 @@ class Result:
         ns = int(out.n_status)
         st = np.frombuffer((C.c_uint32 * max(ns, 1)).from_address(out.status), dtype=np.uint32,
                            count=ns)
+        rs = np.frombuffer((C.c_uint32 * max(ns, 1)).from_address(out.result), dtype=np.uint32,
+                           count=ns) if out.result else np.zeros(ns, dtype=np.uint32)
+        self.result = rs.copy() if copy else rs
         self.off = off.copy() if copy else off
         self.data = data.copy() if copy else data
         self.status = st.copy() if copy else st
@@ -282,3 +291,15 @@ class Context:
 
     def nbc_reconcile_resident(self, flags=GEN_ALL | GEN_OWNER_REF):
         self._check(self.lib.nbrm_nbc_reconcile_resident(self.h, flags))
+
+    # --- status mirroring / culling
+    def notebook_status(self, notebooks, stss, pods, now, copy=True):
+        a, b, d, o = notebooks.c_struct(), stss.c_struct(), pods.c_struct(), _Out()
+        self._check(self.lib.nbrm_notebook_status(self.h, C.byref(a), C.byref(b), C.byref(d), now, C.byref(o)))
+        return Result(o, copy)
+
+    def culling_pass(self, notebooks, kernels, terminals, pod_exists, now, idle_min, period_min, copy=True):
+        a, b, d, o = notebooks.c_struct(), kernels.c_struct(), terminals.c_struct(), _Out()
+        self._check(self.lib.nbrm_culling_pass(self.h, C.byref(a), C.byref(b), C.byref(d), pod_exists, now,
+                                               idle_min, period_min, C.byref(o)))
+        return Result(o, copy)

@@ -85,9 +85,9 @@ struct nbrm_ctx {
   EnvLits env;
 
   Slot slot[3];
-  DevBuf segs, nseg, lens, status, aux, out_off, scan_tmp, out, extra;
+  DevBuf segs, nseg, lens, status, result, aux, out_off, scan_tmp, out, extra;
   uint64_t extra_bytes = 0;
-  PinBuf h_out, h_off, h_status, h_total;
+  PinBuf h_out, h_off, h_status, h_result, h_total;
 
   // last *_resident result
   uint32_t res_n_in = 0, res_n_out = 0;
@@ -239,9 +239,9 @@ void nbrm_ctx_destroy(nbrm_ctx* c) {
     s.off.release();
   }
   DevBuf* bufs[] = {&c->pool, &c->segs, &c->nseg, &c->lens, &c->status,
-                    &c->aux,  &c->out_off, &c->scan_tmp, &c->out, &c->extra};
+                    &c->aux,  &c->out_off, &c->scan_tmp, &c->out, &c->extra, &c->result};
   for (auto b : bufs) b->release();
-  PinBuf* pins[] = {&c->h_out, &c->h_off, &c->h_status, &c->h_total};
+  PinBuf* pins[] = {&c->h_out, &c->h_off, &c->h_status, &c->h_result, &c->h_total};
   for (auto b : pins) b->release();
   cudaEventDestroy(c->t0);
   cudaEventDestroy(c->t1);
@@ -336,7 +336,7 @@ namespace {
 // map[k] = the context slot that feeds generator input k, or -1 (all used slots
 // must hold the same number of documents; tuple i is document i of each).
 int run_generator(nbrm_ctx* c, int gen, const int (&map)[3], uint32_t flags, const void* extra,
-                  uint64_t now) {
+                  uint64_t now, uint32_t arg0 = 0, uint32_t arg1 = 0) {
   CK(cudaSetDevice(c->device));
   uint32_t nobj = 0, cap = 0;
   gen_shape(gen, &nobj, &cap);
@@ -363,11 +363,14 @@ int run_generator(nbrm_ctx* c, int gen, const int (&map)[3], uint32_t flags, con
   in.env = c->env;
   in.extra = extra;
   in.now = now;
+  in.arg0 = arg0;
+  in.arg1 = arg1;
   const uint32_t n_out = n * nobj;
   CK(c->segs.reserve((size_t)n_out * cap * sizeof(Seg) + 16));
   CK(c->nseg.reserve((size_t)n_out * 4 + 16));
   CK(c->lens.reserve((size_t)n_out * 4 + 16));
   CK(c->status.reserve((size_t)n * 4 + 16));
+  CK(c->result.reserve((size_t)n * 4 + 16));
   CK(c->aux.reserve(in_bytes + (uint64_t)n * AUX_PAD + 16));
   CK(c->out_off.reserve(((size_t)n_out + 1) * 8));
   CK(c->scan_tmp.reserve(scan_tmp_bytes(n_out)));
@@ -377,6 +380,7 @@ int run_generator(nbrm_ctx* c, int gen, const int (&map)[3], uint32_t flags, con
   po.nseg = c->nseg.as<uint32_t>();
   po.lens = c->lens.as<uint32_t>();
   po.status = c->status.as<uint32_t>();
+  po.result = c->result.as<uint32_t>();
   po.aux = c->aux.as<char>();
   po.cap = cap;
   {
@@ -430,19 +434,24 @@ int nbrm_download(nbrm_ctx* c, nbrm_out* out) {
   CK(c->h_out.reserve(c->res_bytes + 16));
   CK(c->h_off.reserve(((size_t)c->res_n_out + 1) * 8));
   CK(c->h_status.reserve((size_t)c->res_n_in * 4 + 16));
+  CK(c->h_result.reserve((size_t)c->res_n_in * 4 + 16));
   if (c->res_bytes)
     CK(cudaMemcpyAsync(c->h_out.p, c->out.p, c->res_bytes, cudaMemcpyDeviceToHost, c->stream));
   CK(cudaMemcpyAsync(c->h_off.p, c->out_off.p, ((size_t)c->res_n_out + 1) * 8,
                      cudaMemcpyDeviceToHost, c->stream));
-  if (c->res_n_in)
+  if (c->res_n_in) {
     CK(cudaMemcpyAsync(c->h_status.p, c->status.p, (size_t)c->res_n_in * 4, cudaMemcpyDeviceToHost,
                        c->stream));
+    CK(cudaMemcpyAsync(c->h_result.p, c->result.p, (size_t)c->res_n_in * 4, cudaMemcpyDeviceToHost,
+                       c->stream));
+  }
   CK(cudaStreamSynchronize(c->stream));
   out->data = reinterpret_cast<const char*>(c->h_out.p);
   out->off = reinterpret_cast<const uint64_t*>(c->h_off.p);
   out->n = c->res_n_out;
   out->status = reinterpret_cast<const uint32_t*>(c->h_status.p);
   out->n_status = c->res_n_in;
+  out->result = reinterpret_cast<const uint32_t*>(c->h_result.p);
   const uint32_t* st = out->status;
   for (uint32_t i = 0; i < c->res_n_in; ++i)
     if (st[i]) return 1;
@@ -529,6 +538,46 @@ int nbrm_nbc_reconcile(nbrm_ctx* c, const nbrm_docs* notebooks, const nbrm_docs*
   if (int r = nbrm_upload(c, 0, notebooks)) return r;
   if (int r = nbrm_upload(c, 1, found)) return r;
   if (int r = nbrm_nbc_reconcile_resident(c, flags)) return r;
+  return nbrm_download(c, out);
+}
+
+int nbrm_notebook_status_resident(nbrm_ctx* c, uint64_t now_unix) {
+  if (!c) return -2;
+  return run_generator(c, GEN_ID_STATUS, {0, 1, 2}, 0, nullptr, now_unix);
+}
+
+int nbrm_notebook_status(nbrm_ctx* c, const nbrm_docs* notebooks, const nbrm_docs* statefulsets,
+                         const nbrm_docs* pods, uint64_t now_unix, nbrm_out* out) {
+  if (!c || !out) return -2;
+  if (int r = nbrm_upload(c, 0, notebooks)) return r;
+  if (int r = nbrm_upload(c, 1, statefulsets)) return r;
+  if (int r = nbrm_upload(c, 2, pods)) return r;
+  if (int r = nbrm_notebook_status_resident(c, now_unix)) return r;
+  return nbrm_download(c, out);
+}
+
+int nbrm_culling_pass_resident(nbrm_ctx* c, uint64_t now_unix, int32_t cull_idle_minutes,
+                               int32_t check_period_minutes) {
+  if (!c) return -2;
+  const void* pod_exists = nullptr;
+  if (c->extra_bytes) {
+    if (c->extra_bytes != (uint64_t)c->slot[0].n)
+      return fail_msg(c, "nbrm_culling_pass: pod_exists must hold one byte per Notebook");
+    pod_exists = c->extra.p;
+  }
+  return run_generator(c, GEN_ID_CULL, {0, 1, 2}, 0, pod_exists, now_unix, (uint32_t)cull_idle_minutes,
+                       (uint32_t)check_period_minutes);
+}
+
+int nbrm_culling_pass(nbrm_ctx* c, const nbrm_docs* notebooks, const nbrm_docs* kernels,
+                      const nbrm_docs* terminals, const uint8_t* pod_exists, uint64_t now_unix,
+                      int32_t cull_idle_minutes, int32_t check_period_minutes, nbrm_out* out) {
+  if (!c || !out) return -2;
+  if (int r = nbrm_upload(c, 0, notebooks)) return r;
+  if (int r = nbrm_upload(c, 1, kernels)) return r;
+  if (int r = nbrm_upload(c, 2, terminals)) return r;
+  if (int r = nbrm_upload_bytes(c, pod_exists, pod_exists ? notebooks->n : 0)) return r;
+  if (int r = nbrm_culling_pass_resident(c, now_unix, cull_idle_minutes, check_period_minutes)) return r;
   return nbrm_download(c, out);
 }
 

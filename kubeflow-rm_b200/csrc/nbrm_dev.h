@@ -30,6 +30,7 @@ struct PlanIn {
   EnvLits env;
   const void* extra;  // generator-specific side input (device pointer) or null
   uint64_t now;       // caller's clock, Unix seconds
+  uint32_t arg0, arg1;
 };
 
 // Where a plan kernel writes.
@@ -38,6 +39,7 @@ struct PlanOut {
   uint32_t* nseg;     // n * NOBJ
   uint32_t* lens;     // n * NOBJ
   uint32_t* status;   // one per input tuple
+  uint32_t* result;   // one per input tuple, generator-specific
   char* aux;          // aux arena
   uint32_t cap;
 };
@@ -51,7 +53,7 @@ void launch_emit(const Seg* segs, const uint32_t* nseg, const uint32_t* lens, co
                  int sm_count, cudaStream_t st);
 
 // nbrm_plan_kernels.cu
-enum GenId { GEN_ID_NBC = 0, GEN_ID_ODH = 1, GEN_ID_COPY = 2 };
+enum GenId { GEN_ID_NBC = 0, GEN_ID_ODH = 1, GEN_ID_COPY = 2, GEN_ID_STATUS = 3, GEN_ID_CULL = 4 };
 void launch_plan(int gen, const PlanIn& in, const PlanOut& out, uint64_t in_bytes, cudaStream_t st);
 void gen_shape(int gen, uint32_t* nobj, uint32_t* cap);
 

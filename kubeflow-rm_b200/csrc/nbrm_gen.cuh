@@ -33,6 +33,8 @@ struct DocCtx {
   uint32_t index;       // document index within the batch
   const void* extra;    // generator-specific side input (device pointer), may be null
   uint64_t now;         // caller-supplied clock, Unix seconds (generators that stamp times)
+  uint32_t arg0, arg1;  // generator-specific integers (e.g. culling periods)
+  uint32_t result;      // generator-specific per-tuple result word (0 when unused)
 };
 
 // Plans n_obj objects with plan_k(P, k).  One failing object voids the whole

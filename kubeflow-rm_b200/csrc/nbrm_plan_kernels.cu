@@ -3,6 +3,8 @@
 #include "nbrm_nbc.cuh"
 #include "nbrm_odh.cuh"
 #include "nbrm_cmp.cuh"
+#include "nbrm_status.cuh"
+#include "nbrm_cull.cuh"
 
 namespace nbrm {
 
@@ -81,12 +83,16 @@ __global__ void plan_kernel(PlanIn in, PlanOut out, uint32_t smem_cap) {
   c.index = i;
   c.extra = in.extra;
   c.now = in.now;
+  c.arg0 = in.arg0;
+  c.arg1 = in.arg1;
+  c.result = 0;
   ObjSink s;
   s.segs = out.segs + (size_t)i * G::NOBJ * out.cap;
   s.nseg = out.nseg + (size_t)i * G::NOBJ;
   s.lens = out.lens + (size_t)i * G::NOBJ;
   s.cap = out.cap;
   out.status[i] = G::run(c, s);
+  out.result[i] = c.result;
 }
 
 static const uint32_t PLAN_SMEM = 100 * 1024;  // two blocks per SM
@@ -112,6 +118,8 @@ void launch_plan(int gen, const PlanIn& in, const PlanOut& out, uint64_t in_byte
     case GEN_ID_NBC: launch<GenNbc>(in, out, in_bytes, st); break;
     case GEN_ID_ODH: launch<GenOdh>(in, out, in_bytes, st); break;
     case GEN_ID_COPY: launch<GenCopyFields>(in, out, in_bytes, st); break;
+    case GEN_ID_STATUS: launch<GenStatus>(in, out, in_bytes, st); break;
+    case GEN_ID_CULL: launch<GenCull>(in, out, in_bytes, st); break;
   }
 }
 
@@ -120,6 +128,8 @@ void gen_shape(int gen, uint32_t* nobj, uint32_t* cap) {
     case GEN_ID_NBC: *nobj = GenNbc::NOBJ; *cap = GenNbc::CAP; break;
     case GEN_ID_ODH: *nobj = GenOdh::NOBJ; *cap = GenOdh::CAP; break;
     case GEN_ID_COPY: *nobj = GenCopyFields::NOBJ; *cap = GenCopyFields::CAP; break;
+    case GEN_ID_STATUS: *nobj = GenStatus::NOBJ; *cap = GenStatus::CAP; break;
+    case GEN_ID_CULL: *nobj = GenCull::NOBJ; *cap = GenCull::CAP; break;
     default: *nobj = 0; *cap = 0;
   }
 }

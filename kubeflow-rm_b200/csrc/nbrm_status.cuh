@@ -1,0 +1,146 @@
+// nbrm_status.cuh — Notebook status mirroring.
+//
+// Reference: createNotebookStatus, components/notebook-controller/controllers/
+// notebook_controller.go:290-349, and PodCondToNotebookCond :351-390; golden
+// cases notebook_controller_test.go:103-275.
+// Input slot 0: Notebook, slot 1: its StatefulSet, slot 2: its Pod "<name>-0"
+// (empty documents = not found).  Output: the NotebookStatus object.
+#pragma once
+#include "nbrm_cmp.cuh"
+#include "nbrm_time.cuh"
+
+namespace nbrm {
+
+// reflect.DeepEqual(pod.Status, corev1.PodStatus{}) (:304): every member is a
+// zero scalar; any slice or struct value, even an empty one, makes it non-zero.
+NB_HD bool pod_status_is_zero(const Doc& d, Span st) {
+  if (!is_object(d, st)) return true;
+  ObjIter it(d, st);
+  Member m;
+  while (it.next(d, m)) {
+    const Span v = m.val;
+    if (is_null(d, v)) continue;
+    const char c = d.at(v.off);
+    if (c == '"') {
+      if (v.len > 2) return false;
+    } else if (c == '{' || c == '[') {
+      return false;
+    } else if (!(v.len == 1 && c == '0') && !(v.len == 5 && c == 'f')) {
+      return false;
+    }
+  }
+  return true;
+}
+
+// corev1.ContainerState with all three pointers nil.
+NB_HD bool container_state_is_zero(const Doc& d, Span st) {
+  if (!is_object(d, st)) return true;
+  return is_nil(d, FIND(d, st, "waiting")) && is_nil(d, FIND(d, st, "running")) &&
+         is_nil(d, FIND(d, st, "terminated"));
+}
+
+NB_HD bool nonempty_string(const Doc& d, Span v) { return is_string(d, v) && v.len > 2; }
+
+NB_HD void plan_status(Planner& P, DocCtx& c) {
+  const Doc& nb = c.d[0];
+  const Doc& sts = c.d[1];
+  const Doc& pod = c.d[2];
+  LIT(P, STATUS_HEAD);  // {"conditions":[
+  const Span pst = pod.n ? FIND(pod, root(pod), "status") : mk(0, 0);
+  const bool have_pod = !pod_status_is_zero(pod, pst);
+  Span state = mk(0, 0);
+  bool state_set = false;
+  if (have_pod) {
+    // "now" as metav1.Now() would stamp it (:377,:386), once per Notebook
+    uint32_t now_off = 0, now_len = 0;
+    Sep cs;
+    ArrIter it(pod, FIND(pod, pst, "conditions"));
+    Span e;
+    while (it.next(pod, e)) {  // :341-346
+      Span ty = mk(0, 0), stv = mk(0, 0), lp = mk(0, 0), lt = mk(0, 0), rs = mk(0, 0), ms = mk(0, 0);
+      ObjIter ci(pod, e);
+      Member m;
+      while (ci.next(pod, m)) {
+        if (KEY_IS(pod, m, "type")) ty = m.val;
+        else if (KEY_IS(pod, m, "status")) stv = m.val;
+        else if (KEY_IS(pod, m, "lastProbeTime")) lp = m.val;
+        else if (KEY_IS(pod, m, "lastTransitionTime")) lt = m.val;
+        else if (KEY_IS(pod, m, "reason")) rs = m.val;
+        else if (KEY_IS(pod, m, "message")) ms = m.val;
+      }
+      if ((!nonempty_string(pod, lp) || !nonempty_string(pod, lt)) && !now_len) {
+        if (c.aux.used + 32 <= c.aux.cap) {
+          char* o = c.aux.p + c.aux.used;
+          o[0] = '"';
+          now_len = format_rfc3339((long long)c.now, 0, o + 1) + 2;
+          o[now_len - 1] = '"';
+          now_off = c.aux.abs + c.aux.used;
+          c.aux.used += now_len;
+        } else {
+          P.err = E_LIMIT;
+          return;
+        }
+      }
+      cs.next(P);
+      LIT(P, COND_TYPE);  // {"type":
+      if (nonempty_string(pod, ty)) P.in(ty, 2); else LIT(P, EMPTY_STR);
+      LIT(P, COND_STATUS);
+      if (nonempty_string(pod, stv)) P.in(stv, 2); else LIT(P, EMPTY_STR);
+      LIT(P, COND_PROBE);
+      if (nonempty_string(pod, lp)) P.in(lp, 2); else P.aux(now_off, now_len);
+      LIT(P, COND_TRANSITION);
+      if (nonempty_string(pod, lt)) P.in(lt, 2); else P.aux(now_off, now_len);
+      if (nonempty_string(pod, rs)) {
+        LIT(P, COND_REASON);
+        P.in(rs, 2);
+      }
+      if (nonempty_string(pod, ms)) {
+        LIT(P, COND_MESSAGE);
+        P.in(ms, 2);
+      }
+      LIT(P, RBRACE);
+    }
+    // :314-330 the state of the container named like the Notebook
+    const Span nbname = FIND(nb, FIND(nb, root(nb), "metadata"), "name");
+    const Span cur = FIND(nb, FIND(nb, root(nb), "status"), "containerState");
+    const bool cur_zero = container_state_is_zero(nb, cur);
+    ArrIter si(pod, FIND(pod, pst, "containerStatuses"));
+    while (si.next(pod, e)) {
+      const Span nm = FIND(pod, e, "name");
+      const bool same = is_string(nb, nbname) ? (is_string(pod, nm) && str_equal(pod, nm, nb, nbname))
+                                              : (!is_string(pod, nm) || nm.len == 2);
+      if (!same) continue;
+      const Span st = FIND(pod, e, "state");
+      if (container_state_is_zero(pod, st) && cur_zero) continue;  // Go == on three nil pointers (:319)
+      state = st;
+      state_set = true;
+      break;
+    }
+  }
+  LIT(P, STATUS_READY);  // ],"readyReplicas":
+  const Span rr = sts.n ? FIND(sts, FIND(sts, root(sts), "status"), "readyReplicas") : mk(0, 0);
+  if (rr.ok() && !is_null(sts, rr)) P.in(rr, 1); else LIT(P, ZERO);
+  LIT(P, STATUS_STATE);  // ,"containerState":
+  if (state_set && is_object(pod, state)) P.in(state, 2);
+  else {
+    LIT(P, LBRACE);
+    LIT(P, RBRACE);
+  }
+  LIT(P, RBRACE);
+}
+
+struct GenStatus {
+  static const uint32_t NOBJ = 1;
+  static const uint32_t CAP = 160;
+  struct K {
+    DocCtx& c;
+    NB_HD void operator()(Planner& P, uint32_t) { plan_status(P, c); }
+  };
+  NB_HD static uint32_t run(DocCtx& c, ObjSink s) {
+    K k{c};
+    uint32_t st = is_object(c.d[0], root(c.d[0])) ? E_OK : E_PARSE;
+    return plan_objects(c, s, NOBJ, st, k);
+  }
+};
+
+}  // namespace nbrm

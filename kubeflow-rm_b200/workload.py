@@ -257,3 +257,127 @@ def found_variant(rng, desired):
             return x
         f = shuffle(f)
     return f
+
+
+def _stamp(t):
+    import datetime
+    return datetime.datetime.fromtimestamp(t, datetime.timezone.utc).strftime("%Y-%m-%dT%H:%M:%SZ")
+
+
+def pod_variant(rng, nb, now=1793966400):
+    """A Pod "<name>-0" for the status-mirroring tests, or None (NotFound).
+    Shapes after notebook-controller/controllers/notebook_controller_test.go:103-275."""
+    r = rng.random()
+    if r < 0.12:
+        return None
+    name = (nb.get("metadata") or {}).get("name", "")
+    pod = {"apiVersion": "v1", "kind": "Pod",
+           "metadata": {"name": name + "-0", "namespace": (nb.get("metadata") or {}).get("namespace", "")}}
+    if r < 0.2:
+        return pod                                    # no status at all
+    if r < 0.26:
+        pod["status"] = {}
+        return pod
+    if r < 0.3:
+        pod["status"] = {"phase": "", "hostIP": ""}   # all-zero scalars: still the zero PodStatus
+        return pod
+    st = {"phase": rng.choice(["Pending", "Running"])}
+    if rng.random() < 0.85:
+        conds = []
+        for ty in rng.sample(["Initialized", "Ready", "ContainersReady", "PodScheduled"], rng.randint(0, 4)):
+            c = {"type": ty, "status": rng.choice(["True", "False", "false"])}
+            if rng.random() < 0.7:
+                c["lastProbeTime"] = rng.choice([None, _stamp(now - rng.randrange(5000))])
+            if rng.random() < 0.8:
+                c["lastTransitionTime"] = _stamp(now - rng.randrange(5000))
+            if rng.random() < 0.4:
+                c["reason"] = rng.choice(["Unschedulable", "ContainersNotReady", ""])
+            if rng.random() < 0.4:
+                c["message"] = rng.choice(["0/1 nodes are available: 1 Insufficient cpu.",
+                                           "containers with unready status: [\"nb\"]", ""])
+            conds.append(c)
+        st["conditions"] = conds
+    if rng.random() < 0.85:
+        css = []
+        for cname in rng.sample([name, "oauth-proxy", "istio-proxy"], rng.randint(1, 3)):
+            state = rng.choice([{"running": {"startedAt": _stamp(now - 100)}},
+                                {"waiting": {"reason": "PodInitializing"}},
+                                {"terminated": {"exitCode": 1, "reason": "Error"}},
+                                {"running": {"startedAt": None}}, {}, None])
+            cs = {"name": cname, "ready": rng.random() < 0.5, "restartCount": rng.randrange(3),
+                  "image": "img", "imageID": ""}
+            if state is not None or rng.random() < 0.5:
+                cs["state"] = state
+            css.append(cs)
+        st["containerStatuses"] = css
+    pod["status"] = st
+    return pod
+
+
+def sts_variant(rng, nb):
+    if rng.random() < 0.15:
+        return None
+    s = {"apiVersion": "apps/v1", "kind": "StatefulSet", "metadata": dict(nb.get("metadata") or {})}
+    r = rng.random()
+    if r < 0.6:
+        s["status"] = {"replicas": 1, "readyReplicas": rng.randint(0, 1)}
+    elif r < 0.8:
+        s["status"] = {"replicas": 1}
+    return s
+
+
+def status_notebook(rng, nb):
+    """The Notebook as stored, sometimes with a previous status."""
+    import copy
+    nb = copy.deepcopy(nb)
+    r = rng.random()
+    if r < 0.3:
+        nb["status"] = {"conditions": [], "readyReplicas": 0, "containerState": {}}
+    elif r < 0.5:
+        nb["status"] = {"conditions": [], "readyReplicas": 1,
+                        "containerState": {"running": {"startedAt": "2026-11-06T00:00:00Z"}}}
+    return nb
+
+
+def culling_case(rng, i, now):
+    """(notebook, pod_exists, kernels, terminals) for one culling pass; kernels /
+    terminals are the decoded /api/kernels, /api/terminals bodies or None when
+    the GET failed (culling_controller.go:209-279)."""
+    nb = notebook_loadtest(i)
+    a = {}
+    r = rng.random()
+    if r < 0.15:
+        a["kubeflow-resource-stopped"] = rng.choice([_stamp(now - 50), "odh-notebook-controller-lock"])
+    if rng.random() < 0.75:
+        a["notebooks.kubeflow.org/last-activity"] = rng.choice([
+            _stamp(now - rng.randrange(0, 4000)), _stamp(now - rng.randrange(0, 4000)),
+            "2021-08-30T15:37:36.990063Z", "1900-08-30T15:37:36.990063Z", "should-fail",
+            "2026-11-06T11:00:00+02:00", ""])
+    if rng.random() < 0.75:
+        a["notebooks.kubeflow.org/last_activity_check_timestamp"] = rng.choice([
+            _stamp(now - rng.randrange(0, 200)), _stamp(now - 60), _stamp(now - 61), "garbage",
+            _stamp(now + 30)])
+    if rng.random() < 0.5:
+        a["other"] = "kept"
+    r = rng.random()
+    if r < 0.8:
+        nb["metadata"]["annotations"] = a
+    elif r < 0.9 and not a:
+        nb["metadata"]["annotations"] = None
+
+    def acts(n, with_state):
+        out = []
+        for _ in range(n):
+            e = {"id": "k%d" % rng.randrange(1000), "name": "python3",
+                 "last_activity": rng.choice([_stamp(now - rng.randrange(0, 5000)),
+                                              "2026-11-06T11:59:00.123456Z",
+                                              "2026-11-06T13:30:00+02:00", "bad-time"] if rng.random() < 0.15
+                                             else [_stamp(now - rng.randrange(0, 5000))])}
+            if with_state:
+                e["execution_state"] = "idle" if rng.random() < 0.8 else rng.choice(["busy", "starting"])
+                e["connections"] = rng.randrange(3)
+            out.append(e)
+        return out
+    kernels = None if rng.random() < 0.15 else acts(rng.randint(0, 3), True)
+    terminals = None if rng.random() < 0.3 else acts(rng.randint(0, 2), False)
+    return nb, rng.random() > 0.1, kernels, terminals

@@ -13,6 +13,8 @@
 #include "../../kubeflow-rm_b200/csrc/nbrm_nbc.cuh"
 #include "../../kubeflow-rm_b200/csrc/nbrm_odh.cuh"
 #include "../../kubeflow-rm_b200/csrc/nbrm_cmp.cuh"
+#include "../../kubeflow-rm_b200/csrc/nbrm_status.cuh"
+#include "../../kubeflow-rm_b200/csrc/nbrm_cull.cuh"
 #include "../../kubeflow-rm_b200/csrc/nbrm_pool.h"
 
 using namespace nbrm;
@@ -24,12 +26,13 @@ struct Out {
   std::string data;
   std::vector<uint64_t> off;
   std::vector<uint32_t> status;
+  std::vector<uint32_t> result;
 };
 Out g_out;
 
 template <class G>
 int run_host(const char* const data[3], const uint64_t* const off[3], uint64_t n, const nbrm_env* env,
-             uint32_t flags, const void* extra, uint64_t now) {
+             uint32_t flags, const void* extra, uint64_t now, uint32_t arg0, uint32_t arg1) {
   std::string pool;
   EnvLits L;
   build_pool_host(env, pool, L);
@@ -40,6 +43,7 @@ int run_host(const char* const data[3], const uint64_t* const off[3], uint64_t n
   g_out.data.clear();
   g_out.off.assign(1, 0);
   g_out.status.assign(n, 0);
+  g_out.result.assign(n, 0);
   const uint32_t cap = G::CAP;
   std::vector<Seg> segs((size_t)G::NOBJ * cap);
   std::vector<uint32_t> nseg(G::NOBJ), lens(G::NOBJ);
@@ -69,6 +73,9 @@ int run_host(const char* const data[3], const uint64_t* const off[3], uint64_t n
     c.index = (uint32_t)i;
     c.extra = extra;
     c.now = now;
+    c.arg0 = arg0;
+    c.arg1 = arg1;
+    c.result = 0;
     ObjSink s;
     s.segs = segs.data();
     s.nseg = nseg.data();
@@ -76,6 +83,7 @@ int run_host(const char* const data[3], const uint64_t* const off[3], uint64_t n
     s.cap = cap;
     uint32_t st = G::run(c, s);
     g_out.status[i] = st;
+    g_out.result[i] = c.result;
     for (uint32_t k = 0; k < G::NOBJ; ++k) {
       size_t before = g_out.data.size();
       for (uint32_t j = 0; j < nseg[k]; ++j) {
@@ -92,22 +100,26 @@ int run_host(const char* const data[3], const uint64_t* const off[3], uint64_t n
 
 extern "C" {
 
-// gen: 0 notebook-controller (3 objects), 1 ODH reconcile (7 objects)
+// gen: 0 notebook-controller (3 objects), 1 ODH reconcile (7), 2 Copy*Fields (1), 3 status (1), 4 culling (1)
 int hostplan_run(int gen, const char* d0, const uint64_t* o0, const char* d1, const uint64_t* o1,
                  const char* d2, const uint64_t* o2, uint64_t n, const nbrm_env* env, uint32_t flags,
-                 const void* extra, uint64_t now, uint32_t* nobj, const char** out_data,
-                 const uint64_t** out_off, const uint32_t** out_status) {
+                 const void* extra, uint64_t now, uint32_t arg0, uint32_t arg1, uint32_t* nobj,
+                 const char** out_data, const uint64_t** out_off, const uint32_t** out_status,
+                 const uint32_t** out_result) {
   const char* data[3] = {d0, d1, d2};
   const uint64_t* off[3] = {o0, o1, o2};
   int rc = -9;
   switch (gen) {
-    case 0: rc = run_host<GenNbc>(data, off, n, env, flags, extra, now); *nobj = GenNbc::NOBJ; break;
-    case 1: rc = run_host<GenOdh>(data, off, n, env, flags, extra, now); *nobj = GenOdh::NOBJ; break;
-    case 2: rc = run_host<GenCopyFields>(data, off, n, env, flags, extra, now); *nobj = GenCopyFields::NOBJ; break;
+    case 0: rc = run_host<GenNbc>(data, off, n, env, flags, extra, now, arg0, arg1); *nobj = GenNbc::NOBJ; break;
+    case 1: rc = run_host<GenOdh>(data, off, n, env, flags, extra, now, arg0, arg1); *nobj = GenOdh::NOBJ; break;
+    case 2: rc = run_host<GenCopyFields>(data, off, n, env, flags, extra, now, arg0, arg1); *nobj = GenCopyFields::NOBJ; break;
+    case 3: rc = run_host<GenStatus>(data, off, n, env, flags, extra, now, arg0, arg1); *nobj = GenStatus::NOBJ; break;
+    case 4: rc = run_host<GenCull>(data, off, n, env, flags, extra, now, arg0, arg1); *nobj = GenCull::NOBJ; break;
   }
   *out_data = g_out.data.data();
   *out_off = g_out.off.data();
   *out_status = g_out.status.data();
+  *out_result = g_out.result.data();
   return rc;
 }
 }

@@ -4,7 +4,7 @@ import ctypes as C
 
 import numpy as np
 
-GEN_NBC, GEN_ODH, GEN_COPY = 0, 1, 2
+GEN_NBC, GEN_ODH, GEN_COPY, GEN_STATUS, GEN_CULL = 0, 1, 2, 3, 4
 
 
 def _pack(docs_list):
@@ -20,7 +20,7 @@ class HostPlan:
         self.lib = C.CDLL(path)
         self.lib.hostplan_run.restype = C.c_int
 
-    def run(self, gen, slots, env=None, flags=0, extra=None, now=0):
+    def run(self, gen, slots, env=None, flags=0, extra=None, now=0, arg0=0, arg1=0, want_result=False):
         """slots: up to three lists of byte strings (None = slot unused)."""
         import __graft_entry__ as graft
         capi = __import__(graft.PKG_NAME + ".capi", fromlist=["x"])
@@ -40,18 +40,24 @@ class HostPlan:
             e = capi._Env()
             for k, v in env.items():
                 setattr(e, capi.ENV_FIELDS[k], None if v is None else v.encode())
-        pd, po, ps, nobj = C.c_void_p(), C.c_void_p(), C.c_void_p(), C.c_uint32()
+        pd, po, ps, pr, nobj = C.c_void_p(), C.c_void_p(), C.c_void_p(), C.c_void_p(), C.c_uint32()
         rc = self.lib.hostplan_run(C.c_int(gen), *args, C.c_uint64(n),
                                    C.byref(e) if e is not None else None, C.c_uint32(flags),
                                    C.c_char_p(extra) if extra is not None else None, C.c_uint64(now),
-                                   C.byref(nobj), C.byref(pd), C.byref(po), C.byref(ps))
+                                   C.c_uint32(arg0), C.c_uint32(arg1),
+                                   C.byref(nobj), C.byref(pd), C.byref(po), C.byref(ps), C.byref(pr))
         assert rc == 0, rc
         m = n * nobj.value
         o = np.frombuffer((C.c_uint64 * (m + 1)).from_address(po.value), dtype=np.uint64).copy()
         buf = C.string_at(pd.value, int(o[m])) if int(o[m]) else b""
         st = np.frombuffer((C.c_uint32 * max(n, 1)).from_address(ps.value), dtype=np.uint32,
                            count=n).copy()
-        return [buf[int(o[i]):int(o[i + 1])] for i in range(m)], st
+        outs = [buf[int(o[i]):int(o[i + 1])] for i in range(m)]
+        if want_result:
+            res = np.frombuffer((C.c_uint32 * max(n, 1)).from_address(pr.value), dtype=np.uint32,
+                                count=n).copy()
+            return outs, st, res
+        return outs, st
 
     def nbc_generate(self, docs_list, env=None, flags=7):
         if not docs_list:
@@ -68,3 +74,10 @@ class HostPlan:
         if not desired_list:
             return [], np.zeros(0, dtype=np.uint32)
         return self.run(GEN_COPY, [desired_list, found_list])
+
+    def status(self, notebooks, stss, pods, now=0):
+        return self.run(GEN_STATUS, [notebooks, stss, pods], now=now)
+
+    def cull(self, notebooks, kernels, terminals, pod_exists, now, idle_min, period_min):
+        return self.run(GEN_CULL, [notebooks, kernels, terminals], extra=bytes(pod_exists), now=now,
+                        arg0=idle_min, arg1=period_min, want_result=True)

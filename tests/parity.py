@@ -2,7 +2,7 @@
 planners) against the oracle, object by object, on canonical JSON."""
 import json
 
-from oracle import gojson, nbc, odh
+from oracle import culling, gojson, nbc, odh
 
 
 def check_nbc_generate(nbs, outs, status, env, flags, owner_api="kubeflow.org/v1beta1"):
@@ -90,3 +90,36 @@ def check_copy_fields(desired, found, outs, status):
         else:
             n_update += 1
     return n_create, n_update, n_none
+
+
+def check_status(nbs, stss, pods, outs, status, now_str):
+    n = 0
+    for i, (nb, sts, pod) in enumerate(zip(nbs, stss, pods)):
+        assert status[i] == 0, (i, status[i])
+        exp = nbc.create_notebook_status(nb, sts or {}, pod or {}, now_str)
+        got = json.loads(outs[i])
+        assert gojson.canon(got) == gojson.canon(exp), \
+            "case %d\n got %s\n exp %s" % (i, gojson.canon(got), gojson.canon(exp))
+        n += 1
+    return n
+
+
+def check_cull(cases, outs, status, result, now, idle_min, period_min):
+    """cases: (notebook, pod_exists, kernels, terminals) tuples."""
+    import collections
+    seen = collections.Counter()
+    cfg = {"CULL_IDLE_TIME": idle_min, "IDLENESS_CHECK_PERIOD": period_min}
+    for i, (nb, pod_exists, kernels, terminals) in enumerate(cases):
+        exp = json.loads(json.dumps(nb))
+        outcome, updates, _ = culling.culling_step(exp, pod_exists, kernels, terminals,
+                                                   now * 10**9, cfg)
+        assert status[i] == 0, (i, status[i])
+        assert int(result[i]) == outcome | (updates << 8), (i, int(result[i]), outcome, updates)
+        if updates == 0:
+            assert outs[i] == b"", i
+        else:
+            got = json.loads(outs[i])
+            assert gojson.canon(got) == gojson.canon(exp), \
+                "case %d outcome %d\n got %s\n exp %s" % (i, outcome, gojson.canon(got), gojson.canon(exp))
+        seen[outcome] += 1
+    return seen
