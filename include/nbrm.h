@@ -228,6 +228,28 @@ int nbrm_odh_generate(nbrm_ctx* ctx, const nbrm_docs* notebooks, const uint8_t* 
                       uint32_t flags, nbrm_out* out);
 int nbrm_odh_generate_resident(nbrm_ctx* ctx, uint32_t flags);
 
+/* ---- ODH Notebook mutating webhook -------------------------------------------
+ * Replaces the object transformation of NotebookWebhook.Handle
+ * (odh-notebook-controller/controllers/notebook_webhook.go:234-302):
+ * InjectReconciliationLock :63-72 (CREATE only), InjectCertConfig :421-535 (with
+ * NBRM_MUT_CA_BUNDLE: the caller found the ConfigMaps CheckAndMountCACertBundle
+ * :373-419 reads), InjectOAuthProxy :76-231 when the inject-oauth annotation
+ * parses true, admission.Denied (status NBRM_E_DENIED) when service mesh is on
+ * too (:272-275), and for UPDATE (old_notebooks != NULL)
+ * maybeRestartRunningNotebook :314-370 with the update-pending annotation
+ * :288-293.  The OAuth proxy image is nbrm_env.oauth_proxy_image.
+ * SetContainerImageFromRegistry (:541-640) needs a live ImageStream list and
+ * stays with the caller.  Output: the mutated Notebook per request (the caller
+ * diffs it against the request object as admission.PatchResponseFromRaw does).
+ * result[i] = 1 when the webhook's own pod-template changes were held back
+ * (UpdatesPending).  The update-pending annotation then carries a fixed text:
+ * the reference's go-cmp diff string is not reproducible outside Go.
+ * Slots used: 1 (request objects), 2 (old objects), 0 (intermediate). */
+enum { NBRM_MUT_CREATE = 1, NBRM_MUT_CA_BUNDLE = 2 };
+int nbrm_odh_mutate(nbrm_ctx* ctx, const nbrm_docs* notebooks, const nbrm_docs* old_notebooks,
+                    uint32_t flags, nbrm_out* out);
+int nbrm_odh_mutate_resident(nbrm_ctx* ctx, uint32_t flags, int is_update);
+
 /* ---- offsets without allocation -----------------------------------------
  * No counterpart in the reference: this entry point exists for embedders, not
  * to replace a reference function.

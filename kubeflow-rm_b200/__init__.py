@@ -8,5 +8,5 @@ CPU fallback: importing works anywhere, but every call needs the built library
 and a CUDA device.
 """
 from .capi import (Context, Docs, Result, NbrmError, lib_path, load_library,  # noqa: F401
-                   GEN_STS, GEN_SVC, GEN_VS, GEN_OWNER_REF, GEN_OWNER_V1, GEN_ALL, ODH_RBAC,
+                   GEN_STS, GEN_SVC, GEN_VS, GEN_OWNER_REF, GEN_OWNER_V1, GEN_ALL, ODH_RBAC, MUT_CREATE, MUT_CA_BUNDLE,
                    scan_lengths_noalloc, SCAN_NOALLOC_MAX_N)

@@ -9,6 +9,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 GEN_STS, GEN_SVC, GEN_VS, GEN_OWNER_REF, GEN_OWNER_V1 = 1, 2, 4, 8, 16
 GEN_ALL = GEN_STS | GEN_SVC | GEN_VS
 ODH_RBAC = 32
+MUT_CREATE, MUT_CA_BUNDLE = 1, 2
 
 STATUS_NAMES = {0: "OK", 1: "E_PARSE", 2: "E_NO_CONTAINERS", 3: "E_SEGS", 4: "E_PORTS_EMPTY",
                 5: "E_NIL_REPLICAS", 6: "E_DENIED", 7: "E_CONFLICT", 8: "E_LIMIT"}
@@ -99,6 +100,8 @@ def load_library():
     lib.nbrm_culling_pass.argtypes = [C.c_void_p, C.POINTER(_Docs), C.POINTER(_Docs), C.POINTER(_Docs),
                                       C.c_char_p, C.c_uint64, C.c_int32, C.c_int32, C.POINTER(_Out)]
     lib.nbrm_culling_pass_resident.argtypes = [C.c_void_p, C.c_uint64, C.c_int32, C.c_int32]
+    lib.nbrm_odh_mutate.argtypes = [C.c_void_p, C.POINTER(_Docs), C.POINTER(_Docs), C.c_uint32, C.POINTER(_Out)]
+    lib.nbrm_odh_mutate_resident.argtypes = [C.c_void_p, C.c_uint32, C.c_int]
     lib.nbrm_scan_lengths_noalloc.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p,
                                               C.c_char_p, C.c_size_t]
     _lib = lib
@@ -302,4 +305,12 @@ class Context:
         a, b, d, o = notebooks.c_struct(), kernels.c_struct(), terminals.c_struct(), _Out()
         self._check(self.lib.nbrm_culling_pass(self.h, C.byref(a), C.byref(b), C.byref(d), pod_exists, now,
                                                idle_min, period_min, C.byref(o)))
+        return Result(o, copy)
+
+    # --- ODH mutating webhook
+    def odh_mutate(self, notebooks, old=None, flags=0, copy=True):
+        d, o = notebooks.c_struct(), _Out()
+        od = old.c_struct() if old is not None else None
+        self._check(self.lib.nbrm_odh_mutate(self.h, C.byref(d), C.byref(od) if od is not None else None,
+                                             flags if old is not None else flags | MUT_CREATE, C.byref(o)))
         return Result(o, copy)

@@ -581,4 +581,22 @@ int nbrm_culling_pass(nbrm_ctx* c, const nbrm_docs* notebooks, const nbrm_docs* 
   return nbrm_download(c, out);
 }
 
+int nbrm_odh_mutate_resident(nbrm_ctx* c, uint32_t flags, int is_update) {
+  if (!c) return -2;
+  if (!is_update) return run_generator(c, GEN_ID_MUTATE, {1, -1, -1}, flags | 1u, nullptr, 0);
+  if (int r = run_generator(c, GEN_ID_MUTATE, {1, -1, -1}, flags & ~1u, nullptr, 0)) return r;
+  if (int r = nbrm_result_to_slot(c, 0)) return r;  // the mutated Notebooks become slot 0
+  return run_generator(c, GEN_ID_GUARD, {0, 1, 2}, 0, nullptr, 0);
+}
+
+int nbrm_odh_mutate(nbrm_ctx* c, const nbrm_docs* notebooks, const nbrm_docs* old_notebooks,
+                    uint32_t flags, nbrm_out* out) {
+  if (!c || !out) return -2;
+  if (int r = nbrm_upload(c, 1, notebooks)) return r;
+  if (old_notebooks)
+    if (int r = nbrm_upload(c, 2, old_notebooks)) return r;
+  if (int r = nbrm_odh_mutate_resident(c, flags, old_notebooks != nullptr)) return r;
+  return nbrm_download(c, out);
+}
+
 }  // extern "C"

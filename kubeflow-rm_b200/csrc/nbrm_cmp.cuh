@@ -105,12 +105,23 @@ NB_HD bool str_equal(const Doc& a, Span x, const Doc& b, Span y) {
   }
 }
 
-NB_HD uint32_t count_members(const Doc& d, Span obj) {  // null-valued members do not count
+// A member that decodes to Go nil.  SEM adds equality.Semantic.DeepEqual's rule
+// that an empty slice or map equals a nil one (odh-notebook-controller/
+// controllers/notebook_webhook.go:353,359).
+template <bool SEM>
+NB_HD bool member_is_nil(const Doc& d, Span v) {
+  if (is_nil(d, v)) return true;
+  if (SEM && (is_object(d, v) || is_array(d, v)) && is_empty_container(d, v)) return true;
+  return false;
+}
+
+template <bool SEM>
+NB_HD uint32_t count_members(const Doc& d, Span obj) {  // nil-valued members do not count
   ObjIter it(d, obj);
   Member m;
   uint32_t n = 0;
   while (it.next(d, m))
-    if (!is_null(d, m.val)) ++n;
+    if (!member_is_nil<SEM>(d, m.val)) ++n;
   return n;
 }
 
@@ -132,8 +143,9 @@ struct EqFrame {
 };
 
 // nil (absent / null) on both sides is equal; nil vs anything else is not.
-NB_HD bool json_equal(const Doc& a, Span x, const Doc& b, Span y) {
-  const bool xn = is_nil(a, x), yn = is_nil(b, y);
+template <bool SEM>
+NB_HD bool json_equal_t(const Doc& a, Span x, const Doc& b, Span y) {
+  const bool xn = member_is_nil<SEM>(a, x), yn = member_is_nil<SEM>(b, y);
   if (xn || yn) return xn && yn;
   EqFrame st[EQ_MAX_DEPTH];
   int sp = 0;
@@ -146,7 +158,7 @@ NB_HD bool json_equal(const Doc& a, Span x, const Doc& b, Span y) {
       if (ta == '"') {
         if (tb != '"' || !str_equal(a, cx, b, cy)) return false;
       } else if (ta == '{') {
-        if (tb != '{' || count_members(a, cx) != count_members(b, cy)) return false;
+        if (tb != '{' || count_members<SEM>(a, cx) != count_members<SEM>(b, cy)) return false;
         if (sp >= EQ_MAX_DEPTH) return false;
         st[sp].ai = cx.off + 1;
         st[sp].aend = cx.end() - 1;
@@ -177,7 +189,7 @@ NB_HD bool json_equal(const Doc& a, Span x, const Doc& b, Span y) {
       Member m;
       bool got = false;
       while (it.next(a, m)) {
-        if (is_null(a, m.val)) continue;
+        if (member_is_nil<SEM>(a, m.val)) continue;
         got = true;
         break;
       }
@@ -187,7 +199,7 @@ NB_HD bool json_equal(const Doc& a, Span x, const Doc& b, Span y) {
         continue;
       }
       Span bv = find_key(b, mk(f.bi, f.bend - f.bi), a, m.key);
-      if (is_nil(b, bv)) return false;
+      if (member_is_nil<SEM>(b, bv)) return false;
       cx = m.val;
       cy = bv;
       have = true;
@@ -211,6 +223,13 @@ NB_HD bool json_equal(const Doc& a, Span x, const Doc& b, Span y) {
       have = true;
     }
   }
+}
+
+NB_HD bool json_equal(const Doc& a, Span x, const Doc& b, Span y) {
+  return json_equal_t<false>(a, x, b, y);
+}
+NB_HD bool semantic_equal(const Doc& a, Span x, const Doc& b, Span y) {
+  return json_equal_t<true>(a, x, b, y);
 }
 
 // ---------------------------------------------------------------- Copy*Fields

@@ -5,6 +5,7 @@
 #include "nbrm_cmp.cuh"
 #include "nbrm_status.cuh"
 #include "nbrm_cull.cuh"
+#include "nbrm_mutate.cuh"
 
 namespace nbrm {
 
@@ -120,6 +121,8 @@ void launch_plan(int gen, const PlanIn& in, const PlanOut& out, uint64_t in_byte
     case GEN_ID_COPY: launch<GenCopyFields>(in, out, in_bytes, st); break;
     case GEN_ID_STATUS: launch<GenStatus>(in, out, in_bytes, st); break;
     case GEN_ID_CULL: launch<GenCull>(in, out, in_bytes, st); break;
+    case GEN_ID_MUTATE: launch<GenMutate>(in, out, in_bytes, st); break;
+    case GEN_ID_GUARD: launch<GenRestartGuard>(in, out, in_bytes, st); break;
   }
 }
 
@@ -130,6 +133,8 @@ void gen_shape(int gen, uint32_t* nobj, uint32_t* cap) {
     case GEN_ID_COPY: *nobj = GenCopyFields::NOBJ; *cap = GenCopyFields::CAP; break;
     case GEN_ID_STATUS: *nobj = GenStatus::NOBJ; *cap = GenStatus::CAP; break;
     case GEN_ID_CULL: *nobj = GenCull::NOBJ; *cap = GenCull::CAP; break;
+    case GEN_ID_MUTATE: *nobj = GenMutate::NOBJ; *cap = GenMutate::CAP; break;
+    case GEN_ID_GUARD: *nobj = GenRestartGuard::NOBJ; *cap = GenRestartGuard::CAP; break;
     default: *nobj = 0; *cap = 0;
   }
 }

@@ -15,6 +15,7 @@
 #include "../../kubeflow-rm_b200/csrc/nbrm_cmp.cuh"
 #include "../../kubeflow-rm_b200/csrc/nbrm_status.cuh"
 #include "../../kubeflow-rm_b200/csrc/nbrm_cull.cuh"
+#include "../../kubeflow-rm_b200/csrc/nbrm_mutate.cuh"
 #include "../../kubeflow-rm_b200/csrc/nbrm_pool.h"
 
 using namespace nbrm;
@@ -115,6 +116,8 @@ int hostplan_run(int gen, const char* d0, const uint64_t* o0, const char* d1, co
     case 2: rc = run_host<GenCopyFields>(data, off, n, env, flags, extra, now, arg0, arg1); *nobj = GenCopyFields::NOBJ; break;
     case 3: rc = run_host<GenStatus>(data, off, n, env, flags, extra, now, arg0, arg1); *nobj = GenStatus::NOBJ; break;
     case 4: rc = run_host<GenCull>(data, off, n, env, flags, extra, now, arg0, arg1); *nobj = GenCull::NOBJ; break;
+    case 5: rc = run_host<GenMutate>(data, off, n, env, flags, extra, now, arg0, arg1); *nobj = GenMutate::NOBJ; break;
+    case 6: rc = run_host<GenRestartGuard>(data, off, n, env, flags, extra, now, arg0, arg1); *nobj = GenRestartGuard::NOBJ; break;
   }
   *out_data = g_out.data.data();
   *out_off = g_out.off.data();

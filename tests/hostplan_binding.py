@@ -4,7 +4,7 @@ import ctypes as C
 
 import numpy as np
 
-GEN_NBC, GEN_ODH, GEN_COPY, GEN_STATUS, GEN_CULL = 0, 1, 2, 3, 4
+GEN_NBC, GEN_ODH, GEN_COPY, GEN_STATUS, GEN_CULL, GEN_MUTATE, GEN_GUARD = 0, 1, 2, 3, 4, 5, 6
 
 
 def _pack(docs_list):
@@ -81,3 +81,9 @@ class HostPlan:
     def cull(self, notebooks, kernels, terminals, pod_exists, now, idle_min, period_min):
         return self.run(GEN_CULL, [notebooks, kernels, terminals], extra=bytes(pod_exists), now=now,
                         arg0=idle_min, arg1=period_min, want_result=True)
+
+    def mutate(self, notebooks, env=None, flags=1):
+        return self.run(GEN_MUTATE, [notebooks], env, flags)
+
+    def restart_guard(self, mutated, updated, old, env=None):
+        return self.run(GEN_GUARD, [mutated, updated, old], env, want_result=True)

@@ -123,3 +123,52 @@ def check_cull(cases, outs, status, result, now, idle_min, period_min):
                 "case %d outcome %d\n got %s\n exp %s" % (i, outcome, gojson.canon(got), gojson.canon(exp))
         seen[outcome] += 1
     return seen
+
+
+PENDING = "notebooks.opendatahub.io/update-pending"
+
+
+def _mask_pending(tree):
+    a = (tree.get("metadata") or {}).get("annotations")
+    if isinstance(a, dict) and PENDING in a:
+        a[PENDING] = "<reason>"       # the reference's text is a go-cmp diff: presence is what is compared
+    return tree
+
+
+def _cert_env_as_set(tree, nb_name):
+    """InjectCertConfig appends its env vars in Go map order (random in the
+    reference): compare the five names as a set, at the tail of the list."""
+    for c in (((tree.get("spec") or {}).get("template") or {}).get("spec") or {}).get("containers") or []:
+        env = c.get("env")
+        if c.get("name") == nb_name and isinstance(env, list):
+            tail = [e for e in env if e.get("name") in odh.CERT_ENV_VARS and e.get("value") == odh.CERT_MOUNT_PATH]
+            head = [e for e in env if e not in tail]
+            c["env"] = head + sorted(tail, key=lambda e: e["name"])
+    return tree
+
+
+def check_mutate(requests, olds, outs, status, result, image, ca_bundle):
+    """requests: Notebook trees; olds: None (CREATE) or trees (UPDATE)."""
+    n_denied = n_blocked = n_ok = 0
+    for i, nb in enumerate(requests):
+        old = olds[i] if olds is not None else None
+        try:
+            exp, reason = odh.mutate_notebook(nb, "CREATE" if olds is None else "UPDATE", old=old,
+                                              image=image, ca_bundle=ca_bundle)
+        except odh.Denied:
+            assert status[i] == 6 and outs[i] == b"", (i, status[i])
+            n_denied += 1
+            continue
+        except (KeyError, TypeError, AttributeError):
+            assert status[i] != 0, i          # a shape the Go decoder would have rejected
+            continue
+        assert status[i] == 0, (i, status[i])
+        got = json.loads(outs[i])
+        name = (nb.get("metadata") or {}).get("name")
+        a = gojson.canon(_cert_env_as_set(_mask_pending(got), name))
+        b = gojson.canon(_cert_env_as_set(_mask_pending(exp), name))
+        assert a == b, "request %d\n got %s\n exp %s" % (i, a, b)
+        assert bool(result[i]) == bool(reason), (i, result[i], reason)
+        n_blocked += bool(reason)
+        n_ok += 1
+    return n_ok, n_denied, n_blocked
