@@ -349,9 +349,14 @@ int run_generator(nbrm_ctx* c, int gen, const int (&map)[3], uint32_t flags, con
     if (map[k] < 0) continue;
     Slot& s = c->slot[map[k]];
     if (!s.off.p) return fail_msg(c, "an input slot this entry point reads was never uploaded");
-    if (first) n = s.n;
-    else if (s.n != n) return fail_msg(c, "input slots hold different numbers of documents");
-    first = false;
+    const bool shared = k == 1 && gen_shared1(gen);
+    if (shared) {
+      in.shared_n = s.n;
+    } else {
+      if (first) n = s.n;
+      else if (s.n != n) return fail_msg(c, "input slots hold different numbers of documents");
+      first = false;
+    }
     in.slot[k].data = s.data.as<char>();
     in.slot[k].off = s.off.as<uint64_t>();
     in_bytes += s.bytes;

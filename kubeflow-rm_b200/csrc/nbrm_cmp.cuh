@@ -497,6 +497,7 @@ NB_HD void plan_copy_fields(Planner& P, const Doc& from, const Doc& to) {
 // The compare generator: slot 0 desired, slot 1 found, one output per pair.
 struct GenCopyFields {
   static const uint32_t NOBJ = 1;
+  static const bool SHARED1 = false;  // slot 1 is per-tuple, not one shared arena
   static const uint32_t CAP = 48;
   struct K {
     DocCtx& c;

@@ -263,6 +263,7 @@ NB_HD void plan_cull(Planner& P, DocCtx& c) {
 
 struct GenCull {
   static const uint32_t NOBJ = 1;
+  static const bool SHARED1 = false;  // slot 1 is per-tuple, not one shared arena
   static const uint32_t CAP = 32;
   struct K {
     DocCtx& c;

@@ -34,6 +34,10 @@ struct DocCtx {
   const void* extra;    // generator-specific side input (device pointer), may be null
   uint64_t now;         // caller-supplied clock, Unix seconds (generators that stamp times)
   uint32_t arg0, arg1;  // generator-specific integers (e.g. culling periods)
+  // generators with SHARED1: input slot 1 as one arena every tuple may read
+  const char* shared;
+  const uint64_t* shared_off;
+  uint32_t shared_n;
   uint32_t result;      // generator-specific per-tuple result word (0 when unused)
 };
 

@@ -364,6 +364,7 @@ NB_HD void plan_notebook_with(Planner& P, const Doc& d, const NbView& v, const E
 
 struct GenMutate {
   static const uint32_t NOBJ = 1;
+  static const bool SHARED1 = false;  // slot 1 is per-tuple, not one shared arena
   static const uint32_t CAP = 224;
   struct K {
     DocCtx& c;
@@ -400,6 +401,7 @@ struct GenMutate {
 // changes were held back.
 struct GenRestartGuard {
   static const uint32_t NOBJ = 1;
+  static const bool SHARED1 = false;  // slot 1 is per-tuple, not one shared arena
   static const uint32_t CAP = 96;
   struct K {
     DocCtx& c;

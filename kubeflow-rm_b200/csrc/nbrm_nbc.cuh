@@ -559,6 +559,7 @@ NB_HD void plan_virtualservice(Planner& P, const Doc& d, const NbView& v, const 
 // The notebook-controller generator: StatefulSet, Service, VirtualService.
 struct GenNbc {
   static const uint32_t NOBJ = 3;
+  static const bool SHARED1 = false;  // slot 1 is per-tuple, not one shared arena
   static const uint32_t CAP = 96;
   struct K {
     DocCtx& c;

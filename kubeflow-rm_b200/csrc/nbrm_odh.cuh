@@ -186,6 +186,7 @@ NB_HD void plan_odh_object(Planner& P, const Doc& d, const NbView& v, const EnvL
 // The ODH reconcile generator.  extra = 16 seed bytes per Notebook (or null).
 struct GenOdh {
   static const uint32_t NOBJ = ODH_OUT_PER_DOC;
+  static const bool SHARED1 = false;  // slot 1 is per-tuple, not one shared arena
   static const uint32_t CAP = 32;
   struct K {
     DocCtx& c;

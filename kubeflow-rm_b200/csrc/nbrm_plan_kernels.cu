@@ -35,7 +35,7 @@ __global__ void plan_kernel(PlanIn in, PlanOut out, uint32_t smem_cap) {
   for (int k = 0; k < 3; ++k) {
     g0[k] = a0[k] = 0;
     soff[k] = total;
-    if (in.slot[k].data) {
+    if (in.slot[k].data && !(G::SHARED1 && k == 1)) {
       g0[k] = in.slot[k].off[b0];
       const uint64_t g1 = in.slot[k].off[b1];
       a0[k] = g0[k] & ~15ull;
@@ -48,7 +48,7 @@ __global__ void plan_kernel(PlanIn in, PlanOut out, uint32_t smem_cap) {
   if (staged) {
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
-      if (!in.slot[k].data) continue;
+      if (!in.slot[k].data || (G::SHARED1 && k == 1)) continue;
       const uint32_t chunks = ((k < 2 ? soff[k + 1] : total) - soff[k]) >> 4;
       const uint4* src = reinterpret_cast<const uint4*>(in.slot[k].data + a0[k]);
       uint4* dst = reinterpret_cast<uint4*>(plan_smem + soff[k]);
@@ -62,7 +62,7 @@ __global__ void plan_kernel(PlanIn in, PlanOut out, uint32_t smem_cap) {
   uint32_t aux_abs = i * AUX_PAD, aux_cap = AUX_PAD;
 #pragma unroll
   for (int k = 0; k < 3; ++k) {
-    if (in.slot[k].data) {
+    if (in.slot[k].data && !(G::SHARED1 && k == 1)) {
       const uint64_t o0 = in.slot[k].off[i], o1 = in.slot[k].off[i + 1];
       c.d[k].p = staged ? plan_smem + soff[k] + (uint32_t)(o0 - a0[k]) : in.slot[k].data + o0;
       c.d[k].n = (uint32_t)(o1 - o0);
@@ -87,6 +87,9 @@ __global__ void plan_kernel(PlanIn in, PlanOut out, uint32_t smem_cap) {
   c.arg0 = in.arg0;
   c.arg1 = in.arg1;
   c.result = 0;
+  c.shared = G::SHARED1 ? in.slot[1].data : nullptr;
+  c.shared_off = G::SHARED1 ? in.slot[1].off : nullptr;
+  c.shared_n = G::SHARED1 ? in.shared_n : 0;
   ObjSink s;
   s.segs = out.segs + (size_t)i * G::NOBJ * out.cap;
   s.nseg = out.nseg + (size_t)i * G::NOBJ;
@@ -138,5 +141,7 @@ void gen_shape(int gen, uint32_t* nobj, uint32_t* cap) {
     default: *nobj = 0; *cap = 0;
   }
 }
+
+bool gen_shared1(int gen) { return gen == GEN_ID_PODDEFAULT; }
 
 }  // namespace nbrm

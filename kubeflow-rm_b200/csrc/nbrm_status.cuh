@@ -131,6 +131,7 @@ NB_HD void plan_status(Planner& P, DocCtx& c) {
 
 struct GenStatus {
   static const uint32_t NOBJ = 1;
+  static const bool SHARED1 = false;  // slot 1 is per-tuple, not one shared arena
   static const uint32_t CAP = 160;
   struct K {
     DocCtx& c;

@@ -266,7 +266,7 @@ def mutate_pod(pod, pds, request_namespace=""):
     patch is produced (:628,:631,:649,:660)."""
     pod = deepcopy(pod)
     m = pod.setdefault("metadata", {})
-    if m.get("namespace", "") == "":
+    if m.get("namespace", "") == "" and request_namespace != "":
         m["namespace"] = request_namespace                          # :616-619
     ann = m.get("annotations")
     if ann is not None:                                             # :625-633

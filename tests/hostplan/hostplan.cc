@@ -33,13 +33,14 @@ Out g_out;
 
 template <class G>
 int run_host(const char* const data[3], const uint64_t* const off[3], uint64_t n, const nbrm_env* env,
-             uint32_t flags, const void* extra, uint64_t now, uint32_t arg0, uint32_t arg1) {
+             uint32_t flags, const void* extra, uint64_t now, uint32_t arg0, uint32_t arg1,
+             uint32_t shared_n) {
   std::string pool;
   EnvLits L;
   build_pool_host(env, pool, L);
   uint64_t total_in = 0;
   for (int k = 0; k < 3; ++k)
-    if (data[k] && n) total_in += off[k][n];
+    if (data[k] && n && !(G::SHARED1 && k == 1)) total_in += off[k][n];
   std::vector<char> aux(total_in + n * AUX_PAD + 16);
   g_out.data.clear();
   g_out.off.assign(1, 0);
@@ -53,7 +54,7 @@ int run_host(const char* const data[3], const uint64_t* const off[3], uint64_t n
     DocCtx c;
     uint32_t aux_abs = (uint32_t)i * AUX_PAD, aux_cap = AUX_PAD;
     for (int k = 0; k < 3; ++k) {
-      if (data[k]) {
+      if (data[k] && !(G::SHARED1 && k == 1)) {
         c.d[k].p = data[k] + off[k][i];
         c.d[k].n = (uint32_t)(off[k][i + 1] - off[k][i]);
         c.base[k] = (uint32_t)off[k][i];
@@ -77,6 +78,9 @@ int run_host(const char* const data[3], const uint64_t* const off[3], uint64_t n
     c.arg0 = arg0;
     c.arg1 = arg1;
     c.result = 0;
+    c.shared = G::SHARED1 ? data[1] : nullptr;
+    c.shared_off = G::SHARED1 ? off[1] : nullptr;
+    c.shared_n = G::SHARED1 ? shared_n : 0;
     ObjSink s;
     s.segs = segs.data();
     s.nseg = nseg.data();
@@ -104,20 +108,21 @@ extern "C" {
 // gen: 0 notebook-controller (3 objects), 1 ODH reconcile (7), 2 Copy*Fields (1), 3 status (1), 4 culling (1)
 int hostplan_run(int gen, const char* d0, const uint64_t* o0, const char* d1, const uint64_t* o1,
                  const char* d2, const uint64_t* o2, uint64_t n, const nbrm_env* env, uint32_t flags,
-                 const void* extra, uint64_t now, uint32_t arg0, uint32_t arg1, uint32_t* nobj,
+                 const void* extra, uint64_t now, uint32_t arg0, uint32_t arg1, uint32_t shared_n,
+                 uint32_t* nobj,
                  const char** out_data, const uint64_t** out_off, const uint32_t** out_status,
                  const uint32_t** out_result) {
   const char* data[3] = {d0, d1, d2};
   const uint64_t* off[3] = {o0, o1, o2};
   int rc = -9;
   switch (gen) {
-    case 0: rc = run_host<GenNbc>(data, off, n, env, flags, extra, now, arg0, arg1); *nobj = GenNbc::NOBJ; break;
-    case 1: rc = run_host<GenOdh>(data, off, n, env, flags, extra, now, arg0, arg1); *nobj = GenOdh::NOBJ; break;
-    case 2: rc = run_host<GenCopyFields>(data, off, n, env, flags, extra, now, arg0, arg1); *nobj = GenCopyFields::NOBJ; break;
-    case 3: rc = run_host<GenStatus>(data, off, n, env, flags, extra, now, arg0, arg1); *nobj = GenStatus::NOBJ; break;
-    case 4: rc = run_host<GenCull>(data, off, n, env, flags, extra, now, arg0, arg1); *nobj = GenCull::NOBJ; break;
-    case 5: rc = run_host<GenMutate>(data, off, n, env, flags, extra, now, arg0, arg1); *nobj = GenMutate::NOBJ; break;
-    case 6: rc = run_host<GenRestartGuard>(data, off, n, env, flags, extra, now, arg0, arg1); *nobj = GenRestartGuard::NOBJ; break;
+    case 0: rc = run_host<GenNbc>(data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenNbc::NOBJ; break;
+    case 1: rc = run_host<GenOdh>(data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenOdh::NOBJ; break;
+    case 2: rc = run_host<GenCopyFields>(data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenCopyFields::NOBJ; break;
+    case 3: rc = run_host<GenStatus>(data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenStatus::NOBJ; break;
+    case 4: rc = run_host<GenCull>(data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenCull::NOBJ; break;
+    case 5: rc = run_host<GenMutate>(data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenMutate::NOBJ; break;
+    case 6: rc = run_host<GenRestartGuard>(data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenRestartGuard::NOBJ; break;
   }
   *out_data = g_out.data.data();
   *out_off = g_out.off.data();

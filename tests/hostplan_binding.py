@@ -20,18 +20,19 @@ class HostPlan:
         self.lib = C.CDLL(path)
         self.lib.hostplan_run.restype = C.c_int
 
-    def run(self, gen, slots, env=None, flags=0, extra=None, now=0, arg0=0, arg1=0, want_result=False):
+    def run(self, gen, slots, env=None, flags=0, extra=None, now=0, arg0=0, arg1=0, want_result=False, shared1=False):
         """slots: up to three lists of byte strings (None = slot unused)."""
         import __graft_entry__ as graft
         capi = __import__(graft.PKG_NAME + ".capi", fromlist=["x"])
         slots = list(slots) + [None] * (3 - len(slots))
         n = len(next(s for s in slots if s is not None))
+        shared_n = len(slots[1]) if shared1 else 0
         args, keep = [], []
-        for s in slots:
+        for k, s in enumerate(slots):
             if s is None:
                 args += [None, None]
             else:
-                assert len(s) == n
+                assert len(s) == n or (shared1 and k == 1)
                 data, off = _pack(s)
                 keep.append((data, off))
                 args += [C.c_char_p(data), C.c_void_p(off.ctypes.data)]
@@ -44,7 +45,7 @@ class HostPlan:
         rc = self.lib.hostplan_run(C.c_int(gen), *args, C.c_uint64(n),
                                    C.byref(e) if e is not None else None, C.c_uint32(flags),
                                    C.c_char_p(extra) if extra is not None else None, C.c_uint64(now),
-                                   C.c_uint32(arg0), C.c_uint32(arg1),
+                                   C.c_uint32(arg0), C.c_uint32(arg1), C.c_uint32(shared_n),
                                    C.byref(nobj), C.byref(pd), C.byref(po), C.byref(ps), C.byref(pr))
         assert rc == 0, rc
         m = n * nobj.value
