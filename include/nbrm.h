@@ -47,7 +47,8 @@ enum {
   NBRM_E_NIL_REPLICAS = 5,  /* reference panics: *Spec.Replicas, common/reconcilehelper/util.go:123 */
   NBRM_E_DENIED = 6,        /* admission.Denied, odh-notebook-controller/controllers/notebook_webhook.go:274 */
   NBRM_E_CONFLICT = 7,      /* PodDefault merge conflict, admission-webhook/main.go:671-679 */
-  NBRM_E_LIMIT = 8          /* a documented fixed limit of this library was exceeded */
+  NBRM_E_LIMIT = 8,         /* a documented fixed limit of this library was exceeded */
+  NBRM_E_SELECTOR = 9       /* label selector conversion failed, admission-webhook/main.go:77-79 */
 };
 
 /* The process environment and flags the reference reads while generating
@@ -249,6 +250,31 @@ enum { NBRM_MUT_CREATE = 1, NBRM_MUT_CA_BUNDLE = 2 };
 int nbrm_odh_mutate(nbrm_ctx* ctx, const nbrm_docs* notebooks, const nbrm_docs* old_notebooks,
                     uint32_t flags, nbrm_out* out);
 int nbrm_odh_mutate_resident(nbrm_ctx* ctx, uint32_t flags, int is_update);
+
+/* ---- PodDefault admission ---------------------------------------------------
+ * Replaces, for a batch of Pod CREATE requests, mutatePods from the decoded Pod
+ * on (admission-webhook/main.go:616-704): the exclude / mirror-pod checks
+ * :625-633, filterPodDefaults :72-97 (label selectors with matchLabels and
+ * matchExpressions In / NotIn / Exists / DoesNotExist, then the same-namespace
+ * test), safeToApplyPodDefaultsOnPod :101-166 with mergeImagePullSecrets :170,
+ * mergeEnv :217, mergeEnvFrom :254, mergeVolumeMounts :266, mergeVolumes :321,
+ * mergeContainers :364, mergeTolerations :411, mergeMap :454,
+ * applyPodDefaultsOnPod :480-556, applyPodDefaultsOnContainer :561-578,
+ * setCommandAndArgs :582-597 and the patch of :685-701.
+ * pods: one Pod per request.  poddefaults: every PodDefault the caller has
+ * listed (the reference lists per request, :635-637; a caller keeps them
+ * cached), grouped so that ranges[2i], ranges[2i+1] = the [begin, end) of the
+ * PodDefaults in Pod i's namespace (NULL = all of them for every Pod).
+ * Output per Pod: an RFC 6902 patch replacing /metadata and /spec (two "add"
+ * operations), or length 0 = allowed without patch.  The reference's patch has
+ * Go-map operation order; equality is by effect (apply it, compare the Pod).
+ * status: NBRM_E_CONFLICT = rejected, conflict while merging (:671-679);
+ * NBRM_E_SELECTOR = rejected, bad selector (:653-656).  result = number of
+ * PodDefaults applied.  Limits: 32 PodDefaults applied to one Pod, 32 items
+ * appended to one list (NBRM_E_LIMIT beyond). */
+int nbrm_poddefault_mutate(nbrm_ctx* ctx, const nbrm_docs* pods, const nbrm_docs* poddefaults,
+                           const uint32_t* ranges, nbrm_out* out);
+int nbrm_poddefault_mutate_resident(nbrm_ctx* ctx);
 
 /* ---- offsets without allocation -----------------------------------------
  * No counterpart in the reference: this entry point exists for embedders, not

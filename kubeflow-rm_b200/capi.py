@@ -12,7 +12,7 @@ ODH_RBAC = 32
 MUT_CREATE, MUT_CA_BUNDLE = 1, 2
 
 STATUS_NAMES = {0: "OK", 1: "E_PARSE", 2: "E_NO_CONTAINERS", 3: "E_SEGS", 4: "E_PORTS_EMPTY",
-                5: "E_NIL_REPLICAS", 6: "E_DENIED", 7: "E_CONFLICT", 8: "E_LIMIT"}
+                5: "E_NIL_REPLICAS", 6: "E_DENIED", 7: "E_CONFLICT", 8: "E_LIMIT", 9: "E_SELECTOR"}
 
 
 class NbrmError(RuntimeError):
@@ -102,6 +102,9 @@ def load_library():
     lib.nbrm_culling_pass_resident.argtypes = [C.c_void_p, C.c_uint64, C.c_int32, C.c_int32]
     lib.nbrm_odh_mutate.argtypes = [C.c_void_p, C.POINTER(_Docs), C.POINTER(_Docs), C.c_uint32, C.POINTER(_Out)]
     lib.nbrm_odh_mutate_resident.argtypes = [C.c_void_p, C.c_uint32, C.c_int]
+    lib.nbrm_poddefault_mutate.argtypes = [C.c_void_p, C.POINTER(_Docs), C.POINTER(_Docs), C.c_void_p,
+                                           C.POINTER(_Out)]
+    lib.nbrm_poddefault_mutate_resident.argtypes = [C.c_void_p]
     lib.nbrm_scan_lengths_noalloc.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p,
                                               C.c_char_p, C.c_size_t]
     _lib = lib
@@ -314,3 +317,16 @@ class Context:
         self._check(self.lib.nbrm_odh_mutate(self.h, C.byref(d), C.byref(od) if od is not None else None,
                                              flags if old is not None else flags | MUT_CREATE, C.byref(o)))
         return Result(o, copy)
+
+    # --- PodDefault admission
+    def poddefault_mutate(self, pods, poddefaults, ranges=None, copy=True):
+        a, b, o = pods.c_struct(), poddefaults.c_struct(), _Out()
+        r = None
+        if ranges is not None:
+            r = np.ascontiguousarray(np.asarray(ranges, dtype=np.uint32).reshape(-1))
+        self._check(self.lib.nbrm_poddefault_mutate(self.h, C.byref(a), C.byref(b),
+                                                    r.ctypes.data if r is not None else None, C.byref(o)))
+        return Result(o, copy)
+
+    def poddefault_mutate_resident(self):
+        self._check(self.lib.nbrm_poddefault_mutate_resident(self.h))

@@ -604,4 +604,25 @@ int nbrm_odh_mutate(nbrm_ctx* c, const nbrm_docs* notebooks, const nbrm_docs* ol
   return nbrm_download(c, out);
 }
 
+int nbrm_poddefault_mutate_resident(nbrm_ctx* c) {
+  if (!c) return -2;
+  const void* ranges = nullptr;
+  if (c->extra_bytes) {
+    if (c->extra_bytes != (uint64_t)c->slot[0].n * 8)
+      return fail_msg(c, "nbrm_poddefault_mutate: ranges must hold two uint32 per Pod");
+    ranges = c->extra.p;
+  }
+  return run_generator(c, GEN_ID_PODDEFAULT, {0, 1, -1}, 0, ranges, 0);
+}
+
+int nbrm_poddefault_mutate(nbrm_ctx* c, const nbrm_docs* pods, const nbrm_docs* poddefaults,
+                           const uint32_t* ranges, nbrm_out* out) {
+  if (!c || !out) return -2;
+  if (int r = nbrm_upload(c, 0, pods)) return r;
+  if (int r = nbrm_upload(c, 1, poddefaults)) return r;
+  if (int r = nbrm_upload_bytes(c, ranges, ranges ? pods->n * 8 : 0)) return r;
+  if (int r = nbrm_poddefault_mutate_resident(c)) return r;
+  return nbrm_download(c, out);
+}
+
 }  // extern "C"

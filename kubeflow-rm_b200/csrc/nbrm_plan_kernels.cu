@@ -6,6 +6,7 @@
 #include "nbrm_status.cuh"
 #include "nbrm_cull.cuh"
 #include "nbrm_mutate.cuh"
+#include "nbrm_pd.cuh"
 
 namespace nbrm {
 
@@ -126,6 +127,7 @@ void launch_plan(int gen, const PlanIn& in, const PlanOut& out, uint64_t in_byte
     case GEN_ID_CULL: launch<GenCull>(in, out, in_bytes, st); break;
     case GEN_ID_MUTATE: launch<GenMutate>(in, out, in_bytes, st); break;
     case GEN_ID_GUARD: launch<GenRestartGuard>(in, out, in_bytes, st); break;
+    case GEN_ID_PODDEFAULT: launch<GenPodDefault>(in, out, in_bytes, st); break;
   }
 }
 
@@ -138,6 +140,7 @@ void gen_shape(int gen, uint32_t* nobj, uint32_t* cap) {
     case GEN_ID_CULL: *nobj = GenCull::NOBJ; *cap = GenCull::CAP; break;
     case GEN_ID_MUTATE: *nobj = GenMutate::NOBJ; *cap = GenMutate::CAP; break;
     case GEN_ID_GUARD: *nobj = GenRestartGuard::NOBJ; *cap = GenRestartGuard::CAP; break;
+    case GEN_ID_PODDEFAULT: *nobj = GenPodDefault::NOBJ; *cap = GenPodDefault::CAP; break;
     default: *nobj = 0; *cap = 0;
   }
 }

@@ -381,3 +381,122 @@ def culling_case(rng, i, now):
     kernels = None if rng.random() < 0.15 else acts(rng.randint(0, 3), True)
     terminals = None if rng.random() < 0.3 else acts(rng.randint(0, 2), False)
     return nb, rng.random() > 0.1, kernels, terminals
+
+
+# ---------------------------------------------------------------- PodDefault admission (C3)
+
+
+def poddefaults_for_namespace(rng, ns, count):
+    """`count` PodDefaults in namespace `ns`: the add-gcp-secret shape of
+    admission-webhook/README.md (1 matchLabel, 1 volume, 1 volumeMount), 25 % with
+    env vars, 10 % with a sidecar (admission-webhook/examples/
+    poddefault-inject-containers.yaml), 5 % conflicting on purpose, a few with
+    matchExpressions, tolerations, annotations, labels, command/args."""
+    out = []
+    for j in range(count):
+        name = "pd-%s-%03d" % (ns, j)
+        sel = {"matchLabels": {"pd-%d" % j: "true"}}
+        r = rng.random()
+        if r < 0.08:
+            sel = {"matchExpressions": [{"key": "tier", "operator": rng.choice(["In", "NotIn"]),
+                                         "values": ["gpu", "cpu"]}]}
+        elif r < 0.12:
+            sel = {"matchExpressions": [{"key": "pd-%d" % j, "operator": rng.choice(["Exists", "DoesNotExist"])}]}
+        elif r < 0.125:
+            sel = {}
+        spec = {"selector": sel, "desc": "inject %d" % j,
+                "volumes": [{"name": "secret-%d" % j, "secret": {"secretName": "user-gcp-sa"}}],
+                "volumeMounts": [{"name": "secret-%d" % j, "mountPath": "/secret/%d" % j}]}
+        if rng.random() < 0.25:
+            spec["env"] = [{"name": "PD_%d_%d" % (j, k), "value": "v%d" % k} for k in range(rng.randint(2, 4))]
+        if rng.random() < 0.1:
+            spec["sidecars"] = [{"name": "sidecar-%d" % j, "image": "busybox", "command": ["sleep", "3600"]}]
+        if rng.random() < 0.05:
+            spec["initContainers"] = [{"name": "init-%d" % j, "image": "busybox"}]
+        if rng.random() < 0.1:
+            spec["tolerations"] = [{"key": "tol-%d" % j, "operator": "Exists", "effect": "NoSchedule"}]
+        if rng.random() < 0.15:
+            spec["annotations"] = {"pd-ann-%d" % j: "x"}
+        if rng.random() < 0.1:
+            spec["labels"] = {"pd-label-%d" % j: "y"}
+        if rng.random() < 0.08:
+            spec["serviceAccountName"] = "sa-%d" % j
+        if rng.random() < 0.05:
+            spec["automountServiceAccountToken"] = rng.random() < 0.5
+        if rng.random() < 0.06:
+            spec["command"] = ["/bin/pd-%d" % j]
+        if rng.random() < 0.06:
+            spec["args"] = ["--from-pd", str(j)]
+        if rng.random() < 0.08:
+            spec["envFrom"] = [{"configMapRef": {"name": "cm-%d" % j}}]
+        if rng.random() < 0.05:
+            spec["imagePullSecrets"] = [{"name": "pull-%d" % j}]
+        if rng.random() < 0.05:                      # conflicts with what pods / other PodDefaults carry
+            spec["env"] = spec.get("env", []) + [{"name": "SHARED", "value": "pd-%d" % j}]
+            spec["volumeMounts"].append({"name": "clash-%d" % j, "mountPath": "/home/jovyan"})
+        if rng.random() < 0.0015:
+            spec["selector"] = {"matchExpressions": [{"key": "a", "operator": "Bogus"}]}
+        out.append({"apiVersion": "kubeflow.org/v1alpha1", "kind": "PodDefault",
+                    "metadata": {"name": name, "namespace": ns, "resourceVersion": str(5000 + j)},
+                    "spec": spec})
+    return out
+
+
+def admission_pod(rng, i, ns, n_pds, match_rate=0.3):
+    """Pod of one admission request, shaped like a Notebook StatefulSet's pod
+    (1-3 containers, 0-8 env, 0-4 mounts, 3-8 labels)."""
+    labels = {"statefulset": "nb-%06d" % i, "notebook-name": "nb-%06d" % i, "app": "nb"}
+    for j in range(n_pds):
+        if rng.random() < match_rate / max(1, n_pds ** 0.5):
+            labels["pd-%d" % j] = "true"
+    if rng.random() < 0.3:
+        labels["tier"] = rng.choice(["gpu", "cpu", "other"])
+    ctrs = []
+    for k in range(rng.randint(1, 3)):
+        c = {"name": ["nb", "oauth-proxy", "istio-proxy"][k], "image": "img-%d" % k}
+        if rng.random() < 0.7:
+            c["env"] = [{"name": "E%d" % e, "value": str(e)} for e in range(rng.randint(0, 8))]
+            if rng.random() < 0.2:
+                c["env"].append({"name": "SHARED", "value": "pod"})
+        if rng.random() < 0.7:
+            c["volumeMounts"] = [{"name": "vol-%d" % v, "mountPath": ["/home/jovyan", "/dev/shm", "/data", "/x"][v]}
+                                 for v in range(rng.randint(0, 4))]
+        if rng.random() < 0.2:
+            c["command"] = ["start.sh"]
+        if rng.random() < 0.1:
+            c["args"] = None
+        ctrs.append(c)
+    md = {"name": "nb-%06d-0" % i, "namespace": ns, "labels": labels}
+    r = rng.random()
+    if r < 0.5:
+        md["annotations"] = {"sidecar.istio.io/inject": "false"}
+    if r < 0.04:
+        md["annotations"] = {"poddefault.admission.kubeflow.org/exclude": "true"}
+    elif r < 0.06:
+        md["annotations"] = {"kubernetes.io/config.mirror": "abc"}
+    elif r < 0.1:
+        md["annotations"] = {"poddefault.admission.kubeflow.org/poddefault-pd-%s-000" % ns: "old-rv"}
+    spec = {"containers": ctrs, "serviceAccountName": "default-editor"}
+    if rng.random() < 0.6:
+        spec["volumes"] = [{"name": "vol-%d" % v, "emptyDir": {}} for v in range(rng.randint(0, 3))]
+    if rng.random() < 0.2:
+        spec["tolerations"] = [{"key": "node", "operator": "Exists"}]
+    return {"apiVersion": "v1", "kind": "Pod", "metadata": md, "spec": spec}
+
+
+def admission_workload(n_pods, pds_per_ns, seed=SEED, pods_per_ns=20):
+    """C3: (pods, poddefaults, ranges) — ranges[i] = [begin, end) of pods[i]'s
+    namespace inside the PodDefault list."""
+    rng = random.Random(seed + pds_per_ns)
+    n_ns = max(1, (n_pods + pods_per_ns - 1) // pods_per_ns)
+    pds, ns_range = [], []
+    for k in range(n_ns):
+        lst = poddefaults_for_namespace(rng, "ns-%03d" % k, pds_per_ns)
+        ns_range.append((len(pds), len(pds) + len(lst)))
+        pds += lst
+    pods, ranges = [], []
+    for i in range(n_pods):
+        k = i // pods_per_ns
+        pods.append(admission_pod(rng, i, "ns-%03d" % k, pds_per_ns))
+        ranges.append(ns_range[k])
+    return pods, pds, ranges

@@ -40,33 +40,35 @@ def selector_matches(sel, labels):
     an unknown operator is an error that aborts the request (:77-79)."""
     sel = sel or {}
     labels = labels or {}
+    # LabelSelectorAsSelector converts (and validates) every requirement before
+    # anything is matched, so an invalid one is an error even when an earlier
+    # requirement would not match
+    for req in sel.get("matchExpressions") or []:
+        op, vals = req.get("operator", ""), req.get("values") or []
+        if op in ("In", "NotIn"):
+            if not vals:
+                raise SelectorError("values: Invalid value: for 'in', 'notin' operators, values set can't be empty")
+        elif op in ("Exists", "DoesNotExist"):
+            if vals:
+                raise SelectorError("values: Invalid value: values set must be empty for exists and does not exist")
+        else:
+            raise SelectorError("%r is not a valid label selector operator" % op)
     for k, v in (sel.get("matchLabels") or {}).items():
-        if labels.get(k) != v or k not in labels:
+        if k not in labels or labels[k] != v:
             return False
     for req in sel.get("matchExpressions") or []:
         key, op, vals = req.get("key", ""), req.get("operator", ""), req.get("values") or []
         if op == "In":
-            if not vals:
-                raise SelectorError("values: Invalid value: for 'in', 'notin' operators, values set can't be empty")
             if key not in labels or labels[key] not in vals:
                 return False
         elif op == "NotIn":
-            if not vals:
-                raise SelectorError("values: Invalid value: for 'in', 'notin' operators, values set can't be empty")
             if key in labels and labels[key] in vals:
                 return False
         elif op == "Exists":
-            if vals:
-                raise SelectorError("values: Invalid value: values set must be empty for exists and does not exist")
             if key not in labels:
                 return False
-        elif op == "DoesNotExist":
-            if vals:
-                raise SelectorError("values: Invalid value: values set must be empty for exists and does not exist")
-            if key in labels:
-                return False
-        else:
-            raise SelectorError("%r is not a valid label selector operator" % op)
+        elif key in labels:
+            return False
     return True
 
 

@@ -4,7 +4,7 @@ import ctypes as C
 
 import numpy as np
 
-GEN_NBC, GEN_ODH, GEN_COPY, GEN_STATUS, GEN_CULL, GEN_MUTATE, GEN_GUARD = 0, 1, 2, 3, 4, 5, 6
+GEN_NBC, GEN_ODH, GEN_COPY, GEN_STATUS, GEN_CULL, GEN_MUTATE, GEN_GUARD, GEN_PD = 0, 1, 2, 3, 4, 5, 6, 7
 
 
 def _pack(docs_list):
@@ -88,3 +88,9 @@ class HostPlan:
 
     def restart_guard(self, mutated, updated, old, env=None):
         return self.run(GEN_GUARD, [mutated, updated, old], env, want_result=True)
+
+    def poddefault(self, pods, pds, ranges=None):
+        extra = None
+        if ranges is not None:
+            extra = np.asarray(ranges, dtype=np.uint32).reshape(-1).tobytes()
+        return self.run(GEN_PD, [pods, pds], extra=extra, want_result=True, shared1=True)

@@ -2,7 +2,7 @@
 planners) against the oracle, object by object, on canonical JSON."""
 import json
 
-from oracle import culling, gojson, nbc, odh
+from oracle import culling, gojson, nbc, odh, poddefault
 
 
 def check_nbc_generate(nbs, outs, status, env, flags, owner_api="kubeflow.org/v1beta1"):
@@ -172,3 +172,32 @@ def check_mutate(requests, olds, outs, status, result, image, ca_bundle):
         n_blocked += bool(reason)
         n_ok += 1
     return n_ok, n_denied, n_blocked
+
+
+def check_poddefault(pods, pds, ranges, outs, status, result):
+    """Patches compared by effect: apply(patch, pod) == the oracle's mutated pod."""
+    import collections
+    seen = collections.Counter()
+    for i, pod in enumerate(pods):
+        lst = pds[ranges[i][0]:ranges[i][1]] if ranges is not None else pds
+        allowed, mutated, msg = poddefault.mutate_pod(pod, lst)
+        if not allowed:
+            exp_status = 7 if msg.startswith("conflict") else 9
+            assert status[i] == exp_status and outs[i] == b"", (i, status[i], msg)
+            seen["conflict" if exp_status == 7 else "selector"] += 1
+            continue
+        assert status[i] == 0, (i, status[i])
+        if mutated is None:
+            assert outs[i] == b"", (i, outs[i])
+            seen["none"] += 1
+            continue
+        assert outs[i] != b"", i
+        patch = json.loads(outs[i])
+        got = poddefault.apply_json_patch(pod, patch)
+        assert gojson.canon(got) == gojson.canon(mutated), \
+            "pod %d\n got %s\n exp %s" % (i, gojson.canon(got), gojson.canon(mutated))
+        n_applied = len([k for k in mutated["metadata"]["annotations"]
+                         if k.startswith("poddefault.admission.kubeflow.org/poddefault-")])
+        assert int(result[i]) >= 1
+        seen["patched"] += 1
+    return seen
