@@ -110,8 +110,13 @@ int nbrm_profile_read(nbrm_ctx* ctx, nbrm_profile* out);
 uint64_t nbrm_launch_count(const nbrm_ctx* ctx);
 
 /* ---- resident inputs -------------------------------------------------- */
-/* Copy a batch into input slot 0..2 of the context; it stays in HBM until the
- * slot is overwritten.  Slot meaning is per entry point. */
+/* A context holds NBRM_SLOTS input slots.  The named entry points below use
+ * slots 0..2 as they document; nbrm_run lets a host compose generators over any
+ * slots (e.g. keep the found-object cache and the Pods resident in slots of
+ * their own while requests stream through another). */
+#define NBRM_SLOTS 8
+/* Copy a batch into an input slot of the context; it stays in HBM until the
+ * slot is overwritten. */
 int nbrm_upload(nbrm_ctx* ctx, int slot, const nbrm_docs* docs);
 /* Copy a raw side input (meaning per entry point, e.g. OAuth cookie seeds) to
  * the device; bytes == 0 clears it. */
@@ -275,6 +280,21 @@ int nbrm_odh_mutate_resident(nbrm_ctx* ctx, uint32_t flags, int is_update);
 int nbrm_poddefault_mutate(nbrm_ctx* ctx, const nbrm_docs* pods, const nbrm_docs* poddefaults,
                            const uint32_t* ranges, nbrm_out* out);
 int nbrm_poddefault_mutate_resident(nbrm_ctx* ctx);
+
+/* ---- composing generators --------------------------------------------------
+ * Run one generator on arbitrary slots: tuple i = document i of slot_a (and of
+ * slot_b / slot_c when >= 0).  Generators: 0 notebook-controller objects (3
+ * per Notebook), 1 ODH objects (7), 2 create-or-update decision (slot_a desired,
+ * slot_b found), 3 status (Notebook, StatefulSet, Pod), 4 culling pass
+ * (Notebook, kernels, terminals; arg0/arg1 = idle / period minutes), 5 webhook
+ * mutation (flags NBRM_MUT_*), 6 restart guard (mutated, request, old),
+ * 7 PodDefault admission (Pods, shared PodDefault arena).  use_side_input: pass
+ * the bytes of nbrm_upload_bytes (seeds / pod_exists / ranges).  The result is
+ * read with nbrm_download or moved on with nbrm_result_to_slot. */
+int nbrm_run(nbrm_ctx* ctx, int generator, int slot_a, int slot_b, int slot_c, uint32_t flags,
+             uint64_t now_unix, uint32_t arg0, uint32_t arg1, int use_side_input);
+/* Copy the documents of a slot to host memory (status and result are NULL). */
+int nbrm_download_slot(nbrm_ctx* ctx, int slot, nbrm_out* out);
 
 /* ---- offsets without allocation -----------------------------------------
  * No counterpart in the reference: this entry point exists for embedders, not

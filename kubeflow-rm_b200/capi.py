@@ -10,6 +10,7 @@ GEN_STS, GEN_SVC, GEN_VS, GEN_OWNER_REF, GEN_OWNER_V1 = 1, 2, 4, 8, 16
 GEN_ALL = GEN_STS | GEN_SVC | GEN_VS
 ODH_RBAC = 32
 MUT_CREATE, MUT_CA_BUNDLE = 1, 2
+(G_NBC, G_ODH, G_COPY, G_STATUS, G_CULL, G_MUTATE, G_GUARD, G_PODDEFAULT) = range(8)
 
 STATUS_NAMES = {0: "OK", 1: "E_PARSE", 2: "E_NO_CONTAINERS", 3: "E_SEGS", 4: "E_PORTS_EMPTY",
                 5: "E_NIL_REPLICAS", 6: "E_DENIED", 7: "E_CONFLICT", 8: "E_LIMIT", 9: "E_SELECTOR"}
@@ -105,6 +106,9 @@ def load_library():
     lib.nbrm_poddefault_mutate.argtypes = [C.c_void_p, C.POINTER(_Docs), C.POINTER(_Docs), C.c_void_p,
                                            C.POINTER(_Out)]
     lib.nbrm_poddefault_mutate_resident.argtypes = [C.c_void_p]
+    lib.nbrm_run.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint32, C.c_uint64,
+                             C.c_uint32, C.c_uint32, C.c_int]
+    lib.nbrm_download_slot.argtypes = [C.c_void_p, C.c_int, C.POINTER(_Out)]
     lib.nbrm_scan_lengths_noalloc.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p,
                                               C.c_char_p, C.c_size_t]
     _lib = lib
@@ -172,9 +176,9 @@ class Result:
         total = int(off[n]) if n else 0
         data = np.frombuffer((C.c_uint8 * max(total, 1)).from_address(out.data), dtype=np.uint8,
                              count=total)
-        ns = int(out.n_status)
+        ns = int(out.n_status) if out.status else 0
         st = np.frombuffer((C.c_uint32 * max(ns, 1)).from_address(out.status), dtype=np.uint32,
-                           count=ns)
+                           count=ns) if out.status else np.zeros(0, dtype=np.uint32)
         rs = np.frombuffer((C.c_uint32 * max(ns, 1)).from_address(out.result), dtype=np.uint32,
                            count=ns) if out.result else np.zeros(ns, dtype=np.uint32)
         self.result = rs.copy() if copy else rs
@@ -330,3 +334,12 @@ class Context:
 
     def poddefault_mutate_resident(self):
         self._check(self.lib.nbrm_poddefault_mutate_resident(self.h))
+
+    # --- composing generators over arbitrary slots
+    def run(self, gen, a, b=-1, c=-1, flags=0, now=0, arg0=0, arg1=0, side=False):
+        self._check(self.lib.nbrm_run(self.h, gen, a, b, c, flags, now, arg0, arg1, 1 if side else 0))
+
+    def download_slot(self, slot, copy=True):
+        o = _Out()
+        self._check(self.lib.nbrm_download_slot(self.h, slot, C.byref(o)))
+        return Result(o, copy)

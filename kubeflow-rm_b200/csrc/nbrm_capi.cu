@@ -84,7 +84,7 @@ struct nbrm_ctx {
   DevBuf pool;
   EnvLits env;
 
-  Slot slot[3];
+  Slot slot[NBRM_SLOTS];
   DevBuf segs, nseg, lens, status, result, aux, out_off, scan_tmp, out, extra;
   uint64_t extra_bytes = 0;
   PinBuf h_out, h_off, h_status, h_result, h_total;
@@ -306,7 +306,7 @@ uint64_t nbrm_launch_count(const nbrm_ctx* c) { return c ? c->launches : 0; }
 
 int nbrm_upload(nbrm_ctx* c, int slot, const nbrm_docs* d) {
   if (!c) return -2;
-  if (slot < 0 || slot > 2) return fail_msg(c, "nbrm_upload: slot must be 0..2");
+  if (slot < 0 || slot >= NBRM_SLOTS) return fail_msg(c, "nbrm_upload: slot out of range");
   if (int r = check_docs(c, d)) return r;
   CK(cudaSetDevice(c->device));
   Slot& s = c->slot[slot];
@@ -506,7 +506,7 @@ int nbrm_odh_generate(nbrm_ctx* c, const nbrm_docs* notebooks, const uint8_t* se
 
 int nbrm_result_to_slot(nbrm_ctx* c, int slot) {
   if (!c) return -2;
-  if (slot < 0 || slot > 2) return fail_msg(c, "nbrm_result_to_slot: slot must be 0..2");
+  if (slot < 0 || slot >= NBRM_SLOTS) return fail_msg(c, "nbrm_result_to_slot: slot out of range");
   if (!c->res_valid) return fail_msg(c, "nbrm_result_to_slot: no result on this context");
   Slot& s = c->slot[slot];
   std::swap(s.data, c->out);
@@ -623,6 +623,40 @@ int nbrm_poddefault_mutate(nbrm_ctx* c, const nbrm_docs* pods, const nbrm_docs* 
   if (int r = nbrm_upload_bytes(c, ranges, ranges ? pods->n * 8 : 0)) return r;
   if (int r = nbrm_poddefault_mutate_resident(c)) return r;
   return nbrm_download(c, out);
+}
+
+int nbrm_run(nbrm_ctx* c, int generator, int slot_a, int slot_b, int slot_c, uint32_t flags,
+             uint64_t now_unix, uint32_t arg0, uint32_t arg1, int use_side_input) {
+  if (!c) return -2;
+  uint32_t nobj = 0, cap = 0;
+  gen_shape(generator, &nobj, &cap);
+  if (!nobj) return fail_msg(c, "nbrm_run: unknown generator");
+  const int map[3] = {slot_a, slot_b, slot_c};
+  for (int k = 0; k < 3; ++k)
+    if (map[k] >= NBRM_SLOTS) return fail_msg(c, "nbrm_run: slot out of range");
+  if (slot_a < 0) return fail_msg(c, "nbrm_run: the first input slot is required");
+  return run_generator(c, generator, map, flags, use_side_input && c->extra_bytes ? c->extra.p : nullptr,
+                       now_unix, arg0, arg1);
+}
+
+int nbrm_download_slot(nbrm_ctx* c, int slot, nbrm_out* out) {
+  if (!c || !out) return -2;
+  if (slot < 0 || slot >= NBRM_SLOTS) return fail_msg(c, "nbrm_download_slot: slot out of range");
+  Slot& s = c->slot[slot];
+  if (!s.off.p) return fail_msg(c, "nbrm_download_slot: the slot is empty");
+  CK(cudaSetDevice(c->device));
+  CK(c->h_out.reserve(s.bytes + 16));
+  CK(c->h_off.reserve(((size_t)s.n + 1) * 8));
+  if (s.bytes) CK(cudaMemcpyAsync(c->h_out.p, s.data.p, s.bytes, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaMemcpyAsync(c->h_off.p, s.off.p, ((size_t)s.n + 1) * 8, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  out->data = reinterpret_cast<const char*>(c->h_out.p);
+  out->off = reinterpret_cast<const uint64_t*>(c->h_off.p);
+  out->n = s.n;
+  out->status = nullptr;
+  out->n_status = 0;
+  out->result = nullptr;
+  return 0;
 }
 
 }  // extern "C"
