@@ -1,21 +1,23 @@
 #!/usr/bin/env python
 """bench.py — Notebook reconciles/sec on B200 (BASELINE.json metric).
 
-A "step" is one pass of the GPU reconcile-generation path over one batch of
-synthetic Notebook CRs: for every Notebook, everything the reference's
-reconcilers compute for it that libnbrm implements (see STAGES below).  One
-Notebook processed = one reconcile.
+A "step" is one full reconcile pass over one batch of synthetic Notebooks of
+BASELINE.json configs[1] (the ODH OAuth Notebook fixture): for every Notebook,
+all the pure work the reference does between admission and the end of both
+controllers' Reconcile calls (STAGES below; kubeflow-rm_b200/reconcile.py),
+against a steady-state cluster (found objects and Pods resident in HBM, as the
+reference keeps them in its informer cache).  One Notebook = one reconcile.
 
-  value  reconciles/s with the batch already resident in HBM (kernels only)
+  value  reconciles/s with the requests already resident in HBM (kernels only)
   e2e    reconciles/s through the C ABI with HOST buffers: pinned host ->
-         device copy of the batch, kernels, device -> host copy of every
-         generated object, all inside the timed region
+         device copy of the requests, kernels, device -> host copy of every
+         result (mutated Notebooks, ODH objects, writes, statuses), all timed
   --impl reference  the oracle (CPU restatement of the reference; the Go
          reference cannot be built here) on all host cores, same workload
 
-Workload: BASELINE.json configs[1] (the ODH OAuth Notebook fixture, 100 per
-namespace), replicated to --batch Notebooks per GPU so that the batch is larger
-than the 126 MB L2; the literal 100-Notebook case is reported as latency in
+The batch is --batch Notebooks per GPU (default 131 072: 90 MB of requests in,
+about 0.9 GB of objects out per step, both larger than the 126 MB L2); the
+literal 100-Notebook case of configs[1] is reported as latency in
 `config.literal_100`.
 """
 import argparse
@@ -34,8 +36,14 @@ METRIC = "Notebook reconciles/sec"
 UNIT = "reconciles/s"
 ENV = {"USE_ISTIO": "true", "ISTIO_GATEWAY": "kubeflow/kubeflow-gateway", "ISTIO_HOST": "*",
        "CLUSTER_DOMAIN": "cluster.local"}
-STAGES = ["generateStatefulSet", "generateService", "generateVirtualService",
-          "SetControllerReference"]
+ENV["CONTROLLER_NAMESPACE"] = "redhat-ods-applications"
+NOW = 1793966400   # 2026-11-06T12:00:00Z, the injected clock
+WORKLOAD = ("configs[1] odh-notebook-controller: OAuth Notebook fixture (100 per namespace) through webhook, "
+            "ODH reconcile and notebook-controller reconcile, steady-state cluster")
+STAGES = ["NotebookWebhook.Handle(CREATE): lock + OAuth sidecar",
+          "ODH desired objects: NetworkPolicies, Route, ServiceAccount, Service, Secret",
+          "generateStatefulSet/Service/VirtualService + SetControllerReference",
+          "Copy*Fields create-or-update decision vs found objects", "createNotebookStatus"]
 
 
 def parse_args():
@@ -44,8 +52,8 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--batch", type=int, default=262144, help="Notebooks per GPU per step")
-    ap.add_argument("--ref-sample", type=int, default=20000,
+    ap.add_argument("--batch", type=int, default=131072, help="Notebooks per GPU per step")
+    ap.add_argument("--ref-sample", type=int, default=8000,
                     help="Notebooks per step of the CPU reference arm")
     return ap.parse_args()
 
@@ -99,41 +107,89 @@ class ClockSampler(threading.Thread):
                 "samples": len(self.samples)}
 
 
-def oracle_reconcile(nb):
-    """One reconcile's worth of pure work in the oracle (same STAGES)."""
-    from oracle import nbc
-    out = [nbc.generate_statefulset(nb, ENV), nbc.generate_service(nb, ENV),
-           nbc.generate_virtualservice(nb, ENV)]
-    for o in out:
-        nbc.set_controller_reference(nb, o)
-    return out
-
-
-def _oracle_chunk(docs):
-    """Worker: parse the Notebook JSON, run the oracle, serialise the objects
-    (the same bytes-in, bytes-out contract as the C ABI)."""
+def _oracle_chunk(items):
+    """Worker: parse the request and its cluster state, run the oracle's full pass,
+    serialise every result (the same bytes-in, bytes-out contract as the C ABI)."""
+    from oracle import gojson, odh, passes
+    now_str = gojson.format_rfc3339(NOW * 10**9)
     n = 0
-    for d in docs:
-        nb = json.loads(d)
-        for o in oracle_reconcile(nb):
+    for req, found, pod, seed in items:
+        r = json.loads(req)
+        f = [json.loads(x) if x else None for x in found]
+        p = json.loads(pod) if pod else None
+        mutated, objs, writes, status = passes.full_pass(r, f, f[0], p, ENV, now_str,
+                                                         odh.cookie_secret_from_seed(seed))
+        for o in [mutated, status] + [x for x in objs if x is not None] + [x for x in writes if x is not None]:
             n += len(json.dumps(o, separators=(",", ":")))
     return n
 
 
-def cpu_baseline(docs, procs):
-    """Oracle timed on host cores over `docs`; returns reconciles/s."""
+def cpu_baseline(items, procs):
+    """Oracle timed on host cores over `items`; returns reconciles/s."""
     if procs <= 1:
         t0 = time.perf_counter()
-        _oracle_chunk(docs)
-        return len(docs) / (time.perf_counter() - t0)
+        _oracle_chunk(items)
+        return len(items) / (time.perf_counter() - t0)
     import multiprocessing as mp
-    chunks = [docs[i::procs] for i in range(procs)]
+    chunks = [items[i::procs] for i in range(procs)]
     with mp.get_context("fork").Pool(procs) as pool:
         pool.map(_oracle_chunk, [c[:8] for c in chunks])  # start the workers
         t0 = time.perf_counter()
         pool.map(_oracle_chunk, chunks)
         dt = time.perf_counter() - t0
-    return len(docs) / dt
+    return len(items) / dt
+
+
+def build_workload(wl, pkg, n, start, need_items, need_docs=True):
+    """configs[1] x n: OAuth Notebook requests plus the steady-state cluster around
+    them (found objects as generated, a running Pod per Notebook).  The found objects
+    come from the oracle for the first Notebook and are re-keyed by text substitution
+    (every C2 Notebook has the same shape), so building 262 144 of them stays cheap."""
+    import random
+    from oracle import nbc, odh
+    rng = random.Random(wl.SEED + start)
+    t_nb = wl.notebook_c2(0)
+    mutated, _ = odh.mutate_notebook(t_nb, "CREATE")
+    desired = [nbc.generate_statefulset(mutated, ENV), nbc.generate_service(mutated, ENV),
+               nbc.generate_virtualservice(mutated, ENV)]
+    for d in desired:
+        nbc.set_controller_reference(mutated, d)
+        d["metadata"]["resourceVersion"] = "7"
+    desired[0]["status"] = {"replicas": 1, "readyReplicas": 1}
+    pod = {"apiVersion": "v1", "kind": "Pod",
+           "metadata": {"name": "nb-000000-0", "namespace": "ns-000", "labels": {"notebook-name": "nb-000000"}},
+           "status": {"phase": "Running",
+                      "conditions": [{"type": t, "status": "True", "lastProbeTime": None,
+                                      "lastTransitionTime": "2026-11-06T11:00:00Z"}
+                                     for t in ("Initialized", "Ready", "ContainersReady", "PodScheduled")],
+                      "containerStatuses": [{"name": "nb-000000", "ready": True, "restartCount": 0,
+                                             "state": {"running": {"startedAt": "2026-11-06T11:00:05Z"}}},
+                                            {"name": "oauth-proxy", "ready": True, "restartCount": 0,
+                                             "state": {"running": {"startedAt": "2026-11-06T11:00:06Z"}}}]}}
+    t_req = wl.dumps(t_nb)
+    t_found = [wl.dumps(d) for d in desired]
+    t_pod = wl.dumps(pod)
+    uid0 = t_nb["metadata"]["uid"].encode()
+
+    def rekey(b, i):
+        md = wl._meta(i)
+        return (b.replace(b"nb-000000", md["name"].encode()).replace(b"ns-000", md["namespace"].encode())
+                .replace(uid0, md["uid"].encode()).replace(b'"resourceVersion":"1000"', b'"resourceVersion":"%d"' % (1000 + i)))
+    reqs, found, stss, pods, items = [], [], [], [], []
+    seeds = rng.randbytes(16 * n)
+    for k in range(n):
+        i = start + k
+        r = rekey(t_req, i)
+        f = [rekey(x, i) for x in t_found]
+        p = rekey(t_pod, i)
+        if need_docs:
+            reqs.append(r)
+            found += f
+            stss.append(f[0])
+            pods.append(p)
+        if need_items and k < need_items:
+            items.append((r, f, p, seeds[16 * k:16 * k + 16]))
+    return reqs, found, stss, pods, seeds, items
 
 
 def run_reference(args):
@@ -141,29 +197,28 @@ def run_reference(args):
     if int(os.environ.get("RANK", "0")) != 0:
         return
     import __graft_entry__ as graft
-    graft.load_pkg()
+    pkg = graft.load_pkg()
     import importlib
     wl = importlib.import_module(graft.PKG_NAME + ".workload")
     cores = os.cpu_count() or 1
     n = args.ref_sample
-    docs = [wl.dumps(nb) for nb in wl.corpus("c2", n)]
+    items = build_workload(wl, pkg, n, 0, n, need_docs=False)[5]
     for _ in range(min(args.warmup, 1)):
-        cpu_baseline(docs[: max(n // 10, 1)], cores)
+        cpu_baseline(items[: max(n // 10, 1)], cores)
     times = []
     for _ in range(args.steps):
         t0 = time.perf_counter()
-        cpu_baseline(docs, cores)
+        cpu_baseline(items, cores)
         times.append(time.perf_counter() - t0)
     dt = sum(times)
     v = n * args.steps / dt
-    sample = "%d Notebooks/step (C2 OAuth fixture), JSON in -> oracle -> JSON out, %d processes" % (n, cores)
+    sample = "%d Notebooks/step (configs[1] fixture + steady-state cluster), JSON in -> oracle full pass -> JSON out, %d processes" % (n, cores)
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
         "data": "synthetic",
-        "config": {"workload": "configs[1] odh-notebook-controller OAuth Notebook fixture", "stages": STAGES,
-                   "batch_notebooks": n},
+        "config": {"workload": WORKLOAD, "stages": STAGES, "batch_notebooks": n},
         "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
@@ -179,6 +234,7 @@ def main():
     pkg = graft.load_pkg()
     import importlib
     wl = importlib.import_module(graft.PKG_NAME + ".workload")
+    rmod = importlib.import_module(graft.PKG_NAME + ".reconcile")
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -201,18 +257,20 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    flags = pkg.GEN_ALL | pkg.GEN_OWNER_REF
     B = args.batch
-    # weak scaling: every rank gets its own B Notebooks (independent keys, no collective)
-    nbs = wl.corpus("c2", B, start=rank * B)
-    raw = [wl.dumps(nb) for nb in nbs]
-    docs = pkg.Docs(raw, pinned=True)
+    # weak scaling: every rank reconciles its own B Notebooks (independent keys, no collective)
+    cb_n = 1500
+    reqs, found, stss, pods, seeds, items = build_workload(wl, pkg, B, rank * B, cb_n if rank == 0 else 0)
+    d_req = pkg.Docs(reqs, pinned=True)
     ctx = pkg.Context(local, env=ENV)
+    rp = rmod.ReconcilePass(ctx, NOW)
+    rp.set_cluster_state(pkg.Docs(found), pkg.Docs(stss), pkg.Docs(pods))
+    del found, stss, pods
 
-    # ---- value: inputs resident in HBM, kernels only
-    ctx.upload(0, docs)
+    # ---- value: requests and cluster state resident in HBM, kernels only
+    rp.upload_requests(d_req, seeds)
     for _ in range(args.warmup):
-        ctx.nbc_generate_resident(flags)
+        rp.run_resident()
     ctx.sync()
     ctx.profile_enable(True)
     sampler = ClockSampler(local)
@@ -221,7 +279,7 @@ def main():
     barrier()
     ctx.timer_start()
     for _ in range(args.steps):
-        ctx.nbc_generate_resident(flags)
+        rp.run_resident()
     ms = ctx.timer_stop()
     barrier()
     launches = ctx.launch_count() - l0
@@ -232,36 +290,39 @@ def main():
 
     # ---- e2e: host buffers through the C ABI, copies inside the timed region
     for _ in range(args.warmup):
-        res = ctx.nbc_generate(docs, flags, copy=False)
+        out = rp.run(d_req, seeds, copy=False)
     barrier()
     ctx.timer_start()
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        res = ctx.nbc_generate(docs, flags, copy=False)
+        out = rp.run(d_req, seeds, copy=False)
     ms_e2e_dev = ctx.timer_stop()
     ms_e2e = 1e3 * (time.perf_counter() - t0)
     barrier()
     clocks = sampler.result()
     ms_e2e = max_over_ranks(max(ms_e2e, ms_e2e_dev))
     e2e_value = world * B * args.steps / (ms_e2e / 1e3)
-    h2d = docs.nbytes + docs.off.nbytes
-    d2h = int(res.off[-1]) + res.off.nbytes + res.status.nbytes
-    assert int(res.status.sum()) == 0
+    h2d = d_req.nbytes + d_req.off.nbytes + len(seeds)
+    d2h = sum(out[k] for k in ("notebooks_bytes", "odh_bytes", "writes_bytes", "status_bytes")) \
+        + 8 * (B + 1) + 8 * (7 * B + 1) + 8 * (3 * B + 1) + 8 * (B + 1) + 4 * 2 * 6 * B
+    assert out["writes_bytes"] == 0, "steady state expected: nothing to create or update"
 
-    # ---- roofline of the dominant kernel (events inside the value loop)
+    # ---- roofline of the dominant kernel (CUDA events inside the value loop, per generator)
     peak, peak_kind = load_peaks()
-    # one plan launch and one emit_objects launch per step (emit_big_objects, launched with
-    # it, finds nothing to do on this workload and is counted in the same bracket)
-    emit_bytes = (prof.emit_bytes_read + prof.emit_bytes_written) / args.steps
-    plan_bytes = prof.plan_bytes_read / args.steps
-    kern = {"emit_objects": (prof.emit_ms / args.steps, emit_bytes),
-            "plan_kernel<GenNbc>": (prof.plan_ms / args.steps, plan_bytes)}
+    names = ["nbc", "odh", "copy_fields", "status", "cull", "mutate", "guard", "poddefault"]
+    kern = {}
+    for g, nm in enumerate(names):
+        if prof.runs_gen[g]:
+            kern["plan_kernel<%s>" % nm] = (prof.plan_ms_gen[g] / args.steps, prof.plan_bytes_gen[g] / args.steps)
+            kern["emit_objects[%s]" % nm] = (prof.emit_ms_gen[g] / args.steps, prof.emit_bytes_gen[g] / args.steps)
     dom = max(kern, key=lambda k: kern[k][0])
     dom_ms, dom_bytes = kern[dom]
     achieved = dom_bytes / (dom_ms / 1e3) / 1e9 if dom_ms > 0 else 0.0
     roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": None, "peak_kind": peak_kind,
                 "avg_launch_ms": dom_ms, "algorithmic_bytes_per_launch": dom_bytes,
+                "all_kernels": {k: {"ms": round(v[0], 4), "GBps": round(v[1] / (v[0] / 1e3) / 1e9, 1) if v[0] else 0}
+                                for k, v in kern.items()},
                 "kernels_ms_per_step": {"plan": prof.plan_ms / args.steps, "scan": prof.scan_ms / args.steps,
                                         "emit": prof.emit_ms / args.steps}}
 
@@ -270,36 +331,36 @@ def main():
             dist.destroy_process_group()
         return
 
-    # literal configs[1]: 100 Notebooks, latency through the C ABI
-    small = pkg.Docs(raw[:100], pinned=True)
+    # literal configs[1]: 100 Notebooks, latency of one full pass through the C ABI
+    small = pkg.Docs(reqs[:100], pinned=True)
+    rp.set_cluster_state(*[pkg.Docs(x) for x in build_workload(wl, pkg, 100, 0, 0)[1:4]])
     for _ in range(5):
-        ctx.nbc_generate(small, flags, copy=False)
+        rp.run(small, seeds[:1600], copy=False)
     lat = []
     for _ in range(50):
         t0 = time.perf_counter()
-        ctx.nbc_generate(small, flags, copy=False)
+        rp.run(small, seeds[:1600], copy=False)
         lat.append(1e3 * (time.perf_counter() - t0))
     lat.sort()
 
     # CPU baseline: the oracle, one core, bounded sample
-    cb_n = 4000
-    cb = cpu_baseline(raw[:cb_n], 1)
+    cb = cpu_baseline(items, 1)
 
     print(json.dumps({
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": "configs[1] odh-notebook-controller OAuth Notebook fixture x %d per GPU "
-                               "(100 per namespace)" % B,
-                   "stages": STAGES, "batch_notebooks": B, "l2": "batch larger than L2 (in %.0f MB, out %.0f MB)"
-                   % (docs.nbytes / 1e6, int(res.off[-1]) / 1e6),
+        "config": {"workload": WORKLOAD + " x %d per GPU" % B,
+                   "stages": STAGES, "batch_notebooks": B,
+                   "l2": "per step in %.0f MB (requests) + %.0f MB resident cluster state, out %.0f MB: larger than L2"
+                   % (d_req.nbytes / 1e6, 0.0, (d2h) / 1e6),
                    "literal_100": {"p50_ms": lat[len(lat) // 2], "p99_ms": lat[-1],
                                    "reconciles_per_s": 100 / (lat[len(lat) // 2] / 1e3)}},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": ms_e2e / args.steps},
         "gpu_launches": launches, "clocks": clocks, "roofline": roofline,
         "cpu_baseline": {"value": cb, "unit": UNIT, "cores": 1, "kind": "port",
-                         "sample": "%d Notebooks of the same workload, JSON in -> oracle -> JSON out" % cb_n},
+                         "sample": "%d Notebooks of the same workload, JSON in -> oracle full pass -> JSON out" % len(items)},
     }))
     ctx.close()
     if dist is not None:

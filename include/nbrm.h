@@ -88,6 +88,10 @@ typedef struct nbrm_profile {
   uint64_t plan_launches, scan_launches, emit_launches;
   uint64_t emit_bytes_read, emit_bytes_written; /* algorithmic bytes of the emit kernel */
   uint64_t plan_bytes_read;                     /* input bytes the plan kernels walked */
+  /* the same per generator id (see nbrm_run): device ms, algorithmic bytes (plan: input
+   * bytes read; emit: output bytes read + written), number of runs */
+  double plan_ms_gen[8], emit_ms_gen[8];
+  uint64_t plan_bytes_gen[8], emit_bytes_gen[8], runs_gen[8];
 } nbrm_profile;
 
 /* ---- context ---------------------------------------------------------- */

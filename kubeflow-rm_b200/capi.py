@@ -39,7 +39,10 @@ class Profile(C.Structure):
     _fields_ = [("plan_ms", C.c_double), ("scan_ms", C.c_double), ("emit_ms", C.c_double),
                 ("plan_launches", C.c_uint64), ("scan_launches", C.c_uint64),
                 ("emit_launches", C.c_uint64), ("emit_bytes_read", C.c_uint64),
-                ("emit_bytes_written", C.c_uint64), ("plan_bytes_read", C.c_uint64)]
+                ("emit_bytes_written", C.c_uint64), ("plan_bytes_read", C.c_uint64),
+                ("plan_ms_gen", C.c_double * 8), ("emit_ms_gen", C.c_double * 8),
+                ("plan_bytes_gen", C.c_uint64 * 8), ("emit_bytes_gen", C.c_uint64 * 8),
+                ("runs_gen", C.c_uint64 * 8)]
 
 
 # reference process environment (nbrm_env) key -> struct field

@@ -68,6 +68,7 @@ enum KClass { K_PLAN = 0, K_SCAN = 1, K_EMIT = 2, K_COUNT = 3 };
 
 struct PendingEvent {
   int cls;
+  int gen;
   cudaEvent_t a, b;
 };
 
@@ -136,10 +137,11 @@ struct KScope {  // brackets one kernel class with events when profiling is on
   nbrm_ctx* c;
   PendingEvent pe;
   bool on;
-  KScope(nbrm_ctx* c_, int cls, uint32_t n_launches) : c(c_), on(c_->prof) {
+  KScope(nbrm_ctx* c_, int cls, uint32_t n_launches, int gen = 0) : c(c_), on(c_->prof) {
     c->launches += n_launches;
     if (!on) return;
     pe.cls = cls;
+    pe.gen = gen & 7;
     pe.a = get_event(c);
     pe.b = get_event(c);
     cudaEventRecord(pe.a, c->stream);
@@ -160,9 +162,15 @@ int drain_profile(nbrm_ctx* c) {
   for (auto& pe : c->pending) {
     float ms = 0;
     cudaEventElapsedTime(&ms, pe.a, pe.b);
-    if (pe.cls == K_PLAN) c->acc.plan_ms += ms;
+    if (pe.cls == K_PLAN) {
+      c->acc.plan_ms += ms;
+      c->acc.plan_ms_gen[pe.gen] += ms;
+    }
     if (pe.cls == K_SCAN) c->acc.scan_ms += ms;
-    if (pe.cls == K_EMIT) c->acc.emit_ms += ms;
+    if (pe.cls == K_EMIT) {
+      c->acc.emit_ms += ms;
+      c->acc.emit_ms_gen[pe.gen] += ms;
+    }
     c->free_events.push_back(pe.a);
     c->free_events.push_back(pe.b);
   }
@@ -389,7 +397,7 @@ int run_generator(nbrm_ctx* c, int gen, const int (&map)[3], uint32_t flags, con
   po.aux = c->aux.as<char>();
   po.cap = cap;
   {
-    KScope k(c, K_PLAN, n ? 1 : 0);
+    KScope k(c, K_PLAN, n ? 1 : 0, gen);
     launch_plan(gen, in, po, in_bytes, c->stream);
   }
   CK(cudaGetLastError());
@@ -411,7 +419,7 @@ int run_generator(nbrm_ctx* c, int gen, const int (&map)[3], uint32_t flags, con
   b.p[SRC_POOL] = c->pool.as<char>();
   b.p[SRC_AUX] = c->aux.as<char>();
   {
-    KScope k(c, K_EMIT, n_out ? 2 : 0);
+    KScope k(c, K_EMIT, n_out ? 2 : 0, gen);
     launch_emit(po.segs, po.nseg, po.lens, c->out_off.as<uint64_t>(), n_out, cap, nobj, b,
                 c->out.as<char>(), c->sm_count, c->stream);
   }
@@ -420,6 +428,9 @@ int run_generator(nbrm_ctx* c, int gen, const int (&map)[3], uint32_t flags, con
     c->acc.emit_bytes_read += total;
     c->acc.emit_bytes_written += total;
     c->acc.plan_bytes_read += in_bytes;
+    c->acc.plan_bytes_gen[gen & 7] += in_bytes;
+    c->acc.emit_bytes_gen[gen & 7] += 2 * total;
+    c->acc.runs_gen[gen & 7] += 1;
   }
   c->res_n_in = n;
   c->res_n_out = n_out;

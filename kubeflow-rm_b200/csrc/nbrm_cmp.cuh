@@ -139,6 +139,7 @@ static const int EQ_MAX_DEPTH = 24;
 struct EqFrame {
   uint32_t ai, aend;  // cursor in A's container
   uint32_t bi, bend;  // cursor in B's array (arrays) / B's object span (objects)
+  uint32_t bc;        // objects: cursor in B for the "same order" fast path
   uint32_t is_obj;
 };
 
@@ -147,6 +148,7 @@ template <bool SEM>
 NB_HD bool json_equal_t(const Doc& a, Span x, const Doc& b, Span y) {
   const bool xn = member_is_nil<SEM>(a, x), yn = member_is_nil<SEM>(b, y);
   if (xn || yn) return xn && yn;
+  if (spans_eq(a, x, b, y)) return true;  // same text: the common steady-state case, one linear pass
   EqFrame st[EQ_MAX_DEPTH];
   int sp = 0;
   // compare one pair of values; containers are pushed
@@ -164,6 +166,7 @@ NB_HD bool json_equal_t(const Doc& a, Span x, const Doc& b, Span y) {
         st[sp].aend = cx.end() - 1;
         st[sp].bi = cy.off;
         st[sp].bend = cy.end();
+        st[sp].bc = cy.off + 1;
         st[sp].is_obj = 1;
         ++sp;
       } else if (ta == '[') {
@@ -198,7 +201,20 @@ NB_HD bool json_equal_t(const Doc& a, Span x, const Doc& b, Span y) {
         --sp;
         continue;
       }
-      Span bv = find_key(b, mk(f.bi, f.bend - f.bi), a, m.key);
+      // objects written by the same encoder list their members in the same order:
+      // try B's next member before searching B for the key
+      Span bv = mk(0, 0);
+      {
+        ObjIter ib(b, mk(0, 0));
+        ib.i = f.bc;
+        ib.end = f.bend - 1;
+        Member bm;
+        if (ib.next(b, bm) && str_equal(b, bm.key, a, m.key)) {
+          bv = bm.val;
+          f.bc = ib.i;
+        }
+      }
+      if (!bv.ok()) bv = find_key(b, mk(f.bi, f.bend - f.bi), a, m.key);
       if (member_is_nil<SEM>(b, bv)) return false;
       cx = m.val;
       cy = bv;
@@ -250,21 +266,88 @@ NB_HD bool map_field_differs(const Doc& from, Span fmap, const Doc& to, Span tma
   return false;
 }
 
+// Spans of an owned object, found in one descent through the document.
 struct ObjView {
-  Span root, meta, labels, annotations, spec;
+  Span root, kind, meta, labels, annotations, spec;
+  Span replicas, tmpl, tmeta, tlabels, tpod;  // StatefulSet: spec.replicas, spec.template.{metadata{labels},spec}
+  Span selector, ports;                       // Service: spec.selector, spec.ports
 };
 
 NB_HD ObjView view_object(const Doc& d) {
   ObjView v;
-  v.root = root(d);
-  v.meta = FIND(d, v.root, "metadata");
-  v.labels = FIND(d, v.meta, "labels");
-  v.annotations = FIND(d, v.meta, "annotations");
-  v.spec = FIND(d, v.root, "spec");
+  v.root = v.kind = v.meta = v.labels = v.annotations = v.spec = mk(0, 0);
+  v.replicas = v.tmpl = v.tmeta = v.tlabels = v.tpod = v.selector = v.ports = mk(0, 0);
+  Cursor c;
+  c.i = skip_ws(d, 0);
+  const uint32_t rs = c.i;
+  if (!obj_enter(d, c)) return v;
+  Member m;
+  while (obj_key(d, c, m)) {
+    if (KEY_IS(d, m, "kind")) {
+      v.kind = val_skip(d, c);
+    } else if (KEY_IS(d, m, "metadata")) {
+      const uint32_t s0 = c.i;
+      if (!obj_enter(d, c)) {
+        val_skip(d, c);
+        continue;
+      }
+      Member mm;
+      while (obj_key(d, c, mm)) {
+        const Span val = val_skip(d, c);
+        if (KEY_IS(d, mm, "labels")) v.labels = val;
+        else if (KEY_IS(d, mm, "annotations")) v.annotations = val;
+      }
+      v.meta = mk(s0, c.i - s0);
+    } else if (KEY_IS(d, m, "spec")) {
+      const uint32_t s0 = c.i;
+      if (!obj_enter(d, c)) {
+        v.spec = val_skip(d, c);
+        continue;
+      }
+      Member sm;
+      while (obj_key(d, c, sm)) {
+        if (KEY_IS(d, sm, "template")) {
+          const uint32_t t0 = c.i;
+          if (!obj_enter(d, c)) {
+            v.tmpl = val_skip(d, c);
+            continue;
+          }
+          Member tm;
+          while (obj_key(d, c, tm)) {
+            if (KEY_IS(d, tm, "metadata")) {
+              const uint32_t m0 = c.i;
+              if (!obj_enter(d, c)) {
+                v.tmeta = val_skip(d, c);
+                continue;
+              }
+              Member lm;
+              while (obj_key(d, c, lm)) {
+                const Span val = val_skip(d, c);
+                if (KEY_IS(d, lm, "labels")) v.tlabels = val;
+              }
+              v.tmeta = mk(m0, c.i - m0);
+            } else {
+              const Span val = val_skip(d, c);
+              if (KEY_IS(d, tm, "spec")) v.tpod = val;
+            }
+          }
+          v.tmpl = mk(t0, c.i - t0);
+        } else {
+          const Span val = val_skip(d, c);
+          if (KEY_IS(d, sm, "replicas")) v.replicas = val;
+          else if (KEY_IS(d, sm, "selector")) v.selector = val;
+          else if (KEY_IS(d, sm, "ports")) v.ports = val;
+        }
+      }
+      v.spec = mk(s0, c.i - s0);
+    } else {
+      val_skip(d, c);
+    }
+  }
+  v.root = mk(rs, c.i - rs);
   return v;
 }
 
-// "metadata":{...to's members without labels/annotations..., from's labels/annotations}
 NB_HD void plan_merged_metadata(Planner& P, const Doc& from, const ObjView& fv, const Doc& to,
                                 const ObjView& tv, const Member& meta_member) {
   P.in(mk(meta_member.key.off, meta_member.val.off - meta_member.key.off), 1);  // "metadata":
@@ -296,7 +379,7 @@ NB_HD bool kind_is(const Doc& d, Span rootv, const char (&k)[N]) {
 
 // The planner for one (desired, found) pair.
 NB_HD void plan_copy_fields(Planner& P, const Doc& from, const Doc& to) {
-  if (to.n == 0 || !is_object(to, root(to))) {  // NotFound -> Create(desired)
+  if (to.n == 0 || to.at(skip_ws(to, 0)) != '{') {  // NotFound -> Create(desired)
     P.in(root(from), 0);
     return;
   }
@@ -308,7 +391,7 @@ NB_HD void plan_copy_fields(Planner& P, const Doc& from, const Doc& to) {
   bool require = map_field_differs(from, fv.labels, to, tv.labels);        // util.go:109-113
   require |= map_field_differs(from, fv.annotations, to, tv.annotations);  // :116-120
 
-  if (kind_is(from, fv.root, "VirtualService")) {  // CopyVirtualService, util.go:199-219
+  if (str_eq(from, fv.kind, "VirtualService")) {  // CopyVirtualService, util.go:199-219
     if (!is_object(from, fv.spec)) return;         // :200-206 from has no spec map: false
     bool upd = !is_object(to, tv.spec) || !json_equal(from, fv.spec, to, tv.spec);
     if (!upd) return;
@@ -327,9 +410,9 @@ NB_HD void plan_copy_fields(Planner& P, const Doc& from, const Doc& to) {
     return;
   }
 
-  if (kind_is(from, fv.root, "Service")) {  // CopyServiceFields, util.go:166-195
-    Span fsel = FIND(from, fv.spec, "selector"), fports = FIND(from, fv.spec, "ports");
-    Span tsel = FIND(to, tv.spec, "selector"), tports = FIND(to, tv.spec, "ports");
+  if (str_eq(from, fv.kind, "Service")) {  // CopyServiceFields, util.go:166-195
+    Span fsel = fv.selector, fports = fv.ports;
+    Span tsel = tv.selector, tports = tv.ports;
     if (!json_equal(from, fsel, to, tsel)) require = true;      // :184
     if (!json_equal(from, fports, to, tports)) require = true;  // :189
     if (!require) return;
@@ -391,15 +474,14 @@ NB_HD void plan_copy_fields(Planner& P, const Doc& from, const Doc& to) {
   }
 
   // StatefulSet: notebook_controller.go:165-169 then CopyStatefulSetFields, util.go:107-134
-  Span frep = FIND(from, fv.spec, "replicas"), trep = FIND(to, tv.spec, "replicas");
+  Span frep = fv.replicas, trep = tv.replicas;
   if (is_nil(from, frep) || is_nil(to, trep)) {
     P.err = E_NIL_REPLICAS;  // util.go:123 dereferences both
     return;
   }
-  Span ftmpl = FIND(from, fv.spec, "template"), ttmpl = FIND(to, tv.spec, "template");
-  Span ftmeta = FIND(from, ftmpl, "metadata"), ttmeta = FIND(to, ttmpl, "metadata");
-  Span ftlabels = FIND(from, ftmeta, "labels"), ttlabels = FIND(to, ttmeta, "labels");
-  Span fpod = FIND(from, ftmpl, "spec"), tpod = FIND(to, ttmpl, "spec");
+  Span ttmpl = tv.tmpl;
+  Span ftlabels = fv.tlabels, ttlabels = tv.tlabels;
+  Span fpod = fv.tpod, tpod = tv.tpod;
   const bool replicas_differ = !spans_eq(from, frep, to, trep);
   // pre-copy: template labels follow only when the replica counts differ
   const bool copy_tlabels = replicas_differ && !json_equal(from, ftlabels, to, ttlabels);

@@ -45,7 +45,7 @@ __global__ void plan_kernel(PlanIn in, PlanOut out, uint32_t smem_cap) {
       total = bytes > 0xffffffffull - total ? 0xffffffffu : total + (uint32_t)bytes;
     }
   }
-  const bool staged = total <= smem_cap;
+  const bool staged = smem_cap != 0 && total <= smem_cap;
   if (staged) {
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
@@ -105,15 +105,23 @@ static const uint32_t PLAN_SMEM = 100 * 1024;  // two blocks per SM
 template <class G>
 static void launch(const PlanIn& in, const PlanOut& out, uint64_t in_bytes, cudaStream_t st) {
   if (!in.n) return;
-  static bool configured = false;  // per instantiation; set once per process and device set
+  static bool configured = false;  // per instantiation
   if (!configured) {
     cudaFuncSetAttribute(plan_kernel<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PLAN_SMEM);
     configured = true;
   }
-  // as many tuples per block as fit the staging area on average, 32..128
+  // Staging pays while a block's tuples (one per thread) fit: 128 or 64 tuples in
+  // 100 KB.  Larger tuples would leave one warp per block and two blocks per SM,
+  // far too few threads to hide the walk's latency; those run unstaged, 128
+  // threads per block with no shared memory, on the L1/L2 caches.
   const uint64_t avg = in_bytes / in.n + 48;
   uint32_t threads = 128;
-  while (threads > 32 && (uint64_t)threads * avg > PLAN_SMEM) threads >>= 1;
+  while (threads > 64 && (uint64_t)threads * avg > PLAN_SMEM) threads >>= 1;
+  if ((uint64_t)threads * avg > PLAN_SMEM) {
+    uint32_t blocks = (in.n + 127) / 128;
+    plan_kernel<G><<<blocks, 128, 0, st>>>(in, out, 0);
+    return;
+  }
   uint32_t blocks = (in.n + threads - 1) / threads;
   plan_kernel<G><<<blocks, threads, PLAN_SMEM, st>>>(in, out, PLAN_SMEM);
 }

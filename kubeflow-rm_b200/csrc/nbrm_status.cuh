@@ -46,7 +46,58 @@ NB_HD void plan_status(Planner& P, DocCtx& c) {
   const Doc& sts = c.d[1];
   const Doc& pod = c.d[2];
   LIT(P, STATUS_HEAD);  // {"conditions":[
-  const Span pst = pod.n ? FIND(pod, root(pod), "status") : mk(0, 0);
+  // each document is descended once: only a few members of each matter here
+  Span pst = mk(0, 0), nbname = mk(0, 0), cur = mk(0, 0), rr = mk(0, 0);
+  if (pod.n) {
+    Cursor pc;
+    pc.i = 0;
+    Member m;
+    if (obj_enter(pod, pc))
+      while (obj_key(pod, pc, m)) {
+        const Span val = val_skip(pod, pc);
+        if (KEY_IS(pod, m, "status")) pst = val;
+      }
+  }
+  {
+    Cursor nc;
+    nc.i = 0;
+    Member m;
+    if (obj_enter(nb, nc))
+      while (obj_key(nb, nc, m)) {
+        if (KEY_IS(nb, m, "metadata") && obj_enter(nb, nc)) {
+          Member mm;
+          while (obj_key(nb, nc, mm)) {
+            const Span val = val_skip(nb, nc);
+            if (KEY_IS(nb, mm, "name")) nbname = val;
+          }
+        } else if (KEY_IS(nb, m, "status") && obj_enter(nb, nc)) {
+          Member mm;
+          while (obj_key(nb, nc, mm)) {
+            const Span val = val_skip(nb, nc);
+            if (KEY_IS(nb, mm, "containerState")) cur = val;
+          }
+        } else {
+          val_skip(nb, nc);
+        }
+      }
+  }
+  if (sts.n) {
+    Cursor sc;
+    sc.i = 0;
+    Member m;
+    if (obj_enter(sts, sc))
+      while (obj_key(sts, sc, m)) {
+        if (KEY_IS(sts, m, "status") && obj_enter(sts, sc)) {
+          Member mm;
+          while (obj_key(sts, sc, mm)) {
+            const Span val = val_skip(sts, sc);
+            if (KEY_IS(sts, mm, "readyReplicas")) rr = val;
+          }
+        } else {
+          val_skip(sts, sc);
+        }
+      }
+  }
   const bool have_pod = !pod_status_is_zero(pod, pst);
   Span state = mk(0, 0);
   bool state_set = false;
@@ -101,8 +152,6 @@ NB_HD void plan_status(Planner& P, DocCtx& c) {
       LIT(P, RBRACE);
     }
     // :314-330 the state of the container named like the Notebook
-    const Span nbname = FIND(nb, FIND(nb, root(nb), "metadata"), "name");
-    const Span cur = FIND(nb, FIND(nb, root(nb), "status"), "containerState");
     const bool cur_zero = container_state_is_zero(nb, cur);
     ArrIter si(pod, FIND(pod, pst, "containerStatuses"));
     while (si.next(pod, e)) {
@@ -118,7 +167,6 @@ NB_HD void plan_status(Planner& P, DocCtx& c) {
     }
   }
   LIT(P, STATUS_READY);  // ],"readyReplicas":
-  const Span rr = sts.n ? FIND(sts, FIND(sts, root(sts), "status"), "readyReplicas") : mk(0, 0);
   if (rr.ok() && !is_null(sts, rr)) P.in(rr, 1); else LIT(P, ZERO);
   LIT(P, STATUS_STATE);  // ,"containerState":
   if (state_set && is_object(pod, state)) P.in(state, 2);
@@ -139,7 +187,9 @@ struct GenStatus {
   };
   NB_HD static uint32_t run(DocCtx& c, ObjSink s) {
     K k{c};
-    uint32_t st = is_object(c.d[0], root(c.d[0])) ? E_OK : E_PARSE;
+    const Doc& nb = c.d[0];
+    const uint32_t i0 = skip_ws(nb, 0);
+    uint32_t st = (i0 < nb.n && nb.at(i0) == '{') ? E_OK : E_PARSE;
     return plan_objects(c, s, NOBJ, st, k);
   }
 };
