@@ -1,0 +1,106 @@
+"""ctypes binding of include/nbrm_host.h (libnbrm_host.so): the C++ object store
+and NotebookReconciler."""
+import ctypes as C
+import os
+
+from . import capi
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+ERR = {0: "Ok", 1: "NotFound", 2: "AlreadyExists", 3: "Conflict", 4: "Invalid"}
+_lib = None
+
+
+def host_lib_path():
+    return os.path.join(_HERE, "libnbrm_host.so")
+
+
+def load_host_library():
+    global _lib
+    if _lib is not None:
+        return _lib
+    capi.load_library()
+    p = host_lib_path()
+    if not os.path.exists(p):
+        raise capi.NbrmError("%s is not built (there is no CPU fallback)" % p)
+    lib = C.CDLL(p)
+    lib.nbrm_store_new.restype = C.c_void_p
+    lib.nbrm_store_free.argtypes = [C.c_void_p]
+    lib.nbrm_store_create.argtypes = [C.c_void_p, C.c_char_p, C.c_uint64]
+    lib.nbrm_store_update.argtypes = [C.c_void_p, C.c_char_p, C.c_uint64]
+    lib.nbrm_store_delete.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_char_p]
+    lib.nbrm_store_get.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_char_p, C.POINTER(C.c_void_p),
+                                   C.POINTER(C.c_uint64)]
+    lib.nbrm_store_counters.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.c_int]
+    lib.nbrm_store_size.argtypes = [C.c_void_p]
+    lib.nbrm_store_size.restype = C.c_uint64
+    lib.nbrm_host_free.argtypes = [C.c_void_p]
+    lib.nbrm_reconciler_new.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int]
+    lib.nbrm_reconciler_new.restype = C.c_void_p
+    lib.nbrm_reconciler_free.argtypes = [C.c_void_p]
+    lib.nbrm_reconciler_reconcile.argtypes = [C.c_void_p, C.c_char_p, C.c_uint64, C.POINTER(C.c_uint64)]
+    _lib = lib
+    return lib
+
+
+class Store:
+    def __init__(self):
+        self.lib = load_host_library()
+        self.h = self.lib.nbrm_store_new()
+
+    def create(self, json_bytes):
+        return self.lib.nbrm_store_create(self.h, json_bytes, len(json_bytes))
+
+    def update(self, json_bytes):
+        return self.lib.nbrm_store_update(self.h, json_bytes, len(json_bytes))
+
+    def delete(self, kind, ns, name):
+        return self.lib.nbrm_store_delete(self.h, kind.encode(), ns.encode(), name.encode())
+
+    def get(self, kind, ns, name):
+        """Returns the object's JSON bytes or None (NotFound)."""
+        out, n = C.c_void_p(), C.c_uint64()
+        rc = self.lib.nbrm_store_get(self.h, kind.encode(), ns.encode(), name.encode(), C.byref(out), C.byref(n))
+        if rc != 0:
+            return None
+        b = C.string_at(out.value, n.value)
+        self.lib.nbrm_host_free(out)
+        return b
+
+    def counters(self, reset=False):
+        c = (C.c_uint64 * 6)()
+        self.lib.nbrm_store_counters(self.h, c, 1 if reset else 0)
+        return dict(zip(("gets", "creates", "updates", "status_updates", "deletes", "conflicts"), list(c)))
+
+    def size(self):
+        return int(self.lib.nbrm_store_size(self.h))
+
+    def close(self):
+        if self.h:
+            self.lib.nbrm_store_free(self.h)
+            self.h = None
+
+
+STAT_NAMES = ("keys", "reconciled", "not_found", "terminating", "creates", "updates", "status_updates",
+              "status_unchanged", "pod_restarts", "errors")
+
+
+class NotebookReconciler:
+    """NotebookReconciler (notebook-controller/controllers/notebook_controller.go:75-81,90-272)."""
+
+    def __init__(self, store, ctx, use_istio=True, status_write_if_changed=False):
+        self.lib = load_host_library()
+        self.store, self.ctx = store, ctx
+        self.h = self.lib.nbrm_reconciler_new(store.h, ctx.h, 1 if use_istio else 0,
+                                              1 if status_write_if_changed else 0)
+
+    def reconcile(self, keys, now):
+        """keys: iterable of (namespace, name).  Returns (n_errors, stats dict)."""
+        text = "\n".join("%s/%s" % k for k in keys).encode()
+        st = (C.c_uint64 * 10)()
+        rc = self.lib.nbrm_reconciler_reconcile(self.h, text, now, st)
+        return rc, dict(zip(STAT_NAMES, list(st)))
+
+    def close(self):
+        if self.h:
+            self.lib.nbrm_reconciler_free(self.h)
+            self.h = None

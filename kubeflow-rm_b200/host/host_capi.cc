@@ -1,0 +1,74 @@
+// host_capi.cc — extern "C" wrappers declared in include/nbrm_host.h.
+#include <stdlib.h>
+#include <string.h>
+
+#include "../../include/nbrm_host.h"
+#include "notebook_reconciler.h"
+
+using namespace nbrm_host;
+
+struct nbrm_store {
+  Store s;
+};
+struct nbrm_reconciler {
+  NotebookReconciler r;
+};
+
+extern "C" {
+
+nbrm_store* nbrm_store_new(void) { return new nbrm_store(); }
+void nbrm_store_free(nbrm_store* s) { delete s; }
+int nbrm_store_create(nbrm_store* s, const char* json, uint64_t len) {
+  return (int)s->s.Create(std::string(json, len));
+}
+int nbrm_store_update(nbrm_store* s, const char* json, uint64_t len) {
+  return (int)s->s.Update(std::string(json, len));
+}
+int nbrm_store_delete(nbrm_store* s, const char* kind, const char* ns, const char* name) {
+  return (int)s->s.Delete(Key{kind, ns, name});
+}
+int nbrm_store_get(nbrm_store* s, const char* kind, const char* ns, const char* name, char** out,
+                   uint64_t* len) {
+  std::string o;
+  Err e = s->s.Get(Key{kind, ns, name}, &o);
+  if (e != Err::Ok) return (int)e;
+  *out = (char*)malloc(o.size() + 1);
+  memcpy(*out, o.data(), o.size());
+  (*out)[o.size()] = 0;
+  *len = o.size();
+  return 0;
+}
+void nbrm_store_counters(nbrm_store* s, uint64_t* c, int reset) {
+  Counters k = s->s.counters();
+  c[0] = k.gets; c[1] = k.creates; c[2] = k.updates; c[3] = k.status_updates; c[4] = k.deletes; c[5] = k.conflicts;
+  if (reset) s->s.reset_counters();
+}
+uint64_t nbrm_store_size(nbrm_store* s) { return s->s.size(); }
+void nbrm_host_free(void* p) { free(p); }
+
+nbrm_reconciler* nbrm_reconciler_new(nbrm_store* s, nbrm_ctx* ctx, int use_istio, int wic) {
+  return new nbrm_reconciler{NotebookReconciler(&s->s, ctx, use_istio != 0, wic != 0)};
+}
+void nbrm_reconciler_free(nbrm_reconciler* r) { delete r; }
+int nbrm_reconciler_reconcile(nbrm_reconciler* r, const char* keys, uint64_t now_unix, uint64_t* stats) {
+  std::vector<Request> reqs;
+  const char* p = keys;
+  while (*p) {
+    const char* e = strchr(p, '\n');
+    std::string line = e ? std::string(p, e - p) : std::string(p);
+    size_t slash = line.find('/');
+    if (slash != std::string::npos) reqs.push_back(Request{line.substr(0, slash), line.substr(slash + 1)});
+    if (!e) break;
+    p = e + 1;
+  }
+  BatchStats st;
+  std::vector<std::string> errs;
+  r->r.ReconcileBatch(reqs, now_unix, &st, &errs);
+  if (stats) {
+    stats[0] = st.keys; stats[1] = st.reconciled; stats[2] = st.not_found; stats[3] = st.terminating;
+    stats[4] = st.creates; stats[5] = st.updates; stats[6] = st.status_updates; stats[7] = st.status_unchanged;
+    stats[8] = st.pod_restarts; stats[9] = st.errors;
+  }
+  return (int)st.errors;
+}
+}

@@ -7,8 +7,8 @@ import re
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def declared_symbols():
-    src = open(os.path.join(ROOT, "include", "nbrm.h")).read()
+def declared_symbols(header="nbrm.h"):
+    src = open(os.path.join(ROOT, "include", header)).read()
     src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
     return sorted(set(re.findall(r"\b(nbrm_[a-z0-9_]+)\s*\(", src)))
 
@@ -22,6 +22,18 @@ def test_library_exports_every_declared_symbol(pkg):
     assert len(syms) >= 15
     missing = [s for s in syms if not hasattr(lib, s)]
     assert not missing, missing
+
+
+def test_host_library_exports_every_declared_symbol(pkg):
+    import __graft_entry__ as graft
+    host = os.path.join(os.path.dirname(pkg.lib_path()), "libnbrm_host.so")
+    if not os.path.exists(host):
+        graft.build()
+    ctypes.CDLL(pkg.lib_path(), mode=ctypes.RTLD_GLOBAL)
+    lib = ctypes.CDLL(host)
+    syms = [s for s in declared_symbols("nbrm_host.h") if s.startswith(("nbrm_store", "nbrm_reconciler", "nbrm_host"))]
+    assert len(syms) >= 10
+    assert not [s for s in syms if not hasattr(lib, s)]
 
 
 def test_no_cpu_fallback_without_device(pkg):
