@@ -64,6 +64,16 @@ typedef struct nbrm_env {
   const char* add_fsgroup;
   const char* controller_namespace;
   const char* oauth_proxy_image;
+  /* profile-controller: --userid-header / --userid-prefix (profile-controller/main.go:75-76),
+   * NOTEBOOK_CONTROLLER_PRINCIPAL, ISTIO_INGRESS_GATEWAY_PRINCIPAL, KFP_UI_PRINCIPAL
+   * (controllers/profile_controller.go:420-430), and the namespace-labels file
+   * (--namespace-labels-path, :775-790) given as a JSON object of strings. */
+  const char* userid_header;
+  const char* userid_prefix;
+  const char* notebook_controller_principal;
+  const char* istio_ingress_gateway_principal;
+  const char* kfp_ui_principal;
+  const char* namespace_labels_json;
 } nbrm_env;
 
 typedef struct nbrm_docs {
@@ -285,6 +295,22 @@ int nbrm_poddefault_mutate(nbrm_ctx* ctx, const nbrm_docs* pods, const nbrm_docs
                            const uint32_t* ranges, nbrm_out* out);
 int nbrm_poddefault_mutate_resident(nbrm_ctx* ctx);
 
+/* ---- profile-controller desired objects ---------------------------------------
+ * Replaces, for a batch of Profiles, the object construction inside
+ * ProfileReconciler.Reconcile (profile-controller/controllers/
+ * profile_controller.go:105-334): the Namespace :127-137 with setNamespaceLabels
+ * :754-772 applied to the configured labels file (nbrm_env.namespace_labels_json),
+ * getAuthorizationPolicy :419-504 with its metadata :512-520, the two
+ * ServiceAccounts and their RoleBindings (updateServiceAccount :592-637), the owner
+ * RoleBinding namespaceAdmin :230-246 and the ResourceQuota :253-262, each with the
+ * controller ownerReference to the Profile.  Output: 8 objects per Profile in that
+ * order; the ResourceQuota has length 0 when spec.resourceQuotaSpec.hard is empty.
+ * Plugins (AWS IRSA / GCP workload identity, :286-294) and the finalizer are I/O
+ * and bookkeeping and stay with the caller.  The Istio proto JSON shape of the
+ * AuthorizationPolicy is recalled, not pinned by a reference test. */
+int nbrm_profile_generate(nbrm_ctx* ctx, const nbrm_docs* profiles, nbrm_out* out);
+int nbrm_profile_generate_resident(nbrm_ctx* ctx);
+
 /* ---- composing generators --------------------------------------------------
  * Run one generator on arbitrary slots: tuple i = document i of slot_a (and of
  * slot_b / slot_c when >= 0).  Generators: 0 notebook-controller objects (3
@@ -292,7 +318,7 @@ int nbrm_poddefault_mutate_resident(nbrm_ctx* ctx);
  * slot_b found), 3 status (Notebook, StatefulSet, Pod), 4 culling pass
  * (Notebook, kernels, terminals; arg0/arg1 = idle / period minutes), 5 webhook
  * mutation (flags NBRM_MUT_*), 6 restart guard (mutated, request, old),
- * 7 PodDefault admission (Pods, shared PodDefault arena).  use_side_input: pass
+ * 7 PodDefault admission (Pods, shared PodDefault arena), 8 Profile objects (8).  use_side_input: pass
  * the bytes of nbrm_upload_bytes (seeds / pod_exists / ranges).  The result is
  * read with nbrm_download or moved on with nbrm_result_to_slot. */
 int nbrm_run(nbrm_ctx* ctx, int generator, int slot_a, int slot_b, int slot_c, uint32_t flags,

@@ -23,7 +23,9 @@ class NbrmError(RuntimeError):
 class _Env(C.Structure):
     _fields_ = [(k, C.c_char_p) for k in (
         "use_istio", "istio_gateway", "istio_host", "cluster_domain", "add_fsgroup",
-        "controller_namespace", "oauth_proxy_image")]
+        "controller_namespace", "oauth_proxy_image", "userid_header", "userid_prefix",
+        "notebook_controller_principal", "istio_ingress_gateway_principal", "kfp_ui_principal",
+        "namespace_labels_json")]
 
 
 class _Docs(C.Structure):
@@ -48,7 +50,11 @@ class Profile(C.Structure):
 # reference process environment (nbrm_env) key -> struct field
 ENV_FIELDS = {"USE_ISTIO": "use_istio", "ISTIO_GATEWAY": "istio_gateway", "ISTIO_HOST": "istio_host",
               "CLUSTER_DOMAIN": "cluster_domain", "ADD_FSGROUP": "add_fsgroup",
-              "CONTROLLER_NAMESPACE": "controller_namespace", "OAUTH_PROXY_IMAGE": "oauth_proxy_image"}
+              "CONTROLLER_NAMESPACE": "controller_namespace", "OAUTH_PROXY_IMAGE": "oauth_proxy_image",
+              "USERID_HEADER": "userid_header", "USERID_PREFIX": "userid_prefix",
+              "NOTEBOOK_CONTROLLER_PRINCIPAL": "notebook_controller_principal",
+              "ISTIO_INGRESS_GATEWAY_PRINCIPAL": "istio_ingress_gateway_principal",
+              "KFP_UI_PRINCIPAL": "kfp_ui_principal", "NAMESPACE_LABELS_JSON": "namespace_labels_json"}
 
 
 def lib_path():
@@ -112,6 +118,8 @@ def load_library():
     lib.nbrm_run.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint32, C.c_uint64,
                              C.c_uint32, C.c_uint32, C.c_int]
     lib.nbrm_download_slot.argtypes = [C.c_void_p, C.c_int, C.POINTER(_Out)]
+    lib.nbrm_profile_generate.argtypes = [C.c_void_p, C.POINTER(_Docs), C.POINTER(_Out)]
+    lib.nbrm_profile_generate_resident.argtypes = [C.c_void_p]
     lib.nbrm_scan_lengths_noalloc.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p,
                                               C.c_char_p, C.c_size_t]
     _lib = lib
@@ -345,4 +353,10 @@ class Context:
     def download_slot(self, slot, copy=True):
         o = _Out()
         self._check(self.lib.nbrm_download_slot(self.h, slot, C.byref(o)))
+        return Result(o, copy)
+
+    # --- profile-controller objects
+    def profile_generate(self, profiles, copy=True):
+        d, o = profiles.c_struct(), _Out()
+        self._check(self.lib.nbrm_profile_generate(self.h, C.byref(d), C.byref(o)))
         return Result(o, copy)

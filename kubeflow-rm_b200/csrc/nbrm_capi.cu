@@ -670,4 +670,16 @@ int nbrm_download_slot(nbrm_ctx* c, int slot, nbrm_out* out) {
   return 0;
 }
 
+int nbrm_profile_generate_resident(nbrm_ctx* c) {
+  if (!c) return -2;
+  return run_generator(c, GEN_ID_PROFILE, {0, -1, -1}, 0, nullptr, 0);
+}
+
+int nbrm_profile_generate(nbrm_ctx* c, const nbrm_docs* profiles, nbrm_out* out) {
+  if (!c || !out) return -2;
+  if (int r = nbrm_upload(c, 0, profiles)) return r;
+  if (int r = nbrm_profile_generate_resident(c)) return r;
+  return nbrm_download(c, out);
+}
+
 }  // extern "C"

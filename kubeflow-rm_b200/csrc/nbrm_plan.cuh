@@ -115,6 +115,11 @@ struct EnvLits {
   Span cluster_domain;  // CLUSTER_DOMAIN or default    (:537-539)
   Span ctrl_namespace;  // ODH controller namespace     (odh main.go:63-72)
   Span oauth_image;     // --oauth-proxy-image          (odh main.go:80)
+  // profile-controller (profile_controller.go:419-504, :127-137)
+  Span prof_when_key;   // "request.headers[<userid header>]" (quoted)
+  Span prof_prefix;     // userid prefix (unquoted, escaped)
+  Span prof_igw, prof_kfp, prof_nbc;  // principals (quoted)
+  Span prof_ns_labels;  // members of the Namespace's labels map, rendered by the host
   uint32_t add_fsgroup; // ADD_FSGROUP unset or "true"  (notebook_controller.go:475)
   uint32_t use_istio;   // USE_ISTIO == "true"          (:213)
 };

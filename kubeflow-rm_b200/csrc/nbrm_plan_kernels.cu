@@ -7,6 +7,7 @@
 #include "nbrm_cull.cuh"
 #include "nbrm_mutate.cuh"
 #include "nbrm_pd.cuh"
+#include "nbrm_profile.cuh"
 
 namespace nbrm {
 
@@ -136,6 +137,7 @@ void launch_plan(int gen, const PlanIn& in, const PlanOut& out, uint64_t in_byte
     case GEN_ID_MUTATE: launch<GenMutate>(in, out, in_bytes, st); break;
     case GEN_ID_GUARD: launch<GenRestartGuard>(in, out, in_bytes, st); break;
     case GEN_ID_PODDEFAULT: launch<GenPodDefault>(in, out, in_bytes, st); break;
+    case GEN_ID_PROFILE: launch<GenProfile>(in, out, in_bytes, st); break;
   }
 }
 
@@ -149,6 +151,7 @@ void gen_shape(int gen, uint32_t* nobj, uint32_t* cap) {
     case GEN_ID_MUTATE: *nobj = GenMutate::NOBJ; *cap = GenMutate::CAP; break;
     case GEN_ID_GUARD: *nobj = GenRestartGuard::NOBJ; *cap = GenRestartGuard::CAP; break;
     case GEN_ID_PODDEFAULT: *nobj = GenPodDefault::NOBJ; *cap = GenPodDefault::CAP; break;
+    case GEN_ID_PROFILE: *nobj = GenProfile::NOBJ; *cap = GenProfile::CAP; break;
     default: *nobj = 0; *cap = 0;
   }
 }

@@ -5,6 +5,8 @@
 #include <string.h>
 
 #include <string>
+#include <utility>
+#include <vector>
 
 #include "../../include/nbrm.h"
 #include "nbrm_plan.cuh"
@@ -34,6 +36,38 @@ inline std::string json_escape(const char* s) {
   return o;
 }
 
+// setNamespaceLabels (profile_controller.go:754-772) applied to the Namespace the
+// reconciler builds (:127-137: labels {"istio-injection": "enabled"}): a default
+// with an empty value removes the key, any other default is added unless the key
+// exists.  labels_json: the labels file as a JSON object of strings (may be null).
+// Returns the members of the resulting map as JSON text ("k":"v","k2":"v2").
+inline std::string render_namespace_labels(const char* labels_json) {
+  std::vector<std::pair<std::string, std::string>> m;  // raw JSON strings, with quotes
+  m.push_back({"\"istio-injection\"", "\"enabled\""});
+  if (labels_json && *labels_json) {
+    Doc d;
+    d.p = labels_json;
+    d.n = (uint32_t)strlen(labels_json);
+    ObjIter it(d, root(d));
+    Member mem;
+    while (it.next(d, mem)) {
+      if (!is_string(d, mem.val)) continue;
+      const std::string k(d.p + mem.key.off, mem.key.len), v(d.p + mem.val.off, mem.val.len);
+      size_t at = m.size();
+      for (size_t i = 0; i < m.size(); ++i)
+        if (m[i].first == k) at = i;
+      if (v == "\"\"") {
+        if (at < m.size()) m.erase(m.begin() + at);
+      } else if (at == m.size()) {
+        m.push_back({k, v});
+      }
+    }
+  }
+  std::string out;
+  for (size_t i = 0; i < m.size(); ++i) out += (i ? "," : "") + m[i].first + ":" + m[i].second;
+  return out;
+}
+
 inline void build_pool_host(const nbrm_env* env, std::string& pool, EnvLits& L) {
   pool.assign(L__TOTAL, '\0');
 #define X(name, text) memcpy(&pool[L_##name], text, sizeof(text) - 1);
@@ -60,6 +94,17 @@ inline void build_pool_host(const nbrm_env* env, std::string& pool, EnvLits& L) 
       env ? env->oauth_proxy_image : nullptr,
       "registry.redhat.io/openshift4/ose-oauth-proxy@sha256:"
       "4f8d66597feeb32bb18699326029f9a71a5aca4a57679d636b876377c2e95695")));
+  // profile-controller strings (GetEnvDefault: unset or empty takes the default)
+  L.prof_when_key = add("\"request.headers[" +
+                        json_escape(get(env ? env->userid_header : nullptr, "x-goog-authenticated-user-email")) + "]\"");
+  L.prof_prefix = add(json_escape(get(env ? env->userid_prefix : nullptr, "accounts.google.com:")));
+  L.prof_igw = add("\"" + json_escape(get(env ? env->istio_ingress_gateway_principal : nullptr,
+                       "cluster.local/ns/istio-system/sa/istio-ingressgateway-service-account")) + "\"");
+  L.prof_kfp = add("\"" + json_escape(get(env ? env->kfp_ui_principal : nullptr,
+                       "cluster.local/ns/kubeflow/sa/ml-pipeline-ui")) + "\"");
+  L.prof_nbc = add("\"" + json_escape(get(env ? env->notebook_controller_principal : nullptr,
+                       "cluster.local/ns/kubeflow/sa/notebook-controller-service-account")) + "\"");
+  L.prof_ns_labels = add(render_namespace_labels(env ? env->namespace_labels_json : nullptr));
   // ADD_FSGROUP: add the fsGroup when unset or exactly "true" (:475)
   L.add_fsgroup = (!env || !env->add_fsgroup || strcmp(env->add_fsgroup, "true") == 0) ? 1u : 0u;
   L.use_istio = (env && env->use_istio && strcmp(env->use_istio, "true") == 0) ? 1u : 0u;

@@ -500,3 +500,23 @@ def admission_workload(n_pods, pds_per_ns, seed=SEED, pods_per_ns=20):
         pods.append(admission_pod(rng, i, "ns-%03d" % k, pds_per_ns))
         ranges.append(ns_range[k])
     return pods, pds, ranges
+
+
+def profile_cr(rng, i):
+    """C4: Profile user-%03d owned by user-%03d@example.com; 10 % with a ResourceQuota
+    (profile-controller/config/samples; BASELINE.json configs[3])."""
+    p = {"apiVersion": "kubeflow.org/v1", "kind": "Profile",
+         "metadata": {"name": "user-%03d" % i, "uid": "p-%06d" % i, "resourceVersion": str(i)},
+         "spec": {"owner": {"kind": "User", "name": "user-%03d@example.com" % i}}}
+    r = rng.random()
+    if r < 0.1:
+        p["spec"]["resourceQuotaSpec"] = {"hard": {"cpu": "4", "memory": "8Gi"}}
+    elif r < 0.15:
+        p["spec"]["resourceQuotaSpec"] = {"hard": {}}
+    elif r < 0.2:
+        p["spec"]["owner"] = {"kind": "User", "apiGroup": "rbac.authorization.k8s.io", "name": "a\"b@x"}
+    elif r < 0.23:
+        del p["spec"]["owner"]
+    elif r < 0.26:
+        del p["metadata"]["uid"]
+    return p

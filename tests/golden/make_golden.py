@@ -315,7 +315,20 @@ adm = {
          "out": {"command": ["cmd2"], "args": ["arg3", "arg4"]}}]},
 }
 
+# ---------------------------------------------------------------------------
+# profile-controller/controllers/profile_controller_test.go:25-111 TestEnforceNamespaceLabelsFromConfig
+_DEF = {"katib.kubeflow.org/metrics-collector-injection": "enabled",
+        "serving.kubeflow.org/inferenceservice": "enabled", "pipelines.kubeflow.org/enabled": "true",
+        "app.kubernetes.io/part-of": "kubeflow-profile"}
+profile = {"set_namespace_labels": {"src": "profile-controller/controllers/profile_controller_test.go:25-111", "cases": [
+    {"current": None, "labels": _DEF, "expected": dict(_DEF)},
+    {"current": {"user-name": "Jim", "serving.kubeflow.org/inferenceservice": "disabled"}, "labels": _DEF,
+     "expected": dict(_DEF, **{"user-name": "Jim", "serving.kubeflow.org/inferenceservice": "disabled"})},
+    {"current": {"user-name": "Jim", "removal-label": "enabled"}, "labels": dict(_DEF, **{"removal-label": ""}),
+     "expected": dict(_DEF, **{"user-name": "Jim"})}]}}
+
 if __name__ == "__main__":
+    write("profile.json", profile)
     write("nbc_status.json", status_cases)
     write("nbc_involved_object.json", involved_cases)
     write("culling.json", culling)

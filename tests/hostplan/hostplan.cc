@@ -17,6 +17,7 @@
 #include "../../kubeflow-rm_b200/csrc/nbrm_cull.cuh"
 #include "../../kubeflow-rm_b200/csrc/nbrm_mutate.cuh"
 #include "../../kubeflow-rm_b200/csrc/nbrm_pd.cuh"
+#include "../../kubeflow-rm_b200/csrc/nbrm_profile.cuh"
 #include "../../kubeflow-rm_b200/csrc/nbrm_pool.h"
 
 using namespace nbrm;
@@ -125,6 +126,7 @@ int hostplan_run(int gen, const char* d0, const uint64_t* o0, const char* d1, co
     case 5: rc = run_host<GenMutate>(data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenMutate::NOBJ; break;
     case 6: rc = run_host<GenRestartGuard>(data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenRestartGuard::NOBJ; break;
     case 7: rc = run_host<GenPodDefault>(data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenPodDefault::NOBJ; break;
+    case 8: rc = run_host<GenProfile>(data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenProfile::NOBJ; break;
   }
   *out_data = g_out.data.data();
   *out_off = g_out.off.data();

@@ -3,6 +3,7 @@ planners) against the oracle, object by object, on canonical JSON."""
 import json
 
 from oracle import culling, gojson, nbc, odh, poddefault
+from oracle import profile as oprofile
 
 
 def check_nbc_generate(nbs, outs, status, env, flags, owner_api="kubeflow.org/v1beta1"):
@@ -201,3 +202,19 @@ def check_poddefault(pods, pds, ranges, outs, status, result):
         assert int(result[i]) >= 1
         seen["patched"] += 1
     return seen
+
+
+def check_profile(profiles, outs, status, env, default_labels):
+    n = 0
+    for i, p in enumerate(profiles):
+        exp = oprofile.profile_objects(p, env, default_labels)
+        assert status[i] == 0, (i, status[i])
+        for k in range(8):
+            got = outs[8 * i + k]
+            if exp[k] is None:
+                assert got == b"", (i, k, got)
+                continue
+            assert gojson.canon(json.loads(got)) == gojson.canon(exp[k]), \
+                "profile %d object %d\n got %s\n exp %s" % (i, k, gojson.canon(json.loads(got)), gojson.canon(exp[k]))
+            n += 1
+    return n

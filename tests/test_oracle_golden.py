@@ -5,7 +5,7 @@ import os
 
 import pytest
 
-from oracle import culling, gojson, nbc, odh, poddefault
+from oracle import culling, gojson, nbc, odh, poddefault, profile
 
 G = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 
@@ -22,7 +22,7 @@ def test_golden_files_are_current():
     spec.loader.exec_module(mg)
     for name, obj in (("nbc_status.json", mg.status_cases), ("culling.json", mg.culling),
                       ("odh.json", mg.odh), ("adm.json", mg.adm),
-                      ("nbc_involved_object.json", mg.involved_cases)):
+                      ("nbc_involved_object.json", mg.involved_cases), ("profile.json", mg.profile)):
         assert load(name) == json.loads(json.dumps(obj)), name
 
 
@@ -191,3 +191,8 @@ def test_selector_semantics():
     for bad in (ex("In"), ex("Exists", ["v"]), ex("Bogus")):
         with pytest.raises(poddefault.SelectorError):
             m(bad, {"k": "v"})
+
+
+def test_profile_namespace_labels():
+    for c in load("profile.json")["set_namespace_labels"]["cases"]:
+        assert profile.set_namespace_labels(c["current"], c["labels"]) == c["expected"]
