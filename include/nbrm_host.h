@@ -31,8 +31,8 @@ uint64_t nbrm_store_size(nbrm_store* s);
 void nbrm_host_free(void* p);
 
 /* NotebookReconciler.  keys = "namespace/name" entries separated by '\n'.
- * stats[10] = keys, reconciled, not_found, terminating, creates, updates,
- * status_updates, status_unchanged, pod_restarts, errors.  Returns 0, or the
+ * stats[11] = keys, reconciled, not_found, terminating, creates, updates,
+ * status_updates, status_unchanged, pod_restarts, errors, events_reissued.  Returns 0, or the
  * number of keys that ended in an error (the reference's `return ctrl.Result{}, err`). */
 nbrm_reconciler* nbrm_reconciler_new(nbrm_store* s, nbrm_ctx* ctx, int use_istio, int status_write_if_changed);
 void nbrm_reconciler_free(nbrm_reconciler* r);

@@ -81,7 +81,7 @@ class Store:
 
 
 STAT_NAMES = ("keys", "reconciled", "not_found", "terminating", "creates", "updates", "status_updates",
-              "status_unchanged", "pod_restarts", "errors")
+              "status_unchanged", "pod_restarts", "errors", "events_reissued")
 
 
 class NotebookReconciler:
@@ -96,7 +96,7 @@ class NotebookReconciler:
     def reconcile(self, keys, now):
         """keys: iterable of (namespace, name).  Returns (n_errors, stats dict)."""
         text = "\n".join("%s/%s" % k for k in keys).encode()
-        st = (C.c_uint64 * 10)()
+        st = (C.c_uint64 * 11)()
         rc = self.lib.nbrm_reconciler_reconcile(self.h, text, now, st)
         return rc, dict(zip(STAT_NAMES, list(st)))
 

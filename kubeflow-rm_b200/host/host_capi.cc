@@ -67,7 +67,7 @@ int nbrm_reconciler_reconcile(nbrm_reconciler* r, const char* keys, uint64_t now
   if (stats) {
     stats[0] = st.keys; stats[1] = st.reconciled; stats[2] = st.not_found; stats[3] = st.terminating;
     stats[4] = st.creates; stats[5] = st.updates; stats[6] = st.status_updates; stats[7] = st.status_unchanged;
-    stats[8] = st.pod_restarts; stats[9] = st.errors;
+    stats[8] = st.pod_restarts; stats[9] = st.errors; stats[10] = st.events_reissued;
   }
   return (int)st.errors;
 }

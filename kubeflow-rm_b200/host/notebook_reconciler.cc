@@ -1,6 +1,8 @@
 // notebook_reconciler.cc — see notebook_reconciler.h.
 #include "notebook_reconciler.h"
 
+#include <ctype.h>
+
 #include "../csrc/nbrm_json.cuh"
 
 namespace nbrm_host {
@@ -51,6 +53,37 @@ int NotebookReconciler::ReconcileBatch(const std::vector<Request>& reqs, uint64_
   std::vector<size_t> live;
   std::vector<std::string> nbs;
   for (size_t i = 0; i < reqs.size(); ++i) {
+    std::string ev;
+    if (store_->Get(Key{"Event", reqs[i].ns, reqs[i].name}, &ev) == Err::Ok) {  // :95-119
+      // nbNameFromInvolvedObject :666-690
+      const std::string kind = read_string(ev, {"involvedObject", "kind"});
+      const std::string oname = read_string(ev, {"involvedObject", "name"});
+      const std::string ons = read_string(ev, {"involvedObject", "namespace"});
+      std::string nb_name, pod;
+      if (kind == "StatefulSet") {
+        nb_name = oname;
+      } else if (kind == "Pod" && store_->Get(Key{"Pod", ons, oname}, &pod) == Err::Ok) {
+        nb_name = read_string(pod, {"metadata", "labels", "notebook-name"});
+      }
+      if (nb_name.empty()) {
+        errs[i] = kind == "Pod" && pod.empty() ? "pod of the event not found" : "object isn't related to a Notebook";
+        continue;
+      }
+      std::string nb;
+      if (store_->Get(Key{"Notebook", reqs[i].ns, nb_name}, &nb) != Err::Ok) continue;  // ignoreNotFound :111
+      std::string lower = kind;
+      for (char& ch : lower) ch = (char)tolower((unsigned char)ch);
+      // EventRecorder.Eventf(notebook, type, reason, "Reissued from %s/%s: %s") :116-117
+      const std::string obj =
+          "{\"apiVersion\":\"v1\",\"kind\":\"Event\",\"metadata\":{\"name\":\"" + nb_name + "." + reqs[i].name +
+          "\",\"namespace\":\"" + reqs[i].ns + "\"},\"involvedObject\":{\"kind\":\"Notebook\",\"name\":\"" + nb_name +
+          "\",\"namespace\":\"" + reqs[i].ns + "\"},\"type\":\"" + read_string(ev, {"type"}) + "\",\"reason\":\"" +
+          read_string(ev, {"reason"}) + "\",\"message\":\"Reissued from " + lower + "/" + oname + ": " +
+          read_string(ev, {"message"}) + "\"}";
+      Err e = store_->Create(obj);
+      if (e == Err::Ok || e == Err::AlreadyExists) ++st.events_reissued;
+      continue;
+    }
     std::string nb;
     if (store_->Get(Key{"Notebook", reqs[i].ns, reqs[i].name}, &nb) != Err::Ok) {
       ++st.not_found;

@@ -11,7 +11,10 @@
 // controller-runtime's guarantee that a key is never reconciled concurrently
 // with itself) and runs their pure work — desired objects, create-or-update
 // decision, status — on the GPU in one pass; Reconcile(req) is a batch of one.
-// Not built: the Event re-emission branch (:95-119) and the metrics counters.
+// A key that names an Event takes the re-emission branch (:95-119) with
+// nbNameFromInvolvedObject (:666-690): the Event is re-issued on the Notebook (here: an
+// Event object created in the store, as record.EventRecorder would).  Not built: the
+// Prometheus counters.
 #pragma once
 #include <string>
 #include <vector>
@@ -33,7 +36,7 @@ struct Result {  // ctrl.Result
 struct BatchStats {
   uint64_t keys = 0, reconciled = 0, not_found = 0, terminating = 0;
   uint64_t creates = 0, updates = 0, status_updates = 0, status_unchanged = 0;
-  uint64_t pod_restarts = 0, errors = 0;
+  uint64_t pod_restarts = 0, errors = 0, events_reissued = 0;
 };
 
 class NotebookReconciler {

@@ -71,6 +71,20 @@ ObjMeta read_meta(const std::string& json) {
   return r;
 }
 
+std::string read_string(const std::string& json, const std::vector<std::string>& path) {
+  Doc d = doc_of(json);
+  Span cur = root(d);
+  for (const std::string& key : path) {
+    Span next = mk(0, 0);
+    ObjIter it(d, cur);
+    Member m;
+    while (it.next(d, m))
+      if (text(d, inner(m.key)) == key) next = m.val;
+    cur = next;
+  }
+  return unquote(d, cur);
+}
+
 std::string read_annotation(const std::string& json, const std::string& key) {
   Doc d = doc_of(json);
   Span ann = find(d, find(d, root(d), "metadata"), "annotations");

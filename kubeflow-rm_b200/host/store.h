@@ -15,6 +15,7 @@
 #include <map>
 #include <mutex>
 #include <string>
+#include <vector>
 
 namespace nbrm_host {
 
@@ -40,6 +41,8 @@ struct ObjMeta {
   bool ok = false;
 };
 ObjMeta read_meta(const std::string& json);
+// A string member of a nested object, e.g. read_string(json, {"involvedObject","kind"}); "" when absent.
+std::string read_string(const std::string& json, const std::vector<std::string>& path);
 // metadata.annotations[key] as the raw JSON string value (with quotes), or "" when absent.
 std::string read_annotation(const std::string& json, const std::string& key);
 // The same object with metadata.<field> set to the JSON value `raw` (or removed when raw is empty).

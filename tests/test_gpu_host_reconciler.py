@@ -104,3 +104,38 @@ def test_pod_restart_and_status_mirroring(pkg, wl):
     rc, st = rec.reconcile([(ns, name)], NOW)
     assert rc == 1 and st["errors"] == 1
     rec.close(); store.close(); ctx.close()
+
+
+def test_event_reissue(pkg, wl):
+    """Reconcile on an Event key re-issues it on the Notebook (notebook_controller.go:95-119) with
+    nbNameFromInvolvedObject as pinned by notebook_controller_test.go:22-92."""
+    import os
+    host = importlib.import_module(graft.PKG_NAME + ".host")
+    g = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "nbc_involved_object.json")))
+    ctx = pkg.Context(0, env=ENV)
+    store = host.Store()
+    rec = host.NotebookReconciler(store, ctx, use_istio=False)
+    ns = "test-namespace"
+    nb = wl.notebook_c1(1)
+    nb["metadata"].update(name="test-notebook", namespace=ns)
+    store.create(wl.dumps(nb))
+    for p in g["pods"]:
+        store.create(wl.dumps(dict(p, kind="Pod", apiVersion="v1")))
+    keys = []
+    for i, c in enumerate(g["cases"]):
+        ev = {"apiVersion": "v1", "kind": "Event", "metadata": {"name": "ev-%d" % i, "namespace": ns},
+              "involvedObject": c["involvedObject"], "type": "Warning", "reason": "FailedScheduling",
+              "message": "0/1 nodes are available"}
+        store.create(wl.dumps(ev))
+        keys.append((ns, "ev-%d" % i))
+    store.create(wl.dumps({"apiVersion": "v1", "kind": "Event", "metadata": {"name": "ev-x", "namespace": ns},
+                           "involvedObject": {"kind": "Node", "name": "n1"}, "type": "Normal", "reason": "r",
+                           "message": "m"}))
+    rc, st = rec.reconcile(keys + [(ns, "ev-x")], NOW)
+    assert st["events_reissued"] == len(g["cases"]) and rc == 1 and st["reconciled"] == 0
+    for i, c in enumerate(g["cases"]):
+        out = json.loads(store.get("Event", ns, "%s.ev-%d" % (c["expected"], i)))
+        assert out["involvedObject"]["name"] == c["expected"] and out["involvedObject"]["kind"] == "Notebook"
+        kind = c["involvedObject"]["kind"].lower()
+        assert out["message"] == "Reissued from %s/%s: 0/1 nodes are available" % (kind, c["involvedObject"]["name"])
+    rec.close(); store.close(); ctx.close()
