@@ -35,8 +35,14 @@ NB_HD Doc pd_doc(const DocCtx& c, uint32_t j) {
   return d;
 }
 
+// Out-of-line doors to the deep compare and the key lookup of nbrm_cmp.cuh: the
+// merges below call them from many places, and one copy each keeps this kernel's
+// compile time in seconds (inlined everywhere it took twenty minutes).
+NB_FN bool pd_equal(const Doc& a, Span x, const Doc& b, Span y) { return json_equal(a, x, b, y); }
+NB_FN Span pd_find_key(const Doc& d, Span obj, const Doc& kd, Span key) { return find_key(d, obj, kd, key); }
+
 // String value or "" when the member is missing / not a string.
-NB_HD bool strval_equal(const Doc& a, Span x, const Doc& b, Span y) {
+NB_FN bool strval_equal(const Doc& a, Span x, const Doc& b, Span y) {
   const bool xs = is_string(a, x) && x.len > 2, ys = is_string(b, y) && y.len > 2;
   if (!xs || !ys) return xs == ys;
   return str_equal(a, x, b, y);
@@ -51,7 +57,7 @@ NB_HD bool strval_is(const Doc& d, Span x, const char (&lit)[N]) {
 // invalid (In/NotIn without values, Exists/DoesNotExist with values, unknown
 // operator).  All requirements are validated before any is evaluated, as
 // LabelSelectorAsSelector does.
-NB_HD int selector_matches(const Doc& pd, Span sel, const Doc& pod, Span labels) {
+NB_FN int selector_matches(const Doc& pd, Span sel, const Doc& pod, Span labels) {
   const Span exprs = find(pd, sel, "matchExpressions");
   {
     ArrIter it(pd, exprs);
@@ -73,7 +79,7 @@ NB_HD int selector_matches(const Doc& pd, Span sel, const Doc& pod, Span labels)
     ObjIter it(pd, find(pd, sel, "matchLabels"));
     Member m;
     while (it.next(pd, m)) {
-      const Span pv = find_key(pod, labels, pd, m.key);
+      const Span pv = pd_find_key(pod, labels, pd, m.key);
       if (!is_string(pod, pv) || !is_string(pd, m.val) || !str_equal(pod, pv, pd, m.val)) return 0;
     }
   }
@@ -144,7 +150,7 @@ struct PdCtx {
 // `existing` is the Pod's array (may be nil); field names the PodDefault spec
 // list; key names the key field.
 template <uint32_t NF, uint32_t NK>
-NB_HD void merge_keyed(PdCtx& x, Span existing, const char (&field)[NF], const char (&key)[NK],
+NB_FN void merge_keyed(PdCtx& x, Span existing, const char (&field)[NF], const char (&key)[NK],
                        AddList& out) {
   out.n = 0;
   const Doc& pod = *x.pod;
@@ -163,7 +169,7 @@ NB_HD void merge_keyed(PdCtx& x, Span existing, const char (&field)[NF], const c
           if (strval_equal(pod, find(pod, e, key), pd, vk)) held = e;
       }
       if (held.ok()) {
-        if (!json_equal(pod, held, pd, v)) x.conflict = true;
+        if (!pd_equal(pod, held, pd, v)) x.conflict = true;
         continue;
       }
       // ... or the first appended item with it
@@ -172,7 +178,7 @@ NB_HD void merge_keyed(PdCtx& x, Span existing, const char (&field)[NF], const c
         const Doc od = pd_doc(*x.c, out.a[k].pd);
         if (strval_equal(od, find(od, out.a[k].s, key), pd, vk)) {
           found = true;
-          if (!json_equal(od, out.a[k].s, pd, v)) x.conflict = true;
+          if (!pd_equal(od, out.a[k].s, pd, v)) x.conflict = true;
         }
       }
       if (found) continue;
@@ -189,7 +195,7 @@ NB_HD void merge_keyed(PdCtx& x, Span existing, const char (&field)[NF], const c
 
 // mergeVolumeMounts (:266-317): keyed by name for what is appended, and every
 // PodDefault mount must also agree with whatever holds its mountPath.
-NB_HD void merge_volume_mounts(PdCtx& x, Span existing, AddList& out, AddList& paths) {
+NB_FN void merge_volume_mounts(PdCtx& x, Span existing, AddList& out, AddList& paths) {
   out.n = 0;
   paths.n = 0;
   const Doc& pod = *x.pod;
@@ -209,7 +215,7 @@ NB_HD void merge_volume_mounts(PdCtx& x, Span existing, AddList& out, AddList& p
           if (strval_equal(pod, ek, pd, vk)) held = e;
         }
         if (held.ok()) {
-          if (!json_equal(pod, held, pd, v)) x.conflict = true;
+          if (!pd_equal(pod, held, pd, v)) x.conflict = true;
           continue;
         }
         bool found = false;
@@ -218,7 +224,7 @@ NB_HD void merge_volume_mounts(PdCtx& x, Span existing, AddList& out, AddList& p
           const Span ok = pass ? find(od, tab.a[k].s, "mountPath") : find(od, tab.a[k].s, "name");
           if (strval_equal(od, ok, pd, vk)) {
             found = true;
-            if (!json_equal(od, tab.a[k].s, pd, v)) x.conflict = true;
+            if (!pd_equal(od, tab.a[k].s, pd, v)) x.conflict = true;
           }
         }
         if (found) continue;
@@ -238,7 +244,7 @@ NB_HD void merge_volume_mounts(PdCtx& x, Span existing, AddList& out, AddList& p
 // new is added, one whose key exists must carry the same value.  out holds the
 // added members (key":"value spans of the PodDefault documents).
 template <uint32_t NF>
-NB_HD void merge_map(PdCtx& x, Span existing, const char (&field)[NF], AddList& out) {
+NB_FN void merge_map(PdCtx& x, Span existing, const char (&field)[NF], AddList& out) {
   out.n = 0;
   const Doc& pod = *x.pod;
   for (uint32_t q = 0; q < x.nmatch; ++q) {
@@ -246,7 +252,7 @@ NB_HD void merge_map(PdCtx& x, Span existing, const char (&field)[NF], AddList& 
     ObjIter it(pd, find(pd, find(pd, root(pd), "spec"), field));
     Member m;
     while (it.next(pd, m)) {
-      const Span held = find_key(pod, existing, pd, m.key);
+      const Span held = pd_find_key(pod, existing, pd, m.key);
       if (held.ok()) {
         if (!strval_equal(pod, held, pd, m.val)) x.conflict = true;
         continue;
@@ -284,7 +290,7 @@ NB_HD void put_pd(Planner& P, const DocCtx& c, uint32_t j, Span s) {
 
 // "<key>":[ existing elements , appended items ]   — nothing when both are empty.
 // Returns true when something was emitted.
-NB_HD bool emit_merged_list(Planner& P, Sep& sep, const PdCtx& x, uint32_t key_off, uint32_t key_len,
+NB_FN bool emit_merged_list(Planner& P, Sep& sep, const PdCtx& x, uint32_t key_off, uint32_t key_len,
                             Span existing, const AddList& add) {
   const Doc& pod = *x.pod;
   const bool have_existing = is_array(pod, existing) && !is_empty_container(pod, existing);
@@ -314,7 +320,7 @@ NB_HD Span pd_name(const Doc& pd) {
 
 // The Pod's annotation key `key` is the marker of one of the applied PodDefaults
 // ("poddefault.admission.kubeflow.org/poddefault-<name>", :553-555).
-NB_HD bool is_marker_key(const PdCtx& x, Span key) {
+NB_FN bool is_marker_key(const PdCtx& x, Span key) {
   const Doc& pod = *x.pod;
   const Span k = inner(key);
   const char prefix[] = "poddefault.admission.kubeflow.org/poddefault-";
@@ -334,7 +340,7 @@ NB_HD bool is_marker_key(const PdCtx& x, Span key) {
 
 // One container with env / volumeMounts / envFrom merged and command / args
 // defaulted (applyPodDefaultsOnContainer :561-578, setCommandAndArgs :582-597).
-NB_HD void plan_pd_container(Planner& P, PdCtx& x, Span ctr, AddList& la, AddList& lb) {
+NB_FN void plan_pd_container(Planner& P, PdCtx& x, Span ctr, AddList& la, AddList& lb) {
   const Doc& pod = *x.pod;
   const DocCtx& c = *x.c;
   const bool istio = str_eq(pod, find(pod, ctr, "name"), "istio-proxy");

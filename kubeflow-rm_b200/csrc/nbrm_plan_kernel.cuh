@@ -1,0 +1,137 @@
+// nbrm_plan_kernel.cuh — the plan kernel template and its launcher.  Each
+// generator instantiates it in a translation unit of its own (gen_*.cu) so the
+// generators compile in parallel: in one unit the build took 28 minutes.
+#pragma once
+#include "nbrm_dev.h"
+
+namespace nbrm {
+
+// One input tuple per thread (document i of every input slot in use).  Writes,
+// for each of G::NOBJ output objects, the segment list, its byte length and the
+// segment count; plus one status word per tuple.
+//
+// The documents of a block's tuples are contiguous in each input arena, so the
+// block first copies that range of every slot into shared memory with aligned
+// 16-byte loads (coalesced, each input byte read from HBM once) and the
+// planners then walk shared memory.  Walking global memory directly makes every
+// byte access of a warp touch 32 different cache lines, which is what bounded
+// the first version of this kernel.  A block whose documents do not fit (a
+// Notebook with a huge annotation) walks global memory instead.
+extern __shared__ __align__(16) char plan_smem[];
+
+template <class G>
+__global__ void plan_kernel(PlanIn in, PlanOut out, uint32_t smem_cap) {
+  const uint32_t b0 = blockIdx.x * blockDim.x;
+  const uint32_t b1 = min(b0 + blockDim.x, in.n);
+  const uint32_t i = b0 + threadIdx.x;
+
+  // the block's byte range in every slot, widened to 16-byte boundaries
+  uint64_t g0[3], a0[3];
+  uint32_t soff[3], total = 0;
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    g0[k] = a0[k] = 0;
+    soff[k] = total;
+    if (in.slot[k].data && !(G::SHARED1 && k == 1)) {
+      g0[k] = in.slot[k].off[b0];
+      const uint64_t g1 = in.slot[k].off[b1];
+      a0[k] = g0[k] & ~15ull;
+      const uint64_t a1 = (g1 + 15ull) & ~15ull;
+      const uint64_t bytes = a1 - a0[k];
+      total = bytes > 0xffffffffull - total ? 0xffffffffu : total + (uint32_t)bytes;
+    }
+  }
+  const bool staged = smem_cap != 0 && total <= smem_cap;
+  if (staged) {
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      if (!in.slot[k].data || (G::SHARED1 && k == 1)) continue;
+      const uint32_t chunks = ((k < 2 ? soff[k + 1] : total) - soff[k]) >> 4;
+      const uint4* src = reinterpret_cast<const uint4*>(in.slot[k].data + a0[k]);
+      uint4* dst = reinterpret_cast<uint4*>(plan_smem + soff[k]);
+      for (uint32_t c = threadIdx.x; c < chunks; c += blockDim.x) dst[c] = src[c];
+    }
+  }
+  __syncthreads();
+  if (i >= in.n) return;
+
+  DocCtx c;
+  uint32_t aux_abs = i * AUX_PAD, aux_cap = AUX_PAD;
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    if (in.slot[k].data && !(G::SHARED1 && k == 1)) {
+      const uint64_t o0 = in.slot[k].off[i], o1 = in.slot[k].off[i + 1];
+      c.d[k].p = staged ? plan_smem + soff[k] + (uint32_t)(o0 - a0[k]) : in.slot[k].data + o0;
+      c.d[k].n = (uint32_t)(o1 - o0);
+      c.base[k] = (uint32_t)o0;
+      aux_abs += (uint32_t)o0;
+      aux_cap += c.d[k].n;
+    } else {
+      c.d[k].p = nullptr;
+      c.d[k].n = 0;
+      c.base[k] = 0;
+    }
+  }
+  c.aux.abs = aux_abs;
+  c.aux.p = out.aux + aux_abs;
+  c.aux.cap = aux_cap;
+  c.aux.used = 0;
+  c.env = &in.env;
+  c.flags = in.flags;
+  c.index = i;
+  c.extra = in.extra;
+  c.now = in.now;
+  c.arg0 = in.arg0;
+  c.arg1 = in.arg1;
+  c.result = 0;
+  c.shared = G::SHARED1 ? in.slot[1].data : nullptr;
+  c.shared_off = G::SHARED1 ? in.slot[1].off : nullptr;
+  c.shared_n = G::SHARED1 ? in.shared_n : 0;
+  ObjSink s;
+  s.segs = out.segs + (size_t)i * G::NOBJ * out.cap;
+  s.nseg = out.nseg + (size_t)i * G::NOBJ;
+  s.lens = out.lens + (size_t)i * G::NOBJ;
+  s.cap = out.cap;
+  out.status[i] = G::run(c, s);
+  out.result[i] = c.result;
+}
+
+static const uint32_t PLAN_SMEM = 100 * 1024;  // two blocks per SM
+
+template <class G>
+static void launch(const PlanIn& in, const PlanOut& out, uint64_t in_bytes, cudaStream_t st) {
+  if (!in.n) return;
+  static bool configured = false;  // per instantiation
+  if (!configured) {
+    cudaFuncSetAttribute(plan_kernel<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PLAN_SMEM);
+    configured = true;
+  }
+  // Staging pays while a block's tuples (one per thread) fit: 128 or 64 tuples in
+  // 100 KB.  Larger tuples would leave one warp per block and two blocks per SM,
+  // far too few threads to hide the walk's latency; those run unstaged, 128
+  // threads per block with no shared memory, on the L1/L2 caches.
+  const uint64_t avg = in_bytes / in.n + 48;
+  uint32_t threads = 128;
+  while (threads > 64 && (uint64_t)threads * avg > PLAN_SMEM) threads >>= 1;
+  if ((uint64_t)threads * avg > PLAN_SMEM) {
+    uint32_t blocks = (in.n + 127) / 128;
+    plan_kernel<G><<<blocks, 128, 0, st>>>(in, out, 0);
+    return;
+  }
+  uint32_t blocks = (in.n + threads - 1) / threads;
+  plan_kernel<G><<<blocks, threads, PLAN_SMEM, st>>>(in, out, PLAN_SMEM);
+}
+
+// Defines the two entry points nbrm_plan_kernels.cu dispatches to.
+#define NBRM_DEFINE_GENERATOR(NAME, G)                                                        \
+  void launch_plan_##NAME(const PlanIn& in, const PlanOut& out, uint64_t in_bytes,           \
+                          cudaStream_t st) {                                                  \
+    launch<G>(in, out, in_bytes, st);                                                         \
+  }                                                                                           \
+  void gen_shape_##NAME(uint32_t* nobj, uint32_t* cap, bool* shared1) {                       \
+    *nobj = G::NOBJ;                                                                          \
+    *cap = G::CAP;                                                                            \
+    *shared1 = G::SHARED1;                                                                    \
+  }
+
+}  // namespace nbrm

@@ -1,161 +1,70 @@
-// nbrm_plan_kernels.cu — the plan kernel, instantiated once per generator.
+// nbrm_plan_kernels.cu — dispatch from a generator id to its plan kernel.  The
+// kernels themselves are instantiated in gen_*.cu, one unit per generator.
 #include "nbrm_dev.h"
-#include "nbrm_nbc.cuh"
-#include "nbrm_odh.cuh"
-#include "nbrm_cmp.cuh"
-#include "nbrm_status.cuh"
-#include "nbrm_cull.cuh"
-#include "nbrm_mutate.cuh"
-#include "nbrm_pd.cuh"
-#include "nbrm_profile.cuh"
 
 namespace nbrm {
 
-// One input tuple per thread (document i of every input slot in use).  Writes,
-// for each of G::NOBJ output objects, the segment list, its byte length and the
-// segment count; plus one status word per tuple.
-//
-// The documents of a block's tuples are contiguous in each input arena, so the
-// block first copies that range of every slot into shared memory with aligned
-// 16-byte loads (coalesced, each input byte read from HBM once) and the
-// planners then walk shared memory.  Walking global memory directly makes every
-// byte access of a warp touch 32 different cache lines, which is what bounded
-// the first version of this kernel.  A block whose documents do not fit (a
-// Notebook with a huge annotation) walks global memory instead.
-extern __shared__ __align__(16) char plan_smem[];
-
-template <class G>
-__global__ void plan_kernel(PlanIn in, PlanOut out, uint32_t smem_cap) {
-  const uint32_t b0 = blockIdx.x * blockDim.x;
-  const uint32_t b1 = min(b0 + blockDim.x, in.n);
-  const uint32_t i = b0 + threadIdx.x;
-
-  // the block's byte range in every slot, widened to 16-byte boundaries
-  uint64_t g0[3], a0[3];
-  uint32_t soff[3], total = 0;
-#pragma unroll
-  for (int k = 0; k < 3; ++k) {
-    g0[k] = a0[k] = 0;
-    soff[k] = total;
-    if (in.slot[k].data && !(G::SHARED1 && k == 1)) {
-      g0[k] = in.slot[k].off[b0];
-      const uint64_t g1 = in.slot[k].off[b1];
-      a0[k] = g0[k] & ~15ull;
-      const uint64_t a1 = (g1 + 15ull) & ~15ull;
-      const uint64_t bytes = a1 - a0[k];
-      total = bytes > 0xffffffffull - total ? 0xffffffffu : total + (uint32_t)bytes;
-    }
-  }
-  const bool staged = smem_cap != 0 && total <= smem_cap;
-  if (staged) {
-#pragma unroll
-    for (int k = 0; k < 3; ++k) {
-      if (!in.slot[k].data || (G::SHARED1 && k == 1)) continue;
-      const uint32_t chunks = ((k < 2 ? soff[k + 1] : total) - soff[k]) >> 4;
-      const uint4* src = reinterpret_cast<const uint4*>(in.slot[k].data + a0[k]);
-      uint4* dst = reinterpret_cast<uint4*>(plan_smem + soff[k]);
-      for (uint32_t c = threadIdx.x; c < chunks; c += blockDim.x) dst[c] = src[c];
-    }
-  }
-  __syncthreads();
-  if (i >= in.n) return;
-
-  DocCtx c;
-  uint32_t aux_abs = i * AUX_PAD, aux_cap = AUX_PAD;
-#pragma unroll
-  for (int k = 0; k < 3; ++k) {
-    if (in.slot[k].data && !(G::SHARED1 && k == 1)) {
-      const uint64_t o0 = in.slot[k].off[i], o1 = in.slot[k].off[i + 1];
-      c.d[k].p = staged ? plan_smem + soff[k] + (uint32_t)(o0 - a0[k]) : in.slot[k].data + o0;
-      c.d[k].n = (uint32_t)(o1 - o0);
-      c.base[k] = (uint32_t)o0;
-      aux_abs += (uint32_t)o0;
-      aux_cap += c.d[k].n;
-    } else {
-      c.d[k].p = nullptr;
-      c.d[k].n = 0;
-      c.base[k] = 0;
-    }
-  }
-  c.aux.abs = aux_abs;
-  c.aux.p = out.aux + aux_abs;
-  c.aux.cap = aux_cap;
-  c.aux.used = 0;
-  c.env = &in.env;
-  c.flags = in.flags;
-  c.index = i;
-  c.extra = in.extra;
-  c.now = in.now;
-  c.arg0 = in.arg0;
-  c.arg1 = in.arg1;
-  c.result = 0;
-  c.shared = G::SHARED1 ? in.slot[1].data : nullptr;
-  c.shared_off = G::SHARED1 ? in.slot[1].off : nullptr;
-  c.shared_n = G::SHARED1 ? in.shared_n : 0;
-  ObjSink s;
-  s.segs = out.segs + (size_t)i * G::NOBJ * out.cap;
-  s.nseg = out.nseg + (size_t)i * G::NOBJ;
-  s.lens = out.lens + (size_t)i * G::NOBJ;
-  s.cap = out.cap;
-  out.status[i] = G::run(c, s);
-  out.result[i] = c.result;
-}
-
-static const uint32_t PLAN_SMEM = 100 * 1024;  // two blocks per SM
-
-template <class G>
-static void launch(const PlanIn& in, const PlanOut& out, uint64_t in_bytes, cudaStream_t st) {
-  if (!in.n) return;
-  static bool configured = false;  // per instantiation
-  if (!configured) {
-    cudaFuncSetAttribute(plan_kernel<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PLAN_SMEM);
-    configured = true;
-  }
-  // Staging pays while a block's tuples (one per thread) fit: 128 or 64 tuples in
-  // 100 KB.  Larger tuples would leave one warp per block and two blocks per SM,
-  // far too few threads to hide the walk's latency; those run unstaged, 128
-  // threads per block with no shared memory, on the L1/L2 caches.
-  const uint64_t avg = in_bytes / in.n + 48;
-  uint32_t threads = 128;
-  while (threads > 64 && (uint64_t)threads * avg > PLAN_SMEM) threads >>= 1;
-  if ((uint64_t)threads * avg > PLAN_SMEM) {
-    uint32_t blocks = (in.n + 127) / 128;
-    plan_kernel<G><<<blocks, 128, 0, st>>>(in, out, 0);
-    return;
-  }
-  uint32_t blocks = (in.n + threads - 1) / threads;
-  plan_kernel<G><<<blocks, threads, PLAN_SMEM, st>>>(in, out, PLAN_SMEM);
-}
+void launch_plan_nbc(const PlanIn&, const PlanOut&, uint64_t, cudaStream_t);
+void gen_shape_nbc(uint32_t*, uint32_t*, bool*);
+void launch_plan_odh(const PlanIn&, const PlanOut&, uint64_t, cudaStream_t);
+void gen_shape_odh(uint32_t*, uint32_t*, bool*);
+void launch_plan_copy(const PlanIn&, const PlanOut&, uint64_t, cudaStream_t);
+void gen_shape_copy(uint32_t*, uint32_t*, bool*);
+void launch_plan_status(const PlanIn&, const PlanOut&, uint64_t, cudaStream_t);
+void gen_shape_status(uint32_t*, uint32_t*, bool*);
+void launch_plan_cull(const PlanIn&, const PlanOut&, uint64_t, cudaStream_t);
+void gen_shape_cull(uint32_t*, uint32_t*, bool*);
+void launch_plan_mutate(const PlanIn&, const PlanOut&, uint64_t, cudaStream_t);
+void gen_shape_mutate(uint32_t*, uint32_t*, bool*);
+void launch_plan_guard(const PlanIn&, const PlanOut&, uint64_t, cudaStream_t);
+void gen_shape_guard(uint32_t*, uint32_t*, bool*);
+void launch_plan_poddefault(const PlanIn&, const PlanOut&, uint64_t, cudaStream_t);
+void gen_shape_poddefault(uint32_t*, uint32_t*, bool*);
+void launch_plan_profile(const PlanIn&, const PlanOut&, uint64_t, cudaStream_t);
+void gen_shape_profile(uint32_t*, uint32_t*, bool*);
 
 void launch_plan(int gen, const PlanIn& in, const PlanOut& out, uint64_t in_bytes, cudaStream_t st) {
   switch (gen) {
-    case GEN_ID_NBC: launch<GenNbc>(in, out, in_bytes, st); break;
-    case GEN_ID_ODH: launch<GenOdh>(in, out, in_bytes, st); break;
-    case GEN_ID_COPY: launch<GenCopyFields>(in, out, in_bytes, st); break;
-    case GEN_ID_STATUS: launch<GenStatus>(in, out, in_bytes, st); break;
-    case GEN_ID_CULL: launch<GenCull>(in, out, in_bytes, st); break;
-    case GEN_ID_MUTATE: launch<GenMutate>(in, out, in_bytes, st); break;
-    case GEN_ID_GUARD: launch<GenRestartGuard>(in, out, in_bytes, st); break;
-    case GEN_ID_PODDEFAULT: launch<GenPodDefault>(in, out, in_bytes, st); break;
-    case GEN_ID_PROFILE: launch<GenProfile>(in, out, in_bytes, st); break;
+    case GEN_ID_NBC: launch_plan_nbc(in, out, in_bytes, st); break;
+    case GEN_ID_ODH: launch_plan_odh(in, out, in_bytes, st); break;
+    case GEN_ID_COPY: launch_plan_copy(in, out, in_bytes, st); break;
+    case GEN_ID_STATUS: launch_plan_status(in, out, in_bytes, st); break;
+    case GEN_ID_CULL: launch_plan_cull(in, out, in_bytes, st); break;
+    case GEN_ID_MUTATE: launch_plan_mutate(in, out, in_bytes, st); break;
+    case GEN_ID_GUARD: launch_plan_guard(in, out, in_bytes, st); break;
+    case GEN_ID_PODDEFAULT: launch_plan_poddefault(in, out, in_bytes, st); break;
+    case GEN_ID_PROFILE: launch_plan_profile(in, out, in_bytes, st); break;
   }
+}
+
+static bool shape_of(int gen, uint32_t* nobj, uint32_t* cap, bool* shared1) {
+  switch (gen) {
+    case GEN_ID_NBC: gen_shape_nbc(nobj, cap, shared1); return true;
+    case GEN_ID_ODH: gen_shape_odh(nobj, cap, shared1); return true;
+    case GEN_ID_COPY: gen_shape_copy(nobj, cap, shared1); return true;
+    case GEN_ID_STATUS: gen_shape_status(nobj, cap, shared1); return true;
+    case GEN_ID_CULL: gen_shape_cull(nobj, cap, shared1); return true;
+    case GEN_ID_MUTATE: gen_shape_mutate(nobj, cap, shared1); return true;
+    case GEN_ID_GUARD: gen_shape_guard(nobj, cap, shared1); return true;
+    case GEN_ID_PODDEFAULT: gen_shape_poddefault(nobj, cap, shared1); return true;
+    case GEN_ID_PROFILE: gen_shape_profile(nobj, cap, shared1); return true;
+  }
+  *nobj = 0;
+  *cap = 0;
+  *shared1 = false;
+  return false;
 }
 
 void gen_shape(int gen, uint32_t* nobj, uint32_t* cap) {
-  switch (gen) {
-    case GEN_ID_NBC: *nobj = GenNbc::NOBJ; *cap = GenNbc::CAP; break;
-    case GEN_ID_ODH: *nobj = GenOdh::NOBJ; *cap = GenOdh::CAP; break;
-    case GEN_ID_COPY: *nobj = GenCopyFields::NOBJ; *cap = GenCopyFields::CAP; break;
-    case GEN_ID_STATUS: *nobj = GenStatus::NOBJ; *cap = GenStatus::CAP; break;
-    case GEN_ID_CULL: *nobj = GenCull::NOBJ; *cap = GenCull::CAP; break;
-    case GEN_ID_MUTATE: *nobj = GenMutate::NOBJ; *cap = GenMutate::CAP; break;
-    case GEN_ID_GUARD: *nobj = GenRestartGuard::NOBJ; *cap = GenRestartGuard::CAP; break;
-    case GEN_ID_PODDEFAULT: *nobj = GenPodDefault::NOBJ; *cap = GenPodDefault::CAP; break;
-    case GEN_ID_PROFILE: *nobj = GenProfile::NOBJ; *cap = GenProfile::CAP; break;
-    default: *nobj = 0; *cap = 0;
-  }
+  bool s;
+  shape_of(gen, nobj, cap, &s);
 }
 
-bool gen_shared1(int gen) { return gen == GEN_ID_PODDEFAULT; }
+bool gen_shared1(int gen) {
+  uint32_t a, b;
+  bool s;
+  shape_of(gen, &a, &b, &s);
+  return s;
+}
 
 }  // namespace nbrm
