@@ -260,7 +260,7 @@ def main():
 
     B = args.batch
     # weak scaling: every rank reconciles its own B Notebooks (independent keys, no collective)
-    cb_n = 1500
+    cb_n = 24000   # about 10 s of oracle work on one core
     reqs, found, stss, pods, seeds, items = build_workload(wl, pkg, B, rank * B, cb_n if rank == 0 else 0)
     d_req = pkg.Docs(reqs, pinned=True)
     ctx = pkg.Context(local, env=ENV)
