@@ -1,9 +1,10 @@
 // nbrm_plan.cuh — the plan an object generator writes and the emit kernel reads.
 //
 // Every generator is split in two:
-//   plan  (one document per thread, branchy, reads the input JSON once)
+//   plan  (one input tuple per thread, branchy, reads the input JSON once)
 //         -> a short list of segments per output object + its byte length
-//   emit  (one output object per warp, pure gather-copy, HBM-bound)
+//   emit  (one output object per thread, lanes of a warp on the same object
+//          kind; pure gather-copy)
 //         -> packed output bytes at the offsets an exclusive scan of the
 //            lengths gives
 // A segment is (source buffer, offset, length).  Sources are the input arenas

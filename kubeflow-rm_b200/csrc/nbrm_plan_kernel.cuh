@@ -101,11 +101,9 @@ static const uint32_t PLAN_SMEM = 100 * 1024;  // two blocks per SM
 template <class G>
 static void launch(const PlanIn& in, const PlanOut& out, uint64_t in_bytes, cudaStream_t st) {
   if (!in.n) return;
-  static bool configured = false;  // per instantiation
-  if (!configured) {
-    cudaFuncSetAttribute(plan_kernel<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PLAN_SMEM);
-    configured = true;
-  }
+  // opt in to 100 KB of dynamic shared memory; the attribute belongs to the current
+  // device's context, so it is set on every launch (a process may drive several GPUs)
+  cudaFuncSetAttribute(plan_kernel<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PLAN_SMEM);
   // Staging pays while a block's tuples (one per thread) fit: 128 or 64 tuples in
   // 100 KB.  Larger tuples would leave one warp per block and two blocks per SM,
   // far too few threads to hide the walk's latency; those run unstaged, 128
