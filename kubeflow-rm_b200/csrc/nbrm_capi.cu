@@ -62,6 +62,9 @@ struct Slot {
   DevBuf data, off;
   uint32_t n = 0;
   uint64_t bytes = 0;
+  // documents per producing tuple when the slot holds a generator's result (kinds repeat
+  // with this period: StatefulSet, Service, VirtualService, ...); 1 for uploaded documents
+  uint32_t period = 1;
 };
 
 enum KClass { K_PLAN = 0, K_SCAN = 1, K_EMIT = 2, K_COUNT = 3 };
@@ -91,7 +94,7 @@ struct nbrm_ctx {
   PinBuf h_out, h_off, h_status, h_result, h_total;
 
   // last *_resident result
-  uint32_t res_n_in = 0, res_n_out = 0;
+  uint32_t res_n_in = 0, res_n_out = 0, res_nobj = 1;
   uint64_t res_bytes = 0;
   bool res_valid = false;
 
@@ -319,6 +322,7 @@ int nbrm_upload(nbrm_ctx* c, int slot, const nbrm_docs* d) {
   CK(cudaSetDevice(c->device));
   Slot& s = c->slot[slot];
   s.n = (uint32_t)d->n;
+  s.period = 1;
   uint64_t base = d->n ? d->off[0] : 0;
   if (base != 0) return fail_msg(c, "nbrm_docs: off[0] must be 0");
   s.bytes = d->n ? d->off[d->n] : 0;
@@ -378,6 +382,7 @@ int run_generator(nbrm_ctx* c, int gen, const int (&map)[3], uint32_t flags, con
   in.now = now;
   in.arg0 = arg0;
   in.arg1 = arg1;
+  in.period = map[0] >= 0 ? c->slot[map[0]].period : 1;
   const uint32_t n_out = n * nobj;
   CK(c->segs.reserve((size_t)n_out * cap * sizeof(Seg) + 16));
   CK(c->nseg.reserve((size_t)n_out * 4 + 16));
@@ -434,6 +439,7 @@ int run_generator(nbrm_ctx* c, int gen, const int (&map)[3], uint32_t flags, con
   }
   c->res_n_in = n;
   c->res_n_out = n_out;
+  c->res_nobj = nobj;
   c->res_bytes = total;
   c->res_valid = true;
   return 0;
@@ -523,6 +529,7 @@ int nbrm_result_to_slot(nbrm_ctx* c, int slot) {
   std::swap(s.data, c->out);
   std::swap(s.off, c->out_off);
   s.n = c->res_n_out;
+  s.period = c->res_nobj;
   s.bytes = c->res_bytes;
   c->res_valid = false;
   return 0;

@@ -32,6 +32,7 @@ struct PlanIn {
   uint64_t now;       // caller's clock, Unix seconds
   uint32_t arg0, arg1;
   uint32_t shared_n;  // documents in slot 1 when the generator reads it as a shared arena
+  uint32_t period;    // kinds of document repeat with this period in slot 0 (1 = all alike)
 };
 
 // Where a plan kernel writes.

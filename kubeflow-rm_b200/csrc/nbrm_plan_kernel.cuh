@@ -20,10 +20,23 @@ namespace nbrm {
 extern __shared__ __align__(16) char plan_smem[];
 
 template <class G>
-__global__ void plan_kernel(PlanIn in, PlanOut out, uint32_t smem_cap) {
+__global__ void plan_kernel(PlanIn in, PlanOut out, uint32_t smem_cap, uint32_t period) {
   const uint32_t b0 = blockIdx.x * blockDim.x;
   const uint32_t b1 = min(b0 + blockDim.x, in.n);
-  const uint32_t i = b0 + threadIdx.x;
+  // Tuples whose kinds repeat with period P (the three objects of one Notebook,
+  // one of them ten times the size of the others): threads that run together
+  // take tuples of one residue, so they walk documents of one kind and finish
+  // together instead of idling behind the largest.  Staged: the block has P
+  // warps over 32*P consecutive tuples, warp w takes residue w.  Unstaged: the
+  // whole block takes one residue (block b: residue b % P), so the blocks of the
+  // small kinds retire at once and the SM fills up with warps of the large one.
+  uint32_t i = b0 + threadIdx.x;
+  if (period > 1) {
+    if (smem_cap)
+      i = b0 + (threadIdx.x & 31) * period + (threadIdx.x >> 5);
+    else
+      i = ((blockIdx.x / period) * blockDim.x + threadIdx.x) * period + blockIdx.x % period;
+  }
 
   // the block's byte range in every slot, widened to 16-byte boundaries
   uint64_t g0[3], a0[3];
@@ -32,7 +45,7 @@ __global__ void plan_kernel(PlanIn in, PlanOut out, uint32_t smem_cap) {
   for (int k = 0; k < 3; ++k) {
     g0[k] = a0[k] = 0;
     soff[k] = total;
-    if (in.slot[k].data && !(G::SHARED1 && k == 1)) {
+    if (smem_cap && in.slot[k].data && !(G::SHARED1 && k == 1)) {
       g0[k] = in.slot[k].off[b0];
       const uint64_t g1 = in.slot[k].off[b1];
       a0[k] = g0[k] & ~15ull;
@@ -109,15 +122,27 @@ static void launch(const PlanIn& in, const PlanOut& out, uint64_t in_bytes, cuda
   // far too few threads to hide the walk's latency; those run unstaged, 128
   // threads per block with no shared memory, on the L1/L2 caches.
   const uint64_t avg = in_bytes / in.n + 48;
+  if (in.period > 1 && in.period <= 8) {  // threads that run together take one kind (see plan_kernel)
+    if ((uint64_t)32 * in.period * avg <= PLAN_SMEM) {
+      const uint32_t threads = 32 * in.period;
+      plan_kernel<G><<<(in.n + threads - 1) / threads, threads, PLAN_SMEM, st>>>(in, out, PLAN_SMEM,
+                                                                                 in.period);
+    } else {
+      const uint32_t per_kind = (in.n + in.period - 1) / in.period;
+      const uint32_t blocks = ((per_kind + 127) / 128) * in.period;
+      plan_kernel<G><<<blocks, 128, 0, st>>>(in, out, 0, in.period);
+    }
+    return;
+  }
   uint32_t threads = 128;
   while (threads > 64 && (uint64_t)threads * avg > PLAN_SMEM) threads >>= 1;
   if ((uint64_t)threads * avg > PLAN_SMEM) {
     uint32_t blocks = (in.n + 127) / 128;
-    plan_kernel<G><<<blocks, 128, 0, st>>>(in, out, 0);
+    plan_kernel<G><<<blocks, 128, 0, st>>>(in, out, 0, 1);
     return;
   }
   uint32_t blocks = (in.n + threads - 1) / threads;
-  plan_kernel<G><<<blocks, threads, PLAN_SMEM, st>>>(in, out, PLAN_SMEM);
+  plan_kernel<G><<<blocks, threads, PLAN_SMEM, st>>>(in, out, PLAN_SMEM, 1);
 }
 
 // Defines the two entry points nbrm_plan_kernels.cu dispatches to.
