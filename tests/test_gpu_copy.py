@@ -58,3 +58,33 @@ def test_steady_state_is_silent(ctx, pkg, wl):
     # and with every object missing, everything is created, byte for byte the generated object
     res = ctx.nbc_reconcile(docs, pkg.Docs([b""] * (3 * len(nbs))), 7 | 8)
     assert np.array_equal(res.data, gen.data) and np.array_equal(res.off, gen.off)
+
+
+@pytest.mark.parametrize("pad", [0, 3000])
+@pytest.mark.parametrize("n", [1, 2, 43, 129, 515])
+def test_per_kind_thread_mapping_is_invisible(ctx, pkg, wl, n, pad):
+    """The fused pass knows its desired objects repeat with period 3 and gives the threads
+    that run together one kind each (plan_kernel: per warp when staged, per block when the
+    tuples are too large to stage — pad makes them so).  Results must equal the same compare
+    on uploaded documents, where no period is known, at sizes around the block edges."""
+    ctx.set_env(ENV)
+    rng = random.Random(1000 + n)
+    nbs = wl.corpus("fuzz", n, start=500 + n)
+    for nb in nbs:
+        if pad:
+            nb["metadata"].setdefault("annotations", {})["pad"] = "x" * pad
+    docs = pkg.Docs([wl.dumps(nb) for nb in nbs])
+    gen = ctx.nbc_generate(docs, 7 | 8)
+    gdocs = gen.docs()
+    found = []
+    for g in gdocs:
+        if not g or rng.random() < 0.2:
+            found.append(b"")
+        else:
+            found.append(wl.dumps(wl.found_variant(rng, json.loads(g)), rng))
+    plain = ctx.copy_fields(pkg.Docs(gdocs), pkg.Docs(found))
+    p_docs, p_status = plain.docs(), list(plain.status)
+    fused = ctx.nbc_reconcile(docs, pkg.Docs(found), 7 | 8)
+    assert fused.n == 3 * n
+    assert fused.docs() == p_docs
+    assert list(fused.status) == p_status
