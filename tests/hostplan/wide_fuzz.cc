@@ -1,4 +1,4 @@
-// TEST INFRASTRUCTURE: the 8-bytes-per-load container skip of nbrm_json.cuh (device code
+// TEST INFRASTRUCTURE: the 8-bytes-per-load container skip and span compare of nbrm_json.cuh (device code
 // in the product) compiled by g++ and checked against the byte-at-a-time skip on
 // random JSON-like text, at every alignment.  Prints "ok <cases>" or the first
 // difference; run by tests/test_wide_scanners.py.
@@ -154,6 +154,25 @@ int main() {
         if (want != got) {
           printf("inner skip differs at %u: want %u got %u align %u doc %s\n", i, want, got, align,
                  doc.c_str());
+          return 1;
+        }
+      }
+      // bytes_equal against the obvious loop, both operands at every alignment
+      for (uint32_t balign = 0; balign < 8; ++balign) {
+        char* q = base + 32768 + balign;
+        memcpy(q, doc.data(), doc.size());
+        const uint32_t n = (uint32_t)doc.size();
+        q[n] = (char)(p[n] ^ 1);  // a difference just past the span must not matter
+        ++cases;
+        if (!wide::bytes_equal(p, q, n)) {
+          printf("bytes_equal false on equal spans n %u align %u/%u\n", n, align, balign);
+          return 1;
+        }
+        const uint32_t flip = rnd() % n;
+        q[flip] ^= 1;
+        ++cases;
+        if (wide::bytes_equal(p, q, n)) {
+          printf("bytes_equal true with byte %u flipped n %u align %u/%u\n", flip, n, align, balign);
           return 1;
         }
       }

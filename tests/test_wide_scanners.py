@@ -1,5 +1,5 @@
-"""The 8-bytes-per-load container skip (device code of csrc/nbrm_json.cuh) against the
-byte-at-a-time one.
+"""The 8-bytes-per-load container skip and span compare (device code of
+csrc/nbrm_json.cuh) against the byte-at-a-time ones.
 
 tests/hostplan/wide_fuzz.cc compiles the same source with g++ and drives it over random
 JSON-like documents at every alignment, truncated documents included.  On the GPU the
