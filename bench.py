@@ -291,12 +291,12 @@ def main():
 
     # ---- e2e: host buffers through the C ABI, copies inside the timed region
     for _ in range(args.warmup):
-        out = rp.run(d_req, seeds, copy=False)
+        out = rp.run(d_req, seeds, copy=False, overlap=True)
     barrier()
     ctx.timer_start()
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        out = rp.run(d_req, seeds, copy=False)
+        out = rp.run(d_req, seeds, copy=False, overlap=True)
     ms_e2e_dev = ctx.timer_stop()
     ms_e2e = 1e3 * (time.perf_counter() - t0)
     barrier()
@@ -339,11 +339,11 @@ def main():
     small = pkg.Docs(reqs[:100], pinned=True)
     rp.set_cluster_state(*[pkg.Docs(x) for x in build_workload(wl, pkg, 100, 0, 0)[1:4]])
     for _ in range(5):
-        rp.run(small, seeds[:1600], copy=False)
+        rp.run(small, seeds[:1600], copy=False, overlap=True)
     lat = []
     for _ in range(50):
         t0 = time.perf_counter()
-        rp.run(small, seeds[:1600], copy=False)
+        rp.run(small, seeds[:1600], copy=False, overlap=True)
         lat.append(1e3 * (time.perf_counter() - t0))
     lat.sort()
 

@@ -93,6 +93,7 @@ typedef struct nbrm_out {
 
 /* Accumulated device time per kernel class since nbrm_profile_enable(ctx, 1),
  * measured with CUDA events on the context's stream. */
+#define NBRM_GENERATORS 16 /* size of the per-generator arrays below; ids 0..9 are in use */
 typedef struct nbrm_profile {
   double plan_ms, scan_ms, emit_ms;
   uint64_t plan_launches, scan_launches, emit_launches;
@@ -100,8 +101,8 @@ typedef struct nbrm_profile {
   uint64_t plan_bytes_read;                     /* input bytes the plan kernels walked */
   /* the same per generator id (see nbrm_run): device ms, algorithmic bytes (plan: input
    * bytes read; emit: output bytes read + written), number of runs */
-  double plan_ms_gen[8], emit_ms_gen[8];
-  uint64_t plan_bytes_gen[8], emit_bytes_gen[8], runs_gen[8];
+  double plan_ms_gen[NBRM_GENERATORS], emit_ms_gen[NBRM_GENERATORS];
+  uint64_t plan_bytes_gen[NBRM_GENERATORS], emit_bytes_gen[NBRM_GENERATORS], runs_gen[NBRM_GENERATORS];
 } nbrm_profile;
 
 /* ---- context ---------------------------------------------------------- */
@@ -318,13 +319,36 @@ int nbrm_profile_generate_resident(nbrm_ctx* ctx);
  * slot_b found), 3 status (Notebook, StatefulSet, Pod), 4 culling pass
  * (Notebook, kernels, terminals; arg0/arg1 = idle / period minutes), 5 webhook
  * mutation (flags NBRM_MUT_*), 6 restart guard (mutated, request, old),
- * 7 PodDefault admission (Pods, shared PodDefault arena), 8 Profile objects (8).  use_side_input: pass
+ * 7 PodDefault admission (Pods, shared PodDefault arena), 8 Profile objects (8),
+ * 9 ODH write decision (slot_a desired ODH objects, slot_b found; result word 0 nothing,
+ * 1 create, 2 update: reconcileRoute / reconcileNetworkPolicy / reconcileRoleBinding and the
+ * create-once ServiceAccount, Service, Secret).  use_side_input: pass
  * the bytes of nbrm_upload_bytes (seeds / pod_exists / ranges).  The result is
  * read with nbrm_download or moved on with nbrm_result_to_slot. */
 int nbrm_run(nbrm_ctx* ctx, int generator, int slot_a, int slot_b, int slot_c, uint32_t flags,
              uint64_t now_unix, uint32_t arg0, uint32_t arg1, int use_side_input);
 /* Copy the documents of a slot to host memory (status and result are NULL). */
 int nbrm_download_slot(nbrm_ctx* ctx, int slot, nbrm_out* out);
+
+/* ---- downloads that overlap the next generator ------------------------------
+ * The reference hands each object to the API server as soon as it is built
+ * (r.Create / r.Update, notebook_controller.go:160,176,198,208 and the ODH
+ * reconcilers) and goes on with the next one; the batch equivalent is to send a
+ * finished result to the host while the device already runs the next generator.
+ * nbrm_download_begin takes the current result away from the context (like
+ * nbrm_result_to_slot it is then no longer "the result") and starts copying it
+ * on a second stream into pinned buffers that belong to download lane `lane`
+ * (0 .. NBRM_DL_LANES-1); nbrm_download_slot_begin does the same for the
+ * documents of an input slot, which stay where they are.  nbrm_download_wait
+ * blocks until that lane's copy is complete and fills *out exactly as
+ * nbrm_download / nbrm_download_slot would (same return value: 1 when a status
+ * word is non-zero).  The pointers stay valid until the next *_begin on the
+ * same lane.  A lane holds one download at a time: begin on a lane whose last
+ * download was not waited for is an error (-2). */
+#define NBRM_DL_LANES 4
+int nbrm_download_begin(nbrm_ctx* ctx, int lane);
+int nbrm_download_slot_begin(nbrm_ctx* ctx, int slot, int lane);
+int nbrm_download_wait(nbrm_ctx* ctx, int lane, nbrm_out* out);
 
 /* ---- offsets without allocation -----------------------------------------
  * No counterpart in the reference: this entry point exists for embedders, not

@@ -11,6 +11,7 @@ GEN_ALL = GEN_STS | GEN_SVC | GEN_VS
 ODH_RBAC = 32
 MUT_CREATE, MUT_CA_BUNDLE = 1, 2
 (G_NBC, G_ODH, G_COPY, G_STATUS, G_CULL, G_MUTATE, G_GUARD, G_PODDEFAULT) = range(8)
+G_ODH_DECIDE = 9
 
 STATUS_NAMES = {0: "OK", 1: "E_PARSE", 2: "E_NO_CONTAINERS", 3: "E_SEGS", 4: "E_PORTS_EMPTY",
                 5: "E_NIL_REPLICAS", 6: "E_DENIED", 7: "E_CONFLICT", 8: "E_LIMIT", 9: "E_SELECTOR"}
@@ -42,9 +43,9 @@ class Profile(C.Structure):
                 ("plan_launches", C.c_uint64), ("scan_launches", C.c_uint64),
                 ("emit_launches", C.c_uint64), ("emit_bytes_read", C.c_uint64),
                 ("emit_bytes_written", C.c_uint64), ("plan_bytes_read", C.c_uint64),
-                ("plan_ms_gen", C.c_double * 8), ("emit_ms_gen", C.c_double * 8),
-                ("plan_bytes_gen", C.c_uint64 * 8), ("emit_bytes_gen", C.c_uint64 * 8),
-                ("runs_gen", C.c_uint64 * 8)]
+                ("plan_ms_gen", C.c_double * 16), ("emit_ms_gen", C.c_double * 16),
+                ("plan_bytes_gen", C.c_uint64 * 16), ("emit_bytes_gen", C.c_uint64 * 16),
+                ("runs_gen", C.c_uint64 * 16)]
 
 
 # reference process environment (nbrm_env) key -> struct field
@@ -118,6 +119,9 @@ def load_library():
     lib.nbrm_run.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint32, C.c_uint64,
                              C.c_uint32, C.c_uint32, C.c_int]
     lib.nbrm_download_slot.argtypes = [C.c_void_p, C.c_int, C.POINTER(_Out)]
+    lib.nbrm_download_begin.argtypes = [C.c_void_p, C.c_int]
+    lib.nbrm_download_slot_begin.argtypes = [C.c_void_p, C.c_int, C.c_int]
+    lib.nbrm_download_wait.argtypes = [C.c_void_p, C.c_int, C.POINTER(_Out)]
     lib.nbrm_profile_generate.argtypes = [C.c_void_p, C.POINTER(_Docs), C.POINTER(_Out)]
     lib.nbrm_profile_generate_resident.argtypes = [C.c_void_p]
     lib.nbrm_scan_lengths_noalloc.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p,
@@ -353,6 +357,25 @@ class Context:
     def download_slot(self, slot, copy=True):
         o = _Out()
         self._check(self.lib.nbrm_download_slot(self.h, slot, C.byref(o)))
+        return Result(o, copy)
+
+    def odh_decide(self, desired, found, copy=True):
+        """ODH write decision for (desired, found) pairs: result word 0 nothing, 1 create, 2 update."""
+        self.upload(0, desired)
+        self.upload(1, found)
+        self.run(G_ODH_DECIDE, 0, 1)
+        return self.download(copy)
+
+    # --- downloads that overlap the next generator (one at a time per lane, 0..3)
+    def download_begin(self, lane):
+        self._check(self.lib.nbrm_download_begin(self.h, lane))
+
+    def download_slot_begin(self, slot, lane):
+        self._check(self.lib.nbrm_download_slot_begin(self.h, slot, lane))
+
+    def download_wait(self, lane, copy=True):
+        o = _Out()
+        self._check(self.lib.nbrm_download_wait(self.h, lane, C.byref(o)))
         return Result(o, copy)
 
     # --- profile-controller objects

@@ -17,9 +17,10 @@ namespace {
 struct DevBuf {
   void* p = nullptr;
   size_t cap = 0;
-  cudaError_t reserve(size_t n) {
-    if (n <= cap) return cudaSuccess;
-    size_t want = n + n / 4 + 256;
+  cudaError_t reserve(size_t n) { return n <= cap ? cudaSuccess : allocate(n + n / 4 + 256); }
+  // no headroom: for a buffer that must match another one's capacity
+  cudaError_t reserve_exact(size_t n) { return n <= cap ? cudaSuccess : allocate(n); }
+  cudaError_t allocate(size_t want) {
     if (p) cudaFree(p);
     p = nullptr;
     cap = 0;
@@ -67,6 +68,20 @@ struct Slot {
   uint32_t period = 1;
 };
 
+// One download lane (nbrm_download_begin / _wait): the device buffers it took over
+// from the result, its pinned host buffers, and the events that order the copy.
+struct Lane {
+  DevBuf data, off;
+  PinBuf h_out, h_off, h_status, h_result;
+  cudaEvent_t ready = nullptr;   // compute stream: the result is complete
+  cudaEvent_t done = nullptr;    // copy stream: the documents are in host memory
+  cudaEvent_t small = nullptr;   // compute stream: status / result words are in host memory
+  uint32_t n_in = 0, n_out = 0;
+  uint64_t bytes = 0;
+  int src_slot = -1;             // >= 0: the copy reads this input slot
+  bool pending = false;
+};
+
 enum KClass { K_PLAN = 0, K_SCAN = 1, K_EMIT = 2, K_COUNT = 3 };
 
 struct PendingEvent {
@@ -92,6 +107,8 @@ struct nbrm_ctx {
   DevBuf segs, nseg, lens, status, result, aux, out_off, scan_tmp, out, extra;
   uint64_t extra_bytes = 0;
   PinBuf h_out, h_off, h_status, h_result, h_total;
+  Lane lane[NBRM_DL_LANES];
+  cudaStream_t copy_stream = nullptr;
 
   // last *_resident result
   uint32_t res_n_in = 0, res_n_out = 0, res_nobj = 1;
@@ -124,6 +141,31 @@ int fail_msg(nbrm_ctx* c, const char* what) {
     cudaError_t e_ = (call);                       \
     if (e_ != cudaSuccess) return fail(c, #call, e_); \
   } while (0)
+
+// A download lane that is still reading input slot `slot`: finish it before the
+// slot's buffers are replaced.
+int settle_slot_readers(nbrm_ctx* c, int slot) {
+  for (auto& l : c->lane)
+    if (l.pending && l.src_slot == slot) CK(cudaEventSynchronize(l.done));
+  return 0;
+}
+
+int lane_prepare(nbrm_ctx* c, int lane_id, const char* who) {
+  if (lane_id < 0 || lane_id >= NBRM_DL_LANES) return fail_msg(c, "download lane out of range");
+  Lane& l = c->lane[lane_id];
+  if (l.pending) {
+    c->err = std::string(who) + ": the lane's previous download was not waited for";
+    return -2;
+  }
+  CK(cudaSetDevice(c->device));
+  if (!c->copy_stream) CK(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+  if (!l.ready) {
+    CK(cudaEventCreateWithFlags(&l.ready, cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&l.done, cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&l.small, cudaEventDisableTiming));
+  }
+  return 0;
+}
 
 cudaEvent_t get_event(nbrm_ctx* c) {
   if (!c->free_events.empty()) {
@@ -167,12 +209,12 @@ int drain_profile(nbrm_ctx* c) {
     cudaEventElapsedTime(&ms, pe.a, pe.b);
     if (pe.cls == K_PLAN) {
       c->acc.plan_ms += ms;
-      c->acc.plan_ms_gen[pe.gen] += ms;
+      c->acc.plan_ms_gen[pe.gen & (NBRM_GENERATORS - 1)] += ms;
     }
     if (pe.cls == K_SCAN) c->acc.scan_ms += ms;
     if (pe.cls == K_EMIT) {
       c->acc.emit_ms += ms;
-      c->acc.emit_ms_gen[pe.gen] += ms;
+      c->acc.emit_ms_gen[pe.gen & (NBRM_GENERATORS - 1)] += ms;
     }
     c->free_events.push_back(pe.a);
     c->free_events.push_back(pe.b);
@@ -254,6 +296,21 @@ void nbrm_ctx_destroy(nbrm_ctx* c) {
   for (auto b : bufs) b->release();
   PinBuf* pins[] = {&c->h_out, &c->h_off, &c->h_status, &c->h_result, &c->h_total};
   for (auto b : pins) b->release();
+  if (c->copy_stream) {
+    cudaStreamSynchronize(c->copy_stream);
+    cudaStreamDestroy(c->copy_stream);
+  }
+  for (auto& l : c->lane) {
+    l.data.release();
+    l.off.release();
+    l.h_out.release();
+    l.h_off.release();
+    l.h_status.release();
+    l.h_result.release();
+    if (l.ready) cudaEventDestroy(l.ready);
+    if (l.done) cudaEventDestroy(l.done);
+    if (l.small) cudaEventDestroy(l.small);
+  }
   cudaEventDestroy(c->t0);
   cudaEventDestroy(c->t1);
   cudaStreamDestroy(c->stream);
@@ -320,6 +377,7 @@ int nbrm_upload(nbrm_ctx* c, int slot, const nbrm_docs* d) {
   if (slot < 0 || slot >= NBRM_SLOTS) return fail_msg(c, "nbrm_upload: slot out of range");
   if (int r = check_docs(c, d)) return r;
   CK(cudaSetDevice(c->device));
+  if (int r = settle_slot_readers(c, slot)) return r;
   Slot& s = c->slot[slot];
   s.n = (uint32_t)d->n;
   s.period = 1;
@@ -433,9 +491,9 @@ int run_generator(nbrm_ctx* c, int gen, const int (&map)[3], uint32_t flags, con
     c->acc.emit_bytes_read += total;
     c->acc.emit_bytes_written += total;
     c->acc.plan_bytes_read += in_bytes;
-    c->acc.plan_bytes_gen[gen & 7] += in_bytes;
-    c->acc.emit_bytes_gen[gen & 7] += 2 * total;
-    c->acc.runs_gen[gen & 7] += 1;
+    c->acc.plan_bytes_gen[gen & (NBRM_GENERATORS - 1)] += in_bytes;
+    c->acc.emit_bytes_gen[gen & (NBRM_GENERATORS - 1)] += 2 * total;
+    c->acc.runs_gen[gen & (NBRM_GENERATORS - 1)] += 1;
   }
   c->res_n_in = n;
   c->res_n_out = n_out;
@@ -525,6 +583,7 @@ int nbrm_result_to_slot(nbrm_ctx* c, int slot) {
   if (!c) return -2;
   if (slot < 0 || slot >= NBRM_SLOTS) return fail_msg(c, "nbrm_result_to_slot: slot out of range");
   if (!c->res_valid) return fail_msg(c, "nbrm_result_to_slot: no result on this context");
+  if (int r = settle_slot_readers(c, slot)) return r;
   Slot& s = c->slot[slot];
   std::swap(s.data, c->out);
   std::swap(s.off, c->out_off);
@@ -674,6 +733,85 @@ int nbrm_download_slot(nbrm_ctx* c, int slot, nbrm_out* out) {
   out->status = nullptr;
   out->n_status = 0;
   out->result = nullptr;
+  return 0;
+}
+
+int nbrm_download_begin(nbrm_ctx* c, int lane_id) {
+  if (!c) return -2;
+  if (!c->res_valid) return fail_msg(c, "nbrm_download_begin: no result on this context");
+  if (int r = lane_prepare(c, lane_id, "nbrm_download_begin")) return r;
+  Lane& l = c->lane[lane_id];
+  l.n_in = c->res_n_in;
+  l.n_out = c->res_n_out;
+  l.bytes = c->res_bytes;
+  l.src_slot = -1;
+  CK(l.h_out.reserve(l.bytes + 16));
+  CK(l.h_off.reserve(((size_t)l.n_out + 1) * 8));
+  CK(l.h_status.reserve((size_t)l.n_in * 4 + 16));
+  CK(l.h_result.reserve((size_t)l.n_in * 4 + 16));
+  // the buffers that come back to the context must be able to hold what it holds now,
+  // so that after the first pass no generator has to reallocate its output
+  CK(l.data.reserve_exact(c->out.cap));
+  CK(l.off.reserve_exact(c->out_off.cap));
+  // status / result words: small, and the next generator overwrites them, so they
+  // leave on the compute stream, in order
+  if (l.n_in) {
+    CK(cudaMemcpyAsync(l.h_status.p, c->status.p, (size_t)l.n_in * 4, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaMemcpyAsync(l.h_result.p, c->result.p, (size_t)l.n_in * 4, cudaMemcpyDeviceToHost, c->stream));
+  }
+  CK(cudaEventRecord(l.small, c->stream));
+  CK(cudaEventRecord(l.ready, c->stream));
+  std::swap(l.data, c->out);
+  std::swap(l.off, c->out_off);
+  c->res_valid = false;
+  CK(cudaStreamWaitEvent(c->copy_stream, l.ready, 0));
+  if (l.bytes) CK(cudaMemcpyAsync(l.h_out.p, l.data.p, l.bytes, cudaMemcpyDeviceToHost, c->copy_stream));
+  CK(cudaMemcpyAsync(l.h_off.p, l.off.p, ((size_t)l.n_out + 1) * 8, cudaMemcpyDeviceToHost, c->copy_stream));
+  CK(cudaEventRecord(l.done, c->copy_stream));
+  l.pending = true;
+  return 0;
+}
+
+int nbrm_download_slot_begin(nbrm_ctx* c, int slot, int lane_id) {
+  if (!c) return -2;
+  if (slot < 0 || slot >= NBRM_SLOTS) return fail_msg(c, "nbrm_download_slot_begin: slot out of range");
+  Slot& s = c->slot[slot];
+  if (!s.off.p) return fail_msg(c, "nbrm_download_slot_begin: the slot is empty");
+  if (int r = lane_prepare(c, lane_id, "nbrm_download_slot_begin")) return r;
+  Lane& l = c->lane[lane_id];
+  l.n_in = 0;
+  l.n_out = s.n;
+  l.bytes = s.bytes;
+  l.src_slot = slot;
+  CK(l.h_out.reserve(l.bytes + 16));
+  CK(l.h_off.reserve(((size_t)l.n_out + 1) * 8));
+  CK(cudaEventRecord(l.small, c->stream));
+  CK(cudaEventRecord(l.ready, c->stream));
+  CK(cudaStreamWaitEvent(c->copy_stream, l.ready, 0));
+  if (l.bytes) CK(cudaMemcpyAsync(l.h_out.p, s.data.p, l.bytes, cudaMemcpyDeviceToHost, c->copy_stream));
+  CK(cudaMemcpyAsync(l.h_off.p, s.off.p, ((size_t)l.n_out + 1) * 8, cudaMemcpyDeviceToHost, c->copy_stream));
+  CK(cudaEventRecord(l.done, c->copy_stream));
+  l.pending = true;
+  return 0;
+}
+
+int nbrm_download_wait(nbrm_ctx* c, int lane_id, nbrm_out* out) {
+  if (!c || !out) return -2;
+  if (lane_id < 0 || lane_id >= NBRM_DL_LANES) return fail_msg(c, "download lane out of range");
+  Lane& l = c->lane[lane_id];
+  if (!l.pending) return fail_msg(c, "nbrm_download_wait: nothing was begun on this lane");
+  CK(cudaSetDevice(c->device));
+  CK(cudaEventSynchronize(l.small));
+  CK(cudaEventSynchronize(l.done));
+  l.pending = false;
+  out->data = reinterpret_cast<const char*>(l.h_out.p);
+  out->off = reinterpret_cast<const uint64_t*>(l.h_off.p);
+  out->n = l.n_out;
+  out->status = l.n_in ? reinterpret_cast<const uint32_t*>(l.h_status.p) : nullptr;
+  out->n_status = l.n_in;
+  out->result = l.n_in ? reinterpret_cast<const uint32_t*>(l.h_result.p) : nullptr;
+  for (uint32_t i = 0; i < l.n_in; ++i)
+    if (out->status[i]) return 1;
   return 0;
 }
 

@@ -22,6 +22,8 @@ void launch_plan_poddefault(const PlanIn&, const PlanOut&, uint64_t, cudaStream_
 void gen_shape_poddefault(uint32_t*, uint32_t*, bool*);
 void launch_plan_profile(const PlanIn&, const PlanOut&, uint64_t, cudaStream_t);
 void gen_shape_profile(uint32_t*, uint32_t*, bool*);
+void launch_plan_odhdecide(const PlanIn&, const PlanOut&, uint64_t, cudaStream_t);
+void gen_shape_odhdecide(uint32_t*, uint32_t*, bool*);
 
 void launch_plan(int gen, const PlanIn& in, const PlanOut& out, uint64_t in_bytes, cudaStream_t st) {
   switch (gen) {
@@ -34,6 +36,7 @@ void launch_plan(int gen, const PlanIn& in, const PlanOut& out, uint64_t in_byte
     case GEN_ID_GUARD: launch_plan_guard(in, out, in_bytes, st); break;
     case GEN_ID_PODDEFAULT: launch_plan_poddefault(in, out, in_bytes, st); break;
     case GEN_ID_PROFILE: launch_plan_profile(in, out, in_bytes, st); break;
+    case GEN_ID_ODHDECIDE: launch_plan_odhdecide(in, out, in_bytes, st); break;
   }
 }
 
@@ -48,6 +51,7 @@ static bool shape_of(int gen, uint32_t* nobj, uint32_t* cap, bool* shared1) {
     case GEN_ID_GUARD: gen_shape_guard(nobj, cap, shared1); return true;
     case GEN_ID_PODDEFAULT: gen_shape_poddefault(nobj, cap, shared1); return true;
     case GEN_ID_PROFILE: gen_shape_profile(nobj, cap, shared1); return true;
+    case GEN_ID_ODHDECIDE: gen_shape_odhdecide(nobj, cap, shared1); return true;
   }
   *nobj = 0;
   *cap = 0;

@@ -14,10 +14,12 @@ Slot layout on the context (all device-resident between passes):
   5 requests (the Notebooks as submitted)     0 mutated Notebooks (output of 1)
   1 found StatefulSet/Service/VirtualService  2 desired objects (scratch of 3)
   3 found StatefulSets (for status)           4 Pods "<name>-0"
+  6 found ODH objects, 7 per Notebook (optional)   7 desired ODH objects (scratch of 2)
 """
 from . import capi
 
 SLOT_NOTEBOOKS, SLOT_FOUND, SLOT_DESIRED, SLOT_STS, SLOT_PODS, SLOT_REQUESTS = 0, 1, 2, 3, 4, 5
+SLOT_ODH_FOUND, SLOT_ODH_DESIRED = 6, 7
 STAGES = ["NotebookWebhook.Handle(CREATE): lock + OAuth sidecar",
           "ODH desired objects: 2 NetworkPolicies, Route, ServiceAccount, Service, Secret",
           "generateStatefulSet/Service/VirtualService + SetControllerReference",
@@ -31,44 +33,68 @@ class ReconcilePass:
         self.now = now
         self.nbc_flags = capi.GEN_ALL | capi.GEN_OWNER_REF
         self.odh_flags = capi.GEN_OWNER_REF | capi.GEN_OWNER_V1
+        self.odh_decide = False
 
-    def set_cluster_state(self, found, stss, pods):
-        """The informer-cache side: found objects (3 per Notebook), StatefulSets and Pods."""
+    def set_cluster_state(self, found, stss, pods, odh_found=None):
+        """The informer-cache side: found objects (3 per Notebook), StatefulSets and Pods;
+        optionally the found ODH objects (7 per Notebook, empty = NotFound): with them the
+        "odh" result is what the ODH reconcilers write (create / update / nothing) instead
+        of every desired object."""
         self.ctx.upload(SLOT_FOUND, found)
         self.ctx.upload(SLOT_STS, stss)
         self.ctx.upload(SLOT_PODS, pods)
+        self.odh_decide = odh_found is not None
+        if self.odh_decide:
+            self.ctx.upload(SLOT_ODH_FOUND, odh_found)
 
     def upload_requests(self, requests, seeds=None):
         self.ctx.upload(SLOT_REQUESTS, requests)
         self.ctx.upload_bytes(seeds)
 
-    def run_resident(self, download=False, copy=True):
+    def run_resident(self, download=False, copy=True, overlap=False):
         """The four stages on resident inputs.  Returns the downloaded results when asked
-        (copy=False: views into the context's pinned buffer, each valid until the next download)."""
+        (copy=False: views into the context's pinned buffers, valid until the next pass).
+        overlap=True sends each finished result to the host on the copy stream while the
+        next stage runs (nbrm_download_begin / _wait, one lane per result); the results are
+        the same bytes either way."""
         c = self.ctx
         out = {}
+        lanes = {}
+
+        def fetch(name, lane, slot=None):
+            if not download:
+                return
+            if overlap:
+                if slot is None:
+                    c.download_begin(lane)
+                else:
+                    c.download_slot_begin(slot, lane)
+                lanes[name] = lane
+            else:
+                out[name] = c.download(copy=copy) if slot is None else c.download_slot(slot, copy=copy)
+
         c.run(capi.G_MUTATE, SLOT_REQUESTS, flags=capi.MUT_CREATE)
         c.result_to_slot(SLOT_NOTEBOOKS)
-        if download:
-            out["notebooks"] = c.download_slot(SLOT_NOTEBOOKS, copy=copy)
-            out["notebooks_bytes"] = int(out["notebooks"].off[-1])
+        fetch("notebooks", 0, SLOT_NOTEBOOKS)
         c.run(capi.G_ODH, SLOT_NOTEBOOKS, flags=self.odh_flags, side=True)
-        if download:
-            out["odh"] = c.download(copy=copy)
-            out["odh_bytes"] = int(out["odh"].off[-1])
+        if self.odh_decide:
+            c.result_to_slot(SLOT_ODH_DESIRED)
+            c.run(capi.G_ODH_DECIDE, SLOT_ODH_DESIRED, SLOT_ODH_FOUND)
+        fetch("odh", 1)
         c.run(capi.G_NBC, SLOT_NOTEBOOKS, flags=self.nbc_flags)
         c.result_to_slot(SLOT_DESIRED)
         c.run(capi.G_COPY, SLOT_DESIRED, SLOT_FOUND)
-        if download:
-            out["writes"] = c.download(copy=copy)
-            out["writes_bytes"] = int(out["writes"].off[-1])
+        fetch("writes", 2)
         c.run(capi.G_STATUS, SLOT_NOTEBOOKS, SLOT_STS, SLOT_PODS, now=self.now)
-        if download:
-            out["status"] = c.download(copy=copy)
-            out["status_bytes"] = int(out["status"].off[-1])
+        fetch("status", 3)
+        for name, lane in lanes.items():
+            out[name] = c.download_wait(lane, copy=copy)
+        for name in ("notebooks", "odh", "writes", "status"):
+            if name in out:
+                out[name + "_bytes"] = int(out[name].off[-1])
         return out
 
-    def run(self, requests, seeds=None, copy=True):
+    def run(self, requests, seeds=None, copy=True, overlap=False):
         """Host buffers in, host results out (the e2e path)."""
         self.upload_requests(requests, seeds)
-        return self.run_resident(download=True, copy=copy)
+        return self.run_resident(download=True, copy=copy, overlap=overlap)

@@ -264,6 +264,48 @@ def _stamp(t):
     return datetime.datetime.fromtimestamp(t, datetime.timezone.utc).strftime("%Y-%m-%dT%H:%M:%SZ")
 
 
+
+def odh_found_variant(rng, desired):
+    """A "found" ODH object for `desired` as the API server might return it: None
+    (NotFound), the same object with server-side fields (a Route gets its host from the
+    ingress controller), or one that drifted in labels, spec or subjects.  Used by the
+    ODH write-decision parity tests (odh-notebook-controller/controllers/
+    notebook_route.go:76-139, notebook_network.go:66-122, notebook_rbac.go:89-140)."""
+    import copy
+    if rng.random() < 0.12:
+        return None
+    f = copy.deepcopy(desired)
+    md = f.setdefault("metadata", {})
+    md.update({"uid": "o-%d" % rng.randrange(10**6), "resourceVersion": str(rng.randrange(10**6)),
+               "creationTimestamp": "2026-11-06T00:00:00Z"})
+    kind = desired.get("kind")
+    if kind == "Route":
+        f.setdefault("spec", {})["host"] = "nb-%d.apps.example.com" % rng.randrange(10**4)
+        f["status"] = {"ingress": [{"host": f["spec"]["host"], "routerName": "default"}]}
+    r = rng.random()
+    if r < 0.45:
+        pass
+    elif r < 0.55:
+        md["labels"] = dict(md.get("labels") or {}, drift="1")
+    elif r < 0.6:
+        md.pop("labels", None)
+    elif r < 0.65:
+        md["annotations"] = {"someone": "wrote this"}          # not compared
+    elif r < 0.8 and isinstance(f.get("spec"), dict) and f["spec"]:
+        k = rng.choice(sorted(f["spec"]))
+        if rng.random() < 0.5:
+            del f["spec"][k]
+        else:
+            f["spec"][k] = {"changed": [1, "two", None]}
+    elif r < 0.85 and isinstance(f.get("spec"), dict):
+        f["spec"]["addedByServer"] = {"x": 1}
+    elif r < 0.9 and "subjects" in f:
+        f["subjects"] = f["subjects"] + [{"kind": "User", "name": "eve"}]
+    elif r < 0.93 and "spec" in f:
+        del f["spec"]
+    return f
+
+
 def pod_variant(rng, nb, now=1793966400):
     """A Pod "<name>-0" for the status-mirroring tests, or None (NotFound).
     Shapes after notebook-controller/controllers/notebook_controller_test.go:103-275."""

@@ -218,6 +218,46 @@ def reconcile_objects(nb, ctrl_namespace, rbac=False, cookie_secret="", owner_re
     return out
 
 
+def write_decision(desired, found):
+    """What the ODH reconciler of one object writes, given what it Got:
+    (None, None) | ("create", obj) | ("update", obj).
+      Route           reconcileRoute, notebook_route.go:76-139 (CompareNotebookRoutes :65-72)
+      NetworkPolicy   reconcileNetworkPolicy, notebook_network.go:66-122 (:124-128)
+      ServiceAccount / Service / Secret   notebook_oauth.go:77-113, :151-187, :214-250:
+                      Create when NotFound, otherwise left alone
+      RoleBinding     reconcileRoleBinding, notebook_rbac.go:89-140: Update(desired) when the
+                      subjects differ; the ownerReference is only set on the Create branch.
+    `desired` carries the ownerReference (reconcile_objects), `found` is None for NotFound."""
+    if desired is None:
+        return None, None
+    if found is None:
+        return "create", desired
+    kind = desired.get("kind")
+    if kind in ("Route", "NetworkPolicy"):
+        same = compare_notebook_routes(desired, found) if kind == "Route" \
+            else compare_notebook_network_policies(desired, found)
+        if same:
+            return None, None
+        out = deepcopy(found)
+        if desired.get("spec") is None:
+            out.pop("spec", None)
+        else:
+            out["spec"] = deepcopy(desired["spec"])
+        md = out.setdefault("metadata", {})
+        if meta(desired).get("labels") is None:
+            md.pop("labels", None)
+        else:
+            md["labels"] = deepcopy(meta(desired)["labels"])
+        return "update", out
+    if kind == "RoleBinding":
+        if json_equal(desired.get("subjects"), found.get("subjects")):
+            return None, None
+        out = deepcopy(desired)
+        out.get("metadata", {}).pop("ownerReferences", None)
+        return "update", out
+    return None, None
+
+
 # ---------------------------------------------------------------- webhook mutations
 
 

@@ -6,12 +6,16 @@ CTRL_NS = "redhat-ods-applications"
 
 
 def full_pass(request, found, sts, pod, env, now_str, cookie="", image=odh.OAUTH_PROXY_IMAGE,
-              ctrl_ns=CTRL_NS):
+              ctrl_ns=CTRL_NS, odh_found=None):
     """request: the Notebook as submitted; found: [StatefulSet, Service,
     VirtualService] trees or None each.  Returns (mutated notebook, 7 ODH objects,
-    3 create-or-update results, status)."""
+    3 create-or-update results, status).  With odh_found (7 trees or None each: what the
+    ODH reconcilers Get) the second element is instead the 7 objects those reconcilers
+    write (None = nothing to write), odh.write_decision."""
     mutated, _ = odh.mutate_notebook(request, "CREATE", image=image)
     odh_objs = odh.reconcile_objects(mutated, ctrl_ns, rbac=False, cookie_secret=cookie)
+    if odh_found is not None:
+        odh_objs = [odh.write_decision(d, f)[1] for d, f in zip(odh_objs, odh_found)]
     desired = [nbc.generate_statefulset(mutated, env), nbc.generate_service(mutated, env),
                nbc.generate_virtualservice(mutated, env)]
     writes = []

@@ -13,6 +13,7 @@
 #include "../../kubeflow-rm_b200/csrc/nbrm_nbc.cuh"
 #include "../../kubeflow-rm_b200/csrc/nbrm_odh.cuh"
 #include "../../kubeflow-rm_b200/csrc/nbrm_cmp.cuh"
+#include "../../kubeflow-rm_b200/csrc/nbrm_odhcmp.cuh"
 #include "../../kubeflow-rm_b200/csrc/nbrm_status.cuh"
 #include "../../kubeflow-rm_b200/csrc/nbrm_cull.cuh"
 #include "../../kubeflow-rm_b200/csrc/nbrm_mutate.cuh"
@@ -126,6 +127,7 @@ int hostplan_run(int gen, const char* d0, const uint64_t* o0, const char* d1, co
     case 5: rc = run_host<GenMutate>(data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenMutate::NOBJ; break;
     case 6: rc = run_host<GenRestartGuard>(data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenRestartGuard::NOBJ; break;
     case 7: rc = run_host<GenPodDefault>(data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenPodDefault::NOBJ; break;
+    case 9: rc = run_host<GenOdhDecide>(data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenOdhDecide::NOBJ; break;
     case 8: rc = run_host<GenProfile>(data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenProfile::NOBJ; break;
   }
   *out_data = g_out.data.data();

@@ -5,6 +5,7 @@ import ctypes as C
 import numpy as np
 
 GEN_NBC, GEN_ODH, GEN_COPY, GEN_STATUS, GEN_CULL, GEN_MUTATE, GEN_GUARD, GEN_PD, GEN_PROFILE = 0, 1, 2, 3, 4, 5, 6, 7, 8
+GEN_ODH_DECIDE = 9
 
 
 def _pack(docs_list):
@@ -94,6 +95,11 @@ class HostPlan:
         if ranges is not None:
             extra = np.asarray(ranges, dtype=np.uint32).reshape(-1).tobytes()
         return self.run(GEN_PD, [pods, pds], extra=extra, want_result=True, shared1=True)
+
+    def odh_decide(self, desired_list, found_list):
+        if not desired_list:
+            return [], np.zeros(0, dtype=np.uint32), np.zeros(0, dtype=np.uint32)
+        return self.run(GEN_ODH_DECIDE, [desired_list, found_list], want_result=True)
 
     def profile(self, profiles, env=None):
         return self.run(GEN_PROFILE, [profiles], env)

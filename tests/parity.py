@@ -93,6 +93,31 @@ def check_copy_fields(desired, found, outs, status):
     return n_create, n_update, n_none
 
 
+def check_odh_decide(desired, found, outs, status, result):
+    """desired/found: trees (found None = NotFound, desired None = object not built)."""
+    from oracle import odh
+    n_create = n_update = n_none = 0
+    for i, (d, f) in enumerate(zip(desired, found)):
+        if d is None:
+            assert outs[i] == b"" and status[i] == 0 and result[i] == 0, i
+            continue
+        what, exp = odh.write_decision(d, f)
+        assert status[i] == 0, (i, status[i])
+        assert result[i] == {None: 0, "create": 1, "update": 2}[what], (i, what, result[i])
+        if what is None:
+            assert outs[i] == b"", "pair %d: nothing expected, got %s" % (i, outs[i])
+            n_none += 1
+            continue
+        tree = json.loads(outs[i])
+        assert gojson.canon(tree) == gojson.canon(exp), \
+            "pair %d (%s)\n got %s\n exp %s" % (i, what, gojson.canon(tree), gojson.canon(exp))
+        if what == "create":
+            n_create += 1
+        else:
+            n_update += 1
+    return n_create, n_update, n_none
+
+
 def check_status(nbs, stss, pods, outs, status, now_str):
     n = 0
     for i, (nb, sts, pod) in enumerate(zip(nbs, stss, pods)):

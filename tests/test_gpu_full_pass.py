@@ -4,6 +4,7 @@ import importlib
 import json
 import random
 
+import numpy as np
 import pytest
 
 import __graft_entry__ as graft
@@ -69,4 +70,23 @@ def test_full_pass_matches_oracle(pkg, wl):
         assert gojson.canon(json.loads(status[i])) == gojson.canon(st), i
         checked += 1
     assert checked > 1000
+    # the overlapped downloads (one lane per result, copies on a second stream while the
+    # next stage runs) deliver the same bytes; three passes so the buffers rotate fully
+    for _ in range(3):
+        again = rp.run(d(reqs), seeds, overlap=True)
+        for k in ("notebooks", "odh", "writes", "status"):
+            assert np.array_equal(again[k].off, out[k].off), k
+            assert np.array_equal(again[k].data, out[k].data), k
+            assert np.array_equal(again[k].status, out[k].status), k
+            assert np.array_equal(again[k].result, out[k].result), k
+    # a lane holds one download at a time
+    ctx.run(pkg.G_STATUS, rp_mod.SLOT_NOTEBOOKS, rp_mod.SLOT_STS, rp_mod.SLOT_PODS, now=NOW)
+    ctx.download_begin(0)
+    ctx.run(pkg.G_STATUS, rp_mod.SLOT_NOTEBOOKS, rp_mod.SLOT_STS, rp_mod.SLOT_PODS, now=NOW)
+    with pytest.raises(pkg.NbrmError):
+        ctx.download_begin(0)
+    st = ctx.download_wait(0)
+    assert np.array_equal(st.data, out["status"].data)
+    with pytest.raises(pkg.NbrmError):
+        ctx.download_wait(0)
     ctx.close()
