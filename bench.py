@@ -42,6 +42,7 @@ WORKLOAD = ("configs[1] odh-notebook-controller: OAuth Notebook fixture (100 per
             "ODH reconcile and notebook-controller reconcile, steady-state cluster")
 STAGES = ["NotebookWebhook.Handle(CREATE): lock + OAuth sidecar",
           "ODH desired objects: NetworkPolicies, Route, ServiceAccount, Service, Secret",
+          "ODH write decision vs found objects (reconcileRoute / reconcileNetworkPolicy / create-once)",
           "generateStatefulSet/Service/VirtualService + SetControllerReference",
           "Copy*Fields create-or-update decision vs found objects", "createNotebookStatus"]
 
@@ -113,12 +114,13 @@ def _oracle_chunk(items):
     from oracle import gojson, odh, passes
     now_str = gojson.format_rfc3339(NOW * 10**9)
     n = 0
-    for req, found, pod, seed in items:
+    for req, found, pod, seed, odh_found in items:
         r = json.loads(req)
         f = [json.loads(x) if x else None for x in found]
         p = json.loads(pod) if pod else None
+        of = [json.loads(x) if x else None for x in odh_found]
         mutated, objs, writes, status = passes.full_pass(r, f, f[0], p, ENV, now_str,
-                                                         odh.cookie_secret_from_seed(seed))
+                                                         odh.cookie_secret_from_seed(seed), odh_found=of)
         for o in [mutated, status] + [x for x in objs if x is not None] + [x for x in writes if x is not None]:
             n += len(json.dumps(o, separators=(",", ":")))
     return n
@@ -166,6 +168,15 @@ def build_workload(wl, pkg, n, start, need_items, need_docs=True):
                                              "state": {"running": {"startedAt": "2026-11-06T11:00:05Z"}}},
                                             {"name": "oauth-proxy", "ready": True, "restartCount": 0,
                                              "state": {"running": {"startedAt": "2026-11-06T11:00:06Z"}}}]}}
+    # what the ODH reconcilers Get: the objects as created, plus what the servers add
+    t_odh = []
+    for o in odh.reconcile_objects(mutated, ENV["CONTROLLER_NAMESPACE"], rbac=False, cookie_secret="c3RlYWR5"):
+        if o is not None:
+            o["metadata"]["resourceVersion"] = "7"
+            if o["kind"] == "Route":
+                o["spec"]["host"] = "nb-000000-ns-000.apps.example.com"
+                o["status"] = {"ingress": [{"host": o["spec"]["host"], "routerName": "default"}]}
+        t_odh.append(b"" if o is None else wl.dumps(o))
     t_req = wl.dumps(t_nb)
     t_found = [wl.dumps(d) for d in desired]
     t_pod = wl.dumps(pod)
@@ -175,21 +186,23 @@ def build_workload(wl, pkg, n, start, need_items, need_docs=True):
         md = wl._meta(i)
         return (b.replace(b"nb-000000", md["name"].encode()).replace(b"ns-000", md["namespace"].encode())
                 .replace(uid0, md["uid"].encode()).replace(b'"resourceVersion":"1000"', b'"resourceVersion":"%d"' % (1000 + i)))
-    reqs, found, stss, pods, items = [], [], [], [], []
+    reqs, found, stss, pods, items, odh_found = [], [], [], [], [], []
     seeds = rng.randbytes(16 * n)
     for k in range(n):
         i = start + k
         r = rekey(t_req, i)
         f = [rekey(x, i) for x in t_found]
         p = rekey(t_pod, i)
+        of = [rekey(x, i) for x in t_odh]
         if need_docs:
+            odh_found += of
             reqs.append(r)
             found += f
             stss.append(f[0])
             pods.append(p)
         if need_items and k < need_items:
-            items.append((r, f, p, seeds[16 * k:16 * k + 16]))
-    return reqs, found, stss, pods, seeds, items
+            items.append((r, f, p, seeds[16 * k:16 * k + 16], of))
+    return reqs, found, stss, pods, seeds, items, odh_found
 
 
 def run_reference(args):
@@ -261,12 +274,12 @@ def main():
     B = args.batch
     # weak scaling: every rank reconciles its own B Notebooks (independent keys, no collective)
     cb_n = 24000   # about 10 s of oracle work on one core
-    reqs, found, stss, pods, seeds, items = build_workload(wl, pkg, B, rank * B, cb_n if rank == 0 else 0)
+    reqs, found, stss, pods, seeds, items, odh_found = build_workload(wl, pkg, B, rank * B, cb_n if rank == 0 else 0)
     d_req = pkg.Docs(reqs, pinned=True)
     ctx = pkg.Context(local, env=ENV)
     rp = rmod.ReconcilePass(ctx, NOW)
-    rp.set_cluster_state(pkg.Docs(found), pkg.Docs(stss), pkg.Docs(pods))
-    del found, stss, pods
+    rp.set_cluster_state(pkg.Docs(found), pkg.Docs(stss), pkg.Docs(pods), odh_found=pkg.Docs(odh_found))
+    del found, stss, pods, odh_found
 
     # ---- value: requests and cluster state resident in HBM, kernels only
     rp.upload_requests(d_req, seeds)
@@ -305,12 +318,12 @@ def main():
     e2e_value = world * B * args.steps / (ms_e2e / 1e3)
     h2d = d_req.nbytes + d_req.off.nbytes + len(seeds)
     d2h = sum(out[k] for k in ("notebooks_bytes", "odh_bytes", "writes_bytes", "status_bytes")) \
-        + 8 * (B + 1) + 8 * (7 * B + 1) + 8 * (3 * B + 1) + 8 * (B + 1) + 4 * 2 * 6 * B
-    assert out["writes_bytes"] == 0, "steady state expected: nothing to create or update"
+        + 8 * (B + 1) + 8 * (7 * B + 1) + 8 * (3 * B + 1) + 8 * (B + 1) + 4 * 2 * (7 + 3 + 1) * B
+    assert out["writes_bytes"] == 0 and out["odh_bytes"] == 0, "steady state expected: nothing to create or update"
 
     # ---- roofline of the dominant kernel (CUDA events inside the value loop, per generator)
     peak, peak_kind = load_peaks()
-    names = ["nbc", "odh", "copy_fields", "status", "cull", "mutate", "guard", "poddefault"]
+    names = ["nbc", "odh", "copy_fields", "status", "cull", "mutate", "guard", "poddefault", "profile", "odh_decide"]
     kern = {}
     for g, nm in enumerate(names):
         if prof.runs_gen[g]:
@@ -337,7 +350,8 @@ def main():
 
     # literal configs[1]: 100 Notebooks, latency of one full pass through the C ABI
     small = pkg.Docs(reqs[:100], pinned=True)
-    rp.set_cluster_state(*[pkg.Docs(x) for x in build_workload(wl, pkg, 100, 0, 0)[1:4]])
+    w100 = build_workload(wl, pkg, 100, 0, 0)
+    rp.set_cluster_state(*[pkg.Docs(x) for x in w100[1:4]], odh_found=pkg.Docs(w100[6]))
     for _ in range(5):
         rp.run(small, seeds[:1600], copy=False, overlap=True)
     lat = []
@@ -356,8 +370,10 @@ def main():
         "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
         "config": {"workload": WORKLOAD + " x %d per GPU" % B,
                    "stages": STAGES, "batch_notebooks": B,
-                   "l2": "per step in %.0f MB (requests) + %.0f MB resident cluster state, out %.0f MB: larger than L2"
-                   % (d_req.nbytes / 1e6, 0.0, (d2h) / 1e6),
+                   "l2": "per step %.0f MB of requests in, %.0f MB walked by the plan kernels (requests, generated "
+                         "objects, resident cluster state), %.0f MB of objects written to HBM: larger than L2"
+                   % (d_req.nbytes / 1e6, prof.plan_bytes_read / args.steps / 1e6,
+                      prof.emit_bytes_written / args.steps / 1e6),
                    "literal_100": {"p50_ms": lat[len(lat) // 2], "p99_ms": lat[-1],
                                    "reconciles_per_s": 100 / (lat[len(lat) // 2] / 1e3)}},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,

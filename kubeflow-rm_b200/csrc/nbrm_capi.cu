@@ -186,7 +186,7 @@ struct KScope {  // brackets one kernel class with events when profiling is on
     c->launches += n_launches;
     if (!on) return;
     pe.cls = cls;
-    pe.gen = gen & 7;
+    pe.gen = gen & (NBRM_GENERATORS - 1);
     pe.a = get_event(c);
     pe.b = get_event(c);
     cudaEventRecord(pe.a, c->stream);

@@ -129,25 +129,49 @@ NB_HD uint32_t plan_odh_decide(Planner& P, const Doc& from, const Doc& to) {
     P.in(fr, 0);
     return ODH_CREATE;
   }
-  const Span tr = root(to);
-  const Span kind = FIND(from, fr, "kind");
-  const bool is_route = str_eq(from, kind, "Route");
-  if (is_route || str_eq(from, kind, "NetworkPolicy")) {
-    const Span flabels = FIND(from, FIND(from, fr, "metadata"), "labels");
-    const Span tlabels = FIND(to, FIND(to, tr, "metadata"), "labels");
-    const Span fspec = FIND(from, fr, "spec"), tspec = FIND(to, tr, "spec");
-    bool same = json_equal(from, flabels, to, tlabels);
-    if (same) same = is_route ? route_spec_equal(from, fspec, to, tspec) : json_equal(from, fspec, to, tspec);
-    if (same) return ODH_NONE;
-    plan_spec_labels_update(P, from, fspec, flabels, to);
-    return ODH_UPDATE;
+  // one walk over each root: kind, metadata, spec, subjects
+  Span kind = mk(0, 0), fmeta = mk(0, 0), fspec = mk(0, 0), fsubj = mk(0, 0);
+  {
+    ObjIter it(from, fr);
+    Member m;
+    while (it.next(from, m)) {
+      if (KEY_IS(from, m, "kind")) {
+        kind = m.val;
+        // ServiceAccount, Service, Secret: created once, never compared (kind leads the object)
+        if (!str_eq(from, kind, "Route") && !str_eq(from, kind, "NetworkPolicy") &&
+            !str_eq(from, kind, "RoleBinding"))
+          return ODH_NONE;
+      } else if (KEY_IS(from, m, "metadata")) fmeta = m.val;
+      else if (KEY_IS(from, m, "spec")) fspec = m.val;
+      else if (KEY_IS(from, m, "subjects")) fsubj = m.val;
+    }
   }
-  if (str_eq(from, kind, "RoleBinding")) {
-    if (json_equal(from, FIND(from, fr, "subjects"), to, FIND(to, tr, "subjects"))) return ODH_NONE;
+  const bool is_route = str_eq(from, kind, "Route");
+  const bool is_np = !is_route && str_eq(from, kind, "NetworkPolicy");
+  const bool is_rb = !is_route && !is_np && str_eq(from, kind, "RoleBinding");
+  if (!is_route && !is_np && !is_rb) return ODH_NONE;  // no kind at all
+  Span tmeta = mk(0, 0), tspec = mk(0, 0), tsubj = mk(0, 0);
+  {
+    ObjIter it(to, root(to));
+    Member m;
+    while (it.next(to, m)) {
+      if (KEY_IS(to, m, "metadata")) tmeta = m.val;
+      else if (KEY_IS(to, m, "spec")) tspec = m.val;
+      else if (KEY_IS(to, m, "subjects")) tsubj = m.val;
+    }
+  }
+  if (is_rb) {
+    if (json_equal(from, fsubj, to, tsubj)) return ODH_NONE;
     plan_without_owner(P, from);
     return ODH_UPDATE;
   }
-  return ODH_NONE;  // ServiceAccount, Service, Secret: created once, never compared
+  const Span flabels = FIND(from, fmeta, "labels");
+  const Span tlabels = FIND(to, tmeta, "labels");
+  bool same = json_equal(from, flabels, to, tlabels);
+  if (same) same = is_route ? route_spec_equal(from, fspec, to, tspec) : json_equal(from, fspec, to, tspec);
+  if (same) return ODH_NONE;
+  plan_spec_labels_update(P, from, fspec, flabels, to);
+  return ODH_UPDATE;
 }
 
 // The ODH write decision: slot 0 desired, slot 1 found, one output per pair.

@@ -22,6 +22,7 @@ SLOT_NOTEBOOKS, SLOT_FOUND, SLOT_DESIRED, SLOT_STS, SLOT_PODS, SLOT_REQUESTS = 0
 SLOT_ODH_FOUND, SLOT_ODH_DESIRED = 6, 7
 STAGES = ["NotebookWebhook.Handle(CREATE): lock + OAuth sidecar",
           "ODH desired objects: 2 NetworkPolicies, Route, ServiceAccount, Service, Secret",
+          "ODH write decision vs found ODH objects (when the cluster state has them)",
           "generateStatefulSet/Service/VirtualService + SetControllerReference",
           "Copy*Fields create-or-update decision vs found objects",
           "createNotebookStatus"]
