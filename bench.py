@@ -333,8 +333,8 @@ def main():
     dom_ms, dom_bytes = kern[dom]
     achieved = dom_bytes / (dom_ms / 1e3) / 1e9 if dom_ms > 0 else 0.0
     # DRAM bytes per launch of plan_kernel<copy_fields> from the committed ncu --set full capture
-    # (profiles/r01_ncu_full_v4_full_pass.txt: 1.034 GB read + 0.041 GB written at 65 536 Notebooks)
-    traffic = (1.034422e9 + 41.185024e6) / 65536 * B if dom == "plan_kernel<copy_fields>" else None
+    # (profiles/r01_ncu_full_v5.txt: 924.4 MB read + 24.5 MB written at 65 536 Notebooks)
+    traffic = (924.398336e6 + 24.5248e6) / 65536 * B if dom == "plan_kernel<copy_fields>" else None
     roofline = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": traffic, "peak_kind": peak_kind,
                 "avg_launch_ms": dom_ms, "algorithmic_bytes_per_launch": dom_bytes,
