@@ -129,7 +129,7 @@ uint64_t nbrm_launch_count(const nbrm_ctx* ctx);
  * slots 0..2 as they document; nbrm_run lets a host compose generators over any
  * slots (e.g. keep the found-object cache and the Pods resident in slots of
  * their own while requests stream through another). */
-#define NBRM_SLOTS 8
+#define NBRM_SLOTS 12
 /* Copy a batch into an input slot of the context; it stays in HBM until the
  * slot is overwritten. */
 int nbrm_upload(nbrm_ctx* ctx, int slot, const nbrm_docs* docs);
@@ -329,6 +329,18 @@ int nbrm_run(nbrm_ctx* ctx, int generator, int slot_a, int slot_b, int slot_c, u
              uint64_t now_unix, uint32_t arg0, uint32_t arg1, int use_side_input);
 /* Copy the documents of a slot to host memory (status and result are NULL). */
 int nbrm_download_slot(nbrm_ctx* ctx, int slot, nbrm_out* out);
+
+/* ---- uploads that overlap the running generators -----------------------------
+ * A controller drains its workqueue while the previous batch is still being
+ * reconciled (controller-runtime's workers run concurrently, MaxConcurrentReconciles);
+ * the batch equivalent is to copy the next batch of requests to the device while
+ * the current one runs.  nbrm_upload_async is nbrm_upload on a stream of its own:
+ * generators that read `slot` afterwards wait for the copy on the device, and the
+ * copy waits for the generators already launched that read the slot's previous
+ * documents — so alternate two slots between consecutive batches.  docs->data and
+ * docs->off must be pinned (nbrm_host_alloc) and stay untouched until a generator
+ * that reads the slot has been run and nbrm_sync (or a download) has returned. */
+int nbrm_upload_async(nbrm_ctx* ctx, int slot, const nbrm_docs* docs);
 
 /* ---- downloads that overlap the next generator ------------------------------
  * The reference hands each object to the API server as soon as it is built

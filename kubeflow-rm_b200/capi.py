@@ -119,6 +119,7 @@ def load_library():
     lib.nbrm_run.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint32, C.c_uint64,
                              C.c_uint32, C.c_uint32, C.c_int]
     lib.nbrm_download_slot.argtypes = [C.c_void_p, C.c_int, C.POINTER(_Out)]
+    lib.nbrm_upload_async.argtypes = [C.c_void_p, C.c_int, C.POINTER(_Docs)]
     lib.nbrm_download_begin.argtypes = [C.c_void_p, C.c_int]
     lib.nbrm_download_slot_begin.argtypes = [C.c_void_p, C.c_int, C.c_int]
     lib.nbrm_download_wait.argtypes = [C.c_void_p, C.c_int, C.POINTER(_Out)]
@@ -249,6 +250,12 @@ class Context:
     def upload(self, slot, docs):
         d = docs.c_struct()
         self._check(self.lib.nbrm_upload(self.h, slot, C.byref(d)))
+
+    def upload_async(self, slot, docs):
+        """nbrm_upload on the upload stream; `docs` must be pinned (Docs(..., pinned=True))
+        and alive until a generator that reads the slot has run and been synchronised."""
+        d = docs.c_struct()
+        self._check(self.lib.nbrm_upload_async(self.h, slot, C.byref(d)))
 
     def download(self, copy=True):
         o = _Out()

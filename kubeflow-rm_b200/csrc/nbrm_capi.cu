@@ -66,12 +66,17 @@ struct Slot {
   // documents per producing tuple when the slot holds a generator's result (kinds repeat
   // with this period: StatefulSet, Service, VirtualService, ...); 1 for uploaded documents
   uint32_t period = 1;
+  // nbrm_upload_async: the copy in flight on the upload stream, and the last generator
+  // that read the slot (the next asynchronous copy into it waits for that one)
+  cudaEvent_t uploaded = nullptr, last_read = nullptr;
+  bool upload_pending = false, read_recorded = false;
 };
 
 // One download lane (nbrm_download_begin / _wait): the device buffers it took over
 // from the result, its pinned host buffers, and the events that order the copy.
 struct Lane {
   DevBuf data, off;
+  DevBuf d_status, d_result;     // the lane's copy of the status / result words
   PinBuf h_out, h_off, h_status, h_result;
   cudaEvent_t ready = nullptr;   // compute stream: the result is complete
   cudaEvent_t done = nullptr;    // copy stream: the documents are in host memory
@@ -109,6 +114,7 @@ struct nbrm_ctx {
   PinBuf h_out, h_off, h_status, h_result, h_total;
   Lane lane[NBRM_DL_LANES];
   cudaStream_t copy_stream = nullptr;
+  cudaStream_t up_stream = nullptr;
 
   // last *_resident result
   uint32_t res_n_in = 0, res_n_out = 0, res_nobj = 1;
@@ -147,6 +153,15 @@ int fail_msg(nbrm_ctx* c, const char* what) {
 int settle_slot_readers(nbrm_ctx* c, int slot) {
   for (auto& l : c->lane)
     if (l.pending && l.src_slot == slot) CK(cudaEventSynchronize(l.done));
+  return 0;
+}
+
+// Work queued on the compute stream from here on sees the slot's asynchronous upload.
+int order_after_upload(nbrm_ctx* c, Slot& s) {
+  if (s.upload_pending) {
+    CK(cudaStreamWaitEvent(c->stream, s.uploaded, 0));
+    s.upload_pending = false;
+  }
   return 0;
 }
 
@@ -287,9 +302,15 @@ void nbrm_ctx_destroy(nbrm_ctx* c) {
     cudaEventDestroy(pe.b);
   }
   for (auto e : c->free_events) cudaEventDestroy(e);
+  if (c->up_stream) {
+    cudaStreamSynchronize(c->up_stream);
+    cudaStreamDestroy(c->up_stream);
+  }
   for (auto& s : c->slot) {
     s.data.release();
     s.off.release();
+    if (s.uploaded) cudaEventDestroy(s.uploaded);
+    if (s.last_read) cudaEventDestroy(s.last_read);
   }
   DevBuf* bufs[] = {&c->pool, &c->segs, &c->nseg, &c->lens, &c->status,
                     &c->aux,  &c->out_off, &c->scan_tmp, &c->out, &c->extra, &c->result};
@@ -303,6 +324,8 @@ void nbrm_ctx_destroy(nbrm_ctx* c) {
   for (auto& l : c->lane) {
     l.data.release();
     l.off.release();
+    l.d_status.release();
+    l.d_result.release();
     l.h_out.release();
     l.h_off.release();
     l.h_status.release();
@@ -379,6 +402,7 @@ int nbrm_upload(nbrm_ctx* c, int slot, const nbrm_docs* d) {
   CK(cudaSetDevice(c->device));
   if (int r = settle_slot_readers(c, slot)) return r;
   Slot& s = c->slot[slot];
+  if (int r = order_after_upload(c, s)) return r;
   s.n = (uint32_t)d->n;
   s.period = 1;
   uint64_t base = d->n ? d->off[0] : 0;
@@ -395,6 +419,44 @@ int nbrm_upload(nbrm_ctx* c, int slot, const nbrm_docs* d) {
     CK(cudaMemsetAsync(s.off.p, 0, sizeof(uint64_t), c->stream));
   }
   c->res_valid = false;
+  return 0;
+}
+
+int nbrm_upload_async(nbrm_ctx* c, int slot, const nbrm_docs* d) {
+  if (!c) return -2;
+  if (slot < 0 || slot >= NBRM_SLOTS) return fail_msg(c, "nbrm_upload_async: slot out of range");
+  if (int r = check_docs(c, d)) return r;
+  if (d->n && d->off[0] != 0) return fail_msg(c, "nbrm_docs: off[0] must be 0");
+  CK(cudaSetDevice(c->device));
+  if (int r = settle_slot_readers(c, slot)) return r;
+  Slot& s = c->slot[slot];
+  if (!c->up_stream) CK(cudaStreamCreateWithFlags(&c->up_stream, cudaStreamNonBlocking));
+  if (!s.uploaded) {
+    CK(cudaEventCreateWithFlags(&s.uploaded, cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&s.last_read, cudaEventDisableTiming));
+  }
+  // generators already launched may still read the slot's old contents
+  if (s.read_recorded) CK(cudaStreamWaitEvent(c->up_stream, s.last_read, 0));
+  const uint64_t bytes = d->n ? d->off[d->n] : 0;
+  if (bytes + 16 > s.data.cap || (d->n + 1) * sizeof(uint64_t) > s.off.cap) {
+    // growing frees the old buffer: nothing may be in flight on it
+    CK(cudaStreamSynchronize(c->stream));
+    CK(cudaStreamSynchronize(c->up_stream));
+  }
+  CK(s.data.reserve(bytes + 16));
+  CK(s.off.reserve((d->n + 1) * sizeof(uint64_t)));
+  s.n = (uint32_t)d->n;
+  s.period = 1;
+  s.bytes = bytes;
+  if (bytes) CK(cudaMemcpyAsync(s.data.p, d->data, bytes, cudaMemcpyHostToDevice, c->up_stream));
+  if (d->n) {
+    CK(cudaMemcpyAsync(s.off.p, d->off, (d->n + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice,
+                       c->up_stream));
+  } else {
+    CK(cudaMemsetAsync(s.off.p, 0, sizeof(uint64_t), c->up_stream));
+  }
+  CK(cudaEventRecord(s.uploaded, c->up_stream));
+  s.upload_pending = true;
   return 0;
 }
 
@@ -419,6 +481,7 @@ int run_generator(nbrm_ctx* c, int gen, const int (&map)[3], uint32_t flags, con
     if (map[k] < 0) continue;
     Slot& s = c->slot[map[k]];
     if (!s.off.p) return fail_msg(c, "an input slot this entry point reads was never uploaded");
+    if (int r = order_after_upload(c, s)) return r;
     const bool shared = k == 1 && gen_shared1(gen);
     if (shared) {
       in.shared_n = s.n;
@@ -469,8 +532,10 @@ int run_generator(nbrm_ctx* c, int gen, const int (&map)[3], uint32_t flags, con
     launch_scan(po.lens, n_out, c->scan_tmp.as<uint64_t>(), c->out_off.as<uint64_t>(), c->stream);
   }
   CK(cudaGetLastError());
-  CK(cudaMemcpyAsync(c->h_total.p, c->out_off.as<uint64_t>() + n_out, 8, cudaMemcpyDeviceToHost,
-                     c->stream));
+  // the SM stores the total into pinned host memory (see launch_store_u64)
+  launch_store_u64(c->out_off.as<uint64_t>() + n_out, reinterpret_cast<uint64_t*>(c->h_total.p), c->stream);
+  c->launches += 1;
+  CK(cudaGetLastError());
   CK(cudaStreamSynchronize(c->stream));
   uint64_t total = *reinterpret_cast<uint64_t*>(c->h_total.p);
   if (total >= 0xffffffffull) return fail_msg(c, "output of this batch is 4 GiB or more; split it");
@@ -494,6 +559,14 @@ int run_generator(nbrm_ctx* c, int gen, const int (&map)[3], uint32_t flags, con
     c->acc.plan_bytes_gen[gen & (NBRM_GENERATORS - 1)] += in_bytes;
     c->acc.emit_bytes_gen[gen & (NBRM_GENERATORS - 1)] += 2 * total;
     c->acc.runs_gen[gen & (NBRM_GENERATORS - 1)] += 1;
+  }
+  for (int k = 0; k < 3; ++k) {  // for nbrm_upload_async: this generator read these slots
+    if (map[k] < 0) continue;
+    Slot& s = c->slot[map[k]];
+    if (s.last_read) {
+      CK(cudaEventRecord(s.last_read, c->stream));
+      s.read_recorded = true;
+    }
   }
   c->res_n_in = n;
   c->res_n_out = n_out;
@@ -585,6 +658,7 @@ int nbrm_result_to_slot(nbrm_ctx* c, int slot) {
   if (!c->res_valid) return fail_msg(c, "nbrm_result_to_slot: no result on this context");
   if (int r = settle_slot_readers(c, slot)) return r;
   Slot& s = c->slot[slot];
+  if (int r = order_after_upload(c, s)) return r;
   std::swap(s.data, c->out);
   std::swap(s.off, c->out_off);
   s.n = c->res_n_out;
@@ -722,6 +796,7 @@ int nbrm_download_slot(nbrm_ctx* c, int slot, nbrm_out* out) {
   Slot& s = c->slot[slot];
   if (!s.off.p) return fail_msg(c, "nbrm_download_slot: the slot is empty");
   CK(cudaSetDevice(c->device));
+  if (int r = order_after_upload(c, s)) return r;
   CK(c->h_out.reserve(s.bytes + 16));
   CK(c->h_off.reserve(((size_t)s.n + 1) * 8));
   if (s.bytes) CK(cudaMemcpyAsync(c->h_out.p, s.data.p, s.bytes, cudaMemcpyDeviceToHost, c->stream));
@@ -753,11 +828,16 @@ int nbrm_download_begin(nbrm_ctx* c, int lane_id) {
   // so that after the first pass no generator has to reallocate its output
   CK(l.data.reserve_exact(c->out.cap));
   CK(l.off.reserve_exact(c->out_off.cap));
-  // status / result words: small, and the next generator overwrites them, so they
-  // leave on the compute stream, in order
+  // status / result words: the next generator overwrites them, so the lane takes a copy
+  // on the compute stream (a kernel: a device-to-host copy here would queue behind another
+  // lane's transfer in the copy engine and hold up the generators that follow)
+  CK(l.d_status.reserve((size_t)l.n_in * 4 + 16));
+  CK(l.d_result.reserve((size_t)l.n_in * 4 + 16));
   if (l.n_in) {
-    CK(cudaMemcpyAsync(l.h_status.p, c->status.p, (size_t)l.n_in * 4, cudaMemcpyDeviceToHost, c->stream));
-    CK(cudaMemcpyAsync(l.h_result.p, c->result.p, (size_t)l.n_in * 4, cudaMemcpyDeviceToHost, c->stream));
+    launch_copy_u32(c->status.as<uint32_t>(), l.d_status.as<uint32_t>(), l.n_in, c->stream);
+    launch_copy_u32(c->result.as<uint32_t>(), l.d_result.as<uint32_t>(), l.n_in, c->stream);
+    c->launches += 2;
+    CK(cudaGetLastError());
   }
   CK(cudaEventRecord(l.small, c->stream));
   CK(cudaEventRecord(l.ready, c->stream));
@@ -767,6 +847,10 @@ int nbrm_download_begin(nbrm_ctx* c, int lane_id) {
   CK(cudaStreamWaitEvent(c->copy_stream, l.ready, 0));
   if (l.bytes) CK(cudaMemcpyAsync(l.h_out.p, l.data.p, l.bytes, cudaMemcpyDeviceToHost, c->copy_stream));
   CK(cudaMemcpyAsync(l.h_off.p, l.off.p, ((size_t)l.n_out + 1) * 8, cudaMemcpyDeviceToHost, c->copy_stream));
+  if (l.n_in) {
+    CK(cudaMemcpyAsync(l.h_status.p, l.d_status.p, (size_t)l.n_in * 4, cudaMemcpyDeviceToHost, c->copy_stream));
+    CK(cudaMemcpyAsync(l.h_result.p, l.d_result.p, (size_t)l.n_in * 4, cudaMemcpyDeviceToHost, c->copy_stream));
+  }
   CK(cudaEventRecord(l.done, c->copy_stream));
   l.pending = true;
   return 0;
@@ -778,6 +862,7 @@ int nbrm_download_slot_begin(nbrm_ctx* c, int slot, int lane_id) {
   Slot& s = c->slot[slot];
   if (!s.off.p) return fail_msg(c, "nbrm_download_slot_begin: the slot is empty");
   if (int r = lane_prepare(c, lane_id, "nbrm_download_slot_begin")) return r;
+  if (int r = order_after_upload(c, s)) return r;
   Lane& l = c->lane[lane_id];
   l.n_in = 0;
   l.n_out = s.n;

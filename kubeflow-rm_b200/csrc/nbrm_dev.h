@@ -50,6 +50,8 @@ struct PlanOut {
 void launch_scan(const uint32_t* lens, uint32_t n, uint64_t* tile_tmp, uint64_t* off,
                  cudaStream_t st);
 size_t scan_tmp_bytes(uint32_t n);
+void launch_store_u64(const uint64_t* src, uint64_t* host_dst, cudaStream_t st);
+void launch_copy_u32(const uint32_t* src, uint32_t* dst, uint32_t n, cudaStream_t st);
 void launch_emit(const Seg* segs, const uint32_t* nseg, const uint32_t* lens, const uint64_t* off,
                  uint32_t n_out, uint32_t cap, uint32_t nobj, const SrcBases& bases, char* out,
                  int sm_count, cudaStream_t st);

@@ -110,6 +110,30 @@ void launch_scan(const uint32_t* lens, uint32_t n, uint64_t* tile_tmp, uint64_t*
   scan_write_offsets<<<tiles, SCAN_THREADS, 0, st>>>(lens, n, tile_tmp, off);
 }
 
+// One 8-byte value to pinned host memory, stored by the SM: a cudaMemcpy of it would
+// queue in the device-to-host copy engine behind a download of hundreds of megabytes
+// (nbrm_download_begin) and the host, which needs the value to size the output, with it.
+__global__ void store_u64_kernel(const uint64_t* src, volatile uint64_t* host_dst) {
+  *host_dst = *src;
+  __threadfence_system();
+}
+
+void launch_store_u64(const uint64_t* src, uint64_t* host_dst, cudaStream_t st) {
+  store_u64_kernel<<<1, 1, 0, st>>>(src, host_dst);
+}
+
+// Status / result words into buffers a download lane owns (same reason: no copy engine).
+__global__ void copy_u32_kernel(const uint32_t* __restrict__ src, uint32_t* __restrict__ dst, uint32_t n) {
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+    dst[i] = src[i];
+}
+
+void launch_copy_u32(const uint32_t* src, uint32_t* dst, uint32_t n, cudaStream_t st) {
+  if (!n) return;
+  const uint32_t blocks = (n + 255) / 256 < 592 ? (n + 255) / 256 : 592;
+  copy_u32_kernel<<<blocks, 256, 0, st>>>(src, dst, n);
+}
+
 size_t scan_tmp_bytes(uint32_t n) {
   return sizeof(uint64_t) * ((size_t)(n + SCAN_TILE - 1) / SCAN_TILE + 1);
 }

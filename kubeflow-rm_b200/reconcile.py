@@ -20,6 +20,7 @@ from . import capi
 
 SLOT_NOTEBOOKS, SLOT_FOUND, SLOT_DESIRED, SLOT_STS, SLOT_PODS, SLOT_REQUESTS = 0, 1, 2, 3, 4, 5
 SLOT_ODH_FOUND, SLOT_ODH_DESIRED = 6, 7
+SLOT_REQUESTS_B = 8   # second request buffer of run_pipelined
 STAGES = ["NotebookWebhook.Handle(CREATE): lock + OAuth sidecar",
           "ODH desired objects: 2 NetworkPolicies, Route, ServiceAccount, Service, Secret",
           "ODH write decision vs found ODH objects (when the cluster state has them)",
@@ -52,7 +53,7 @@ class ReconcilePass:
         self.ctx.upload(SLOT_REQUESTS, requests)
         self.ctx.upload_bytes(seeds)
 
-    def run_resident(self, download=False, copy=True, overlap=False):
+    def run_resident(self, download=False, copy=True, overlap=False, request_slot=SLOT_REQUESTS):
         """The four stages on resident inputs.  Returns the downloaded results when asked
         (copy=False: views into the context's pinned buffers, valid until the next pass).
         overlap=True sends each finished result to the host on the copy stream while the
@@ -73,8 +74,10 @@ class ReconcilePass:
                 lanes[name] = lane
             else:
                 out[name] = c.download(copy=copy) if slot is None else c.download_slot(slot, copy=copy)
+                # with copy=False this view is only valid until the next synchronous download
+                out[name + "_bytes"] = int(out[name].off[-1])
 
-        c.run(capi.G_MUTATE, SLOT_REQUESTS, flags=capi.MUT_CREATE)
+        c.run(capi.G_MUTATE, request_slot, flags=capi.MUT_CREATE)
         c.result_to_slot(SLOT_NOTEBOOKS)
         fetch("notebooks", 0, SLOT_NOTEBOOKS)
         c.run(capi.G_ODH, SLOT_NOTEBOOKS, flags=self.odh_flags, side=True)
@@ -90,12 +93,26 @@ class ReconcilePass:
         fetch("status", 3)
         for name, lane in lanes.items():
             out[name] = c.download_wait(lane, copy=copy)
-        for name in ("notebooks", "odh", "writes", "status"):
-            if name in out:
-                out[name + "_bytes"] = int(out[name].off[-1])
+            out[name + "_bytes"] = int(out[name].off[-1])
         return out
 
     def run(self, requests, seeds=None, copy=True, overlap=False):
         """Host buffers in, host results out (the e2e path)."""
         self.upload_requests(requests, seeds)
         return self.run_resident(download=True, copy=copy, overlap=overlap)
+
+    def run_pipelined(self, batches, copy=False):
+        """batches: [(pinned request Docs, seeds), ...].  Yields each batch's results (host
+        buffers in, host results out, like run); the requests of batch i+1 are copied to the
+        device on the upload stream while batch i is being reconciled (nbrm_upload_async on
+        two alternating slots) and results leave on the download lanes.  With copy=False a
+        result is valid until the next batch's results are produced."""
+        slots = (SLOT_REQUESTS, SLOT_REQUESTS_B)
+        if not batches:
+            return
+        self.ctx.upload_async(slots[0], batches[0][0])
+        for i, (_, seeds) in enumerate(batches):
+            if i + 1 < len(batches):
+                self.ctx.upload_async(slots[(i + 1) & 1], batches[i + 1][0])
+            self.ctx.upload_bytes(seeds)
+            yield self.run_resident(download=True, copy=copy, overlap=True, request_slot=slots[i & 1])

@@ -79,6 +79,24 @@ def test_full_pass_matches_oracle(pkg, wl):
             assert np.array_equal(again[k].data, out[k].data), k
             assert np.array_equal(again[k].status, out[k].status), k
             assert np.array_equal(again[k].result, out[k].result), k
+    # pipelined batches (requests of batch i+1 uploaded on a stream of their own while batch i
+    # runs): three different batches, same bytes as one run() per batch
+    third = len(reqs) // 3
+    parts = [(pkg.Docs([wl.dumps(x) for x in reqs[k * third:(k + 1) * third]], pinned=True),
+              seeds[16 * k * third:16 * (k + 1) * third]) for k in range(3)]
+    rp2 = rp_mod.ReconcilePass(ctx, NOW)
+    for k in range(3):
+        lo, hi = k * third, (k + 1) * third
+        rp2.set_cluster_state(d(found[3 * lo:3 * hi]), d(stss[lo:hi]), d(pods[lo:hi]))
+        want = rp2.run(parts[k][0], parts[k][1])
+        got = list(rp2.run_pipelined([parts[k], parts[k]], copy=True))
+        for g in got:
+            for name in ("notebooks", "odh", "writes", "status"):
+                assert np.array_equal(g[name].off, want[name].off), (k, name)
+                assert np.array_equal(g[name].data, want[name].data), (k, name)
+                assert np.array_equal(g[name].status, want[name].status), (k, name)
+    rp.set_cluster_state(d(found), d(stss), d(pods))
+    rp.run(d(reqs), seeds)
     # a lane holds one download at a time
     ctx.run(pkg.G_STATUS, rp_mod.SLOT_NOTEBOOKS, rp_mod.SLOT_STS, rp_mod.SLOT_PODS, now=NOW)
     ctx.download_begin(0)
