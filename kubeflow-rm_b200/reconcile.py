@@ -85,12 +85,15 @@ class ReconcilePass:
             c.result_to_slot(SLOT_ODH_DESIRED)
             c.run(capi.G_ODH_DECIDE, SLOT_ODH_DESIRED, SLOT_ODH_FOUND)
         fetch("odh", 1)
+        # the status depends on the mutated Notebook, its StatefulSet and Pod only; it runs
+        # before the compare so that its download hides under it (the last result, the
+        # write set, is empty in a steady state)
+        c.run(capi.G_STATUS, SLOT_NOTEBOOKS, SLOT_STS, SLOT_PODS, now=self.now)
+        fetch("status", 3)
         c.run(capi.G_NBC, SLOT_NOTEBOOKS, flags=self.nbc_flags)
         c.result_to_slot(SLOT_DESIRED)
         c.run(capi.G_COPY, SLOT_DESIRED, SLOT_FOUND)
         fetch("writes", 2)
-        c.run(capi.G_STATUS, SLOT_NOTEBOOKS, SLOT_STS, SLOT_PODS, now=self.now)
-        fetch("status", 3)
         for name, lane in lanes.items():
             out[name] = c.download_wait(lane, copy=copy)
             out[name + "_bytes"] = int(out[name].off[-1])
