@@ -77,6 +77,10 @@ class ClockSampler(threading.Thread):
          "clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
+        """index: one GPU index, or a comma-separated list (rank 0 samples every GPU of the
+        job in one nvidia-smi call: a sampler per rank means N nvidia-smi processes at a
+        time, each initialising NVML on all GPUs, beside N ranks that synchronise with
+        their GPU six times per step)."""
         super().__init__(daemon=True)
         self.index = index
         self.samples = []
@@ -90,18 +94,20 @@ class ClockSampler(threading.Thread):
                 out = subprocess.run(
                     ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
-                f = [x.strip() for x in out.strip().split(",")]
-                self.samples.append((float(f[0]), float(f[1])))
-                for nm, v in zip(names, f[2:6]):
-                    if v.lower().startswith("active"):
-                        self.reasons.add(nm)
+                for line in out.strip().splitlines():
+                    f = [x.strip() for x in line.split(",")]
+                    self.samples.append((float(f[0]), float(f[1])))
+                    for nm, v in zip(names, f[2:6]):
+                        if v.lower().startswith("active"):
+                            self.reasons.add(nm)
             except Exception:
                 pass
             self.stop_flag.wait(0.1)
 
     def result(self):
         self.stop_flag.set()
-        self.join(timeout=10)
+        if self.is_alive():
+            self.join(timeout=10)
         if not self.samples:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": sorted(self.reasons)}
         return {"sm_mhz": statistics.median(s[0] for s in self.samples),
@@ -288,8 +294,11 @@ def main():
         rp.run_resident()
     ctx.sync()
     ctx.profile_enable(True)
-    sampler = ClockSampler(local)
-    sampler.start()
+    # rank 0 samples the clocks of every GPU of the job; NBRM_BENCH_SAMPLER=all: one per rank
+    per_rank = os.environ.get("NBRM_BENCH_SAMPLER", "rank0") == "all"
+    sampler = ClockSampler(local if per_rank else ",".join(str(i) for i in range(world)))
+    if per_rank or rank == 0:
+        sampler.start()
     l0 = ctx.launch_count()
     barrier()
     ctx.timer_start()

@@ -10,7 +10,8 @@ pkg = graft.load_pkg()
 wl = importlib.import_module(graft.PKG_NAME + ".workload")
 rmod = importlib.import_module(graft.PKG_NAME + ".reconcile")
 B = 131072
-reqs, found, stss, pods, seeds, items, odh_found = bench.build_workload(wl, pkg, B, 0, 0)
+START = int(sys.argv[1]) if len(sys.argv) > 1 else 0   # first Notebook index (rank r of bench.py starts at r * B)
+reqs, found, stss, pods, seeds, items, odh_found = bench.build_workload(wl, pkg, B, START, 0)
 d_req = pkg.Docs(reqs, pinned=True)
 ctx = pkg.Context(0, env=bench.ENV)
 rp = rmod.ReconcilePass(ctx, bench.NOW)
@@ -36,6 +37,13 @@ def kernel_ms(f, n=5):
     p = ctx.profile_read(); ctx.profile_enable(False)
     return wall, (p.plan_ms + p.scan_ms + p.emit_ms) / n
 print("no download:  wall %.2f ms, kernels %.2f ms" % kernel_ms(lambda: rp.run_resident()))
+ctx.profile_enable(True)
+for _ in range(5): rp.run_resident()
+ctx.sync(); p = ctx.profile_read(); ctx.profile_enable(False)
+names = ["nbc", "odh", "copy_fields", "status", "cull", "mutate", "guard", "poddefault", "profile", "odh_decide"]
+print("plan ms per generator:", " ".join("%s=%.2f" % (nm, p.plan_ms_gen[g] / 5) for g, nm in enumerate(names) if p.runs_gen[g]))
+out = rp.run_resident(download=True, copy=True)
+print("bytes out:", {k: v for k, v in out.items() if k.endswith("_bytes")}, "status!=0:", {k: int((out[k].status != 0).sum()) for k in ("odh", "writes", "status")})
 print("overlapped:   wall %.2f ms, kernels %.2f ms" % kernel_ms(lambda: rp.run_resident(download=True, copy=False, overlap=True)))
 def only(names):
     c = ctx
