@@ -181,7 +181,11 @@ int nbrm_result_to_slot(nbrm_ctx* ctx, int slot);
  * the order StatefulSet, Service, VirtualService (empty = NotFound); slot 2 is
  * used for the desired objects.  Output: 3 objects per Notebook as
  * nbrm_copy_fields gives them; in steady state every length is 0 and only the
- * offsets travel back.  The status array then has one entry per object pair. */
+ * offsets travel back.  The status array then has one entry per object pair; a
+ * Notebook the generators rejected (NBRM_E_NO_CONTAINERS, NBRM_E_PORTS_EMPTY,
+ * NBRM_E_PARSE, NBRM_E_SEGS: where the reference panics or errors before it
+ * writes anything) carries that code on all three of its pairs, and the caller
+ * must not go on to the status update for it. */
 int nbrm_nbc_reconcile(nbrm_ctx* ctx, const nbrm_docs* notebooks, const nbrm_docs* found,
                        uint32_t flags, nbrm_out* out);
 int nbrm_nbc_reconcile_resident(nbrm_ctx* ctx, uint32_t flags);
@@ -361,6 +365,21 @@ int nbrm_upload_async(nbrm_ctx* ctx, int slot, const nbrm_docs* docs);
 int nbrm_download_begin(nbrm_ctx* ctx, int lane);
 int nbrm_download_slot_begin(nbrm_ctx* ctx, int slot, int lane);
 int nbrm_download_wait(nbrm_ctx* ctx, int lane, nbrm_out* out);
+
+/* ---- inspection: the structural index --------------------------------------
+ * No counterpart in the reference.  The plan kernels index every input document
+ * before they walk it (kubeflow-rm_b200/csrc/nbrm_tape.cuh: position, kind and
+ * nesting depth of each { } [ ] : , outside strings, plus the links the walkers
+ * hop through).  This call runs that index pass alone over the documents of a
+ * slot and copies the result to host memory, so it can be checked against a
+ * scalar pass over the same text.
+ *   entries  n * cap 64-bit words (low half: pos | kind << 21 | depth << 25,
+ *            high half: the two 16-bit links), document i at entries[i * cap]
+ *   counts   n entry counts (0: the document has no index — over 2 MiB, nested
+ *            deeper than 63, or more than cap entries — and is walked as text)
+ *   flags    n words, bit 0: whitespace occurs between tokens */
+int nbrm_tape_dump(nbrm_ctx* ctx, int slot, uint32_t cap, uint64_t* entries, uint32_t* counts,
+                   uint32_t* flags);
 
 /* ---- offsets without allocation -----------------------------------------
  * No counterpart in the reference: this entry point exists for embedders, not

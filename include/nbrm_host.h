@@ -22,13 +22,14 @@ void nbrm_store_free(nbrm_store* s);
 int nbrm_store_create(nbrm_store* s, const char* json, uint64_t len);
 int nbrm_store_update(nbrm_store* s, const char* json, uint64_t len);
 int nbrm_store_delete(nbrm_store* s, const char* kind, const char* ns, const char* name);
-/* *out is malloc'ed; release with nbrm_host_free. */
+/* *out is malloc'ed; release with nbrm_store_free_string (NOT nbrm_host_free of nbrm.h, which
+ * releases pinned memory of the CUDA runtime: the two libraries are meant to be linked together). */
 int nbrm_store_get(nbrm_store* s, const char* kind, const char* ns, const char* name, char** out,
                    uint64_t* len);
 /* counters[6] = gets, creates, updates, status_updates, deletes, conflicts */
 void nbrm_store_counters(nbrm_store* s, uint64_t* counters, int reset);
 uint64_t nbrm_store_size(nbrm_store* s);
-void nbrm_host_free(void* p);
+void nbrm_store_free_string(char* p);
 
 /* NotebookReconciler.  keys = "namespace/name" entries separated by '\n'.
  * stats[11] = keys, reconciled, not_found, terminating, creates, updates,

@@ -93,6 +93,7 @@ def load_library():
     lib.nbrm_launch_count.argtypes = [C.c_void_p]
     lib.nbrm_launch_count.restype = C.c_uint64
     lib.nbrm_upload.argtypes = [C.c_void_p, C.c_int, C.POINTER(_Docs)]
+    lib.nbrm_tape_dump.argtypes = [C.c_void_p, C.c_int, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.nbrm_download.argtypes = [C.c_void_p, C.POINTER(_Out)]
     lib.nbrm_nbc_generate.argtypes = [C.c_void_p, C.POINTER(_Docs), C.c_uint32, C.POINTER(_Out)]
     lib.nbrm_nbc_generate_resident.argtypes = [C.c_void_p, C.c_uint32]
@@ -365,6 +366,17 @@ class Context:
         o = _Out()
         self._check(self.lib.nbrm_download_slot(self.h, slot, C.byref(o)))
         return Result(o, copy)
+
+    def tape_dump(self, slot, n, cap):
+        """The structural index of every document of `slot` as the plan kernels build it
+        (nbrm_tape_dump; n = documents in the slot): (entries uint64[n, cap], counts uint32[n],
+        flags uint32[n])."""
+        import numpy as np
+        ent = np.zeros((n, cap), dtype=np.uint64)
+        cnt = np.zeros(n, dtype=np.uint32)
+        flg = np.zeros(n, dtype=np.uint32)
+        self._check(self.lib.nbrm_tape_dump(self.h, slot, cap, ent.ctypes.data, cnt.ctypes.data, flg.ctypes.data))
+        return ent, cnt, flg
 
     def odh_decide(self, desired, found, copy=True):
         """ODH write decision for (desired, found) pairs: result word 0 nothing, 1 create, 2 update."""

@@ -110,6 +110,7 @@ struct nbrm_ctx {
 
   Slot slot[NBRM_SLOTS];
   DevBuf segs, nseg, lens, status, result, aux, out_off, scan_tmp, out, extra;
+  DevBuf gen_status;  // nbrm_nbc_reconcile: the generator stage's status words, kept across the compare
   uint64_t extra_bytes = 0;
   PinBuf h_out, h_off, h_status, h_result, h_total;
   Lane lane[NBRM_DL_LANES];
@@ -313,7 +314,7 @@ void nbrm_ctx_destroy(nbrm_ctx* c) {
     if (s.last_read) cudaEventDestroy(s.last_read);
   }
   DevBuf* bufs[] = {&c->pool, &c->segs, &c->nseg, &c->lens, &c->status,
-                    &c->aux,  &c->out_off, &c->scan_tmp, &c->out, &c->extra, &c->result};
+                    &c->aux,  &c->out_off, &c->scan_tmp, &c->out, &c->extra, &c->result, &c->gen_status};
   for (auto b : bufs) b->release();
   PinBuf* pins[] = {&c->h_out, &c->h_off, &c->h_status, &c->h_result, &c->h_total};
   for (auto b : pins) b->release();
@@ -684,8 +685,18 @@ int nbrm_copy_fields(nbrm_ctx* c, const nbrm_docs* desired, const nbrm_docs* fou
 int nbrm_nbc_reconcile_resident(nbrm_ctx* c, uint32_t flags) {
   if (!c) return -2;
   if (int r = run_generator(c, GEN_ID_NBC, {0, -1, -1}, flags, nullptr, 0)) return r;
+  // the compare stage overwrites the status words: keep the generators' (E_NO_CONTAINERS,
+  // E_PORTS_EMPTY, E_PARSE ... where the reference panics before it writes anything)
+  const uint32_t n_nb = c->res_n_in;
+  CK(c->gen_status.reserve((size_t)n_nb * 4 + 16));
+  launch_copy_u32(c->status.as<uint32_t>(), c->gen_status.as<uint32_t>(), n_nb, c->stream);
+  c->launches += n_nb ? 1 : 0;
   if (int r = nbrm_result_to_slot(c, 2)) return r;  // desired objects become input slot 2
-  return run_generator(c, GEN_ID_COPY, {2, 1, -1}, 0, nullptr, 0);
+  if (int r = run_generator(c, GEN_ID_COPY, {2, 1, -1}, 0, nullptr, 0)) return r;
+  launch_merge_status(c->gen_status.as<uint32_t>(), c->status.as<uint32_t>(), c->res_n_in, 3, c->stream);
+  c->launches += c->res_n_in ? 1 : 0;
+  CK(cudaGetLastError());
+  return 0;
 }
 
 int nbrm_nbc_reconcile(nbrm_ctx* c, const nbrm_docs* notebooks, const nbrm_docs* found,
@@ -897,6 +908,38 @@ int nbrm_download_wait(nbrm_ctx* c, int lane_id, nbrm_out* out) {
   out->result = l.n_in ? reinterpret_cast<const uint32_t*>(l.h_result.p) : nullptr;
   for (uint32_t i = 0; i < l.n_in; ++i)
     if (out->status[i]) return 1;
+  return 0;
+}
+
+int nbrm_tape_dump(nbrm_ctx* c, int slot, uint32_t cap, uint64_t* entries, uint32_t* counts, uint32_t* flags) {
+  if (!c || !entries || !counts || !flags) return -2;
+  if (slot < 0 || slot >= NBRM_SLOTS) return fail_msg(c, "nbrm_tape_dump: slot out of range");
+  if (cap == 0 || cap > 24000) return fail_msg(c, "nbrm_tape_dump: cap must be 1..24000 entries");
+  Slot& s = c->slot[slot];
+  if (!s.off.p) return fail_msg(c, "nbrm_tape_dump: the slot is empty");
+  CK(cudaSetDevice(c->device));
+  if (int r = order_after_upload(c, s)) return r;
+  if (!s.n) return 0;
+  DevBuf d_ent, d_cnt, d_flg;
+  cudaError_t e = d_ent.reserve_exact((size_t)s.n * cap * 8);
+  if (e == cudaSuccess) e = d_cnt.reserve_exact((size_t)s.n * 4);
+  if (e == cudaSuccess) e = d_flg.reserve_exact((size_t)s.n * 4);
+  if (e == cudaSuccess) {
+    DevDocs docs;
+    docs.data = s.data.as<char>();
+    docs.off = s.off.as<uint64_t>();
+    launch_tape_dump(docs, s.n, cap, d_ent.p, d_cnt.as<uint32_t>(), d_flg.as<uint32_t>(), c->stream);
+    c->launches += 1;
+    e = cudaGetLastError();
+  }
+  if (e == cudaSuccess) e = cudaMemcpyAsync(entries, d_ent.p, (size_t)s.n * cap * 8, cudaMemcpyDeviceToHost, c->stream);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(counts, d_cnt.p, (size_t)s.n * 4, cudaMemcpyDeviceToHost, c->stream);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(flags, d_flg.p, (size_t)s.n * 4, cudaMemcpyDeviceToHost, c->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+  d_ent.release();
+  d_cnt.release();
+  d_flg.release();
+  if (e != cudaSuccess) return fail(c, "nbrm_tape_dump", e);
   return 0;
 }
 

@@ -136,16 +136,19 @@ NB_HD Span find_key(const Doc& d, Span obj, const Doc& kd, Span key) {
 
 static const int EQ_MAX_DEPTH = 24;
 
+// One open container of the compare: where A's walk stands, and B's side of it.
 struct EqFrame {
-  uint32_t ai, aend;  // cursor in A's container
-  uint32_t bi, bend;  // cursor in B's array (arrays) / B's object span (objects)
-  uint32_t bc;        // objects: cursor in B for the "same order" fast path
+  ObjIter oa, ob;  // objects: A's members; B's members for the "same order" fast path
+  ArrIter aa, ab;  // arrays: both element walks
+  Span bobj;       // objects: B's whole object, for the key search
   uint32_t is_obj;
 };
 
 // nil (absent / null) on both sides is equal; nil vs anything else is not.
+// *overflow is set when the values nest deeper than EQ_MAX_DEPTH: the answer (false) is
+// then not a finding, and the callers report E_LIMIT instead of planning an update.
 template <bool SEM>
-NB_HD bool json_equal_t(const Doc& a, Span x, const Doc& b, Span y) {
+NB_HD bool json_equal_t(const Doc& a, Span x, const Doc& b, Span y, bool* overflow = nullptr) {
   const bool xn = member_is_nil<SEM>(a, x), yn = member_is_nil<SEM>(b, y);
   if (xn || yn) return xn && yn;
   if (spans_eq(a, x, b, y)) return true;  // same text: the common steady-state case, one linear pass
@@ -161,21 +164,23 @@ NB_HD bool json_equal_t(const Doc& a, Span x, const Doc& b, Span y) {
         if (tb != '"' || !str_equal(a, cx, b, cy)) return false;
       } else if (ta == '{') {
         if (tb != '{' || count_members<SEM>(a, cx) != count_members<SEM>(b, cy)) return false;
-        if (sp >= EQ_MAX_DEPTH) return false;
-        st[sp].ai = cx.off + 1;
-        st[sp].aend = cx.end() - 1;
-        st[sp].bi = cy.off;
-        st[sp].bend = cy.end();
-        st[sp].bc = cy.off + 1;
+        if (sp >= EQ_MAX_DEPTH) {
+          if (overflow) *overflow = true;
+          return false;
+        }
+        st[sp].oa = ObjIter(a, cx);
+        st[sp].ob = ObjIter(b, cy);
+        st[sp].bobj = cy;
         st[sp].is_obj = 1;
         ++sp;
       } else if (ta == '[') {
         if (tb != '[') return false;
-        if (sp >= EQ_MAX_DEPTH) return false;
-        st[sp].ai = cx.off + 1;
-        st[sp].aend = cx.end() - 1;
-        st[sp].bi = cy.off + 1;
-        st[sp].bend = cy.end() - 1;
+        if (sp >= EQ_MAX_DEPTH) {
+          if (overflow) *overflow = true;
+          return false;
+        }
+        st[sp].aa = ArrIter(a, cx);
+        st[sp].ab = ArrIter(b, cy);
         st[sp].is_obj = 0;
         ++sp;
       } else {
@@ -186,17 +191,13 @@ NB_HD bool json_equal_t(const Doc& a, Span x, const Doc& b, Span y) {
     if (sp == 0) return true;
     EqFrame& f = st[sp - 1];
     if (f.is_obj) {
-      ObjIter it(a, mk(0, 0));
-      it.i = f.ai;
-      it.end = f.aend;
       Member m;
       bool got = false;
-      while (it.next(a, m)) {
+      while (f.oa.next(a, m)) {
         if (member_is_nil<SEM>(a, m.val)) continue;
         got = true;
         break;
       }
-      f.ai = it.i;
       if (!got) {
         --sp;
         continue;
@@ -205,30 +206,21 @@ NB_HD bool json_equal_t(const Doc& a, Span x, const Doc& b, Span y) {
       // try B's next member before searching B for the key
       Span bv = mk(0, 0);
       {
-        ObjIter ib(b, mk(0, 0));
-        ib.i = f.bc;
-        ib.end = f.bend - 1;
+        ObjIter ib = f.ob;
         Member bm;
         if (ib.next(b, bm) && str_equal(b, bm.key, a, m.key)) {
           bv = bm.val;
-          f.bc = ib.i;
+          f.ob = ib;
         }
       }
-      if (!bv.ok()) bv = find_key(b, mk(f.bi, f.bend - f.bi), a, m.key);
+      if (!bv.ok()) bv = find_key(b, f.bobj, a, m.key);
       if (member_is_nil<SEM>(b, bv)) return false;
       cx = m.val;
       cy = bv;
       have = true;
     } else {
-      ArrIter ia(a, mk(0, 0)), ib(b, mk(0, 0));
-      ia.i = f.ai;
-      ia.end = f.aend;
-      ib.i = f.bi;
-      ib.end = f.bend;
       Span ea, eb;
-      bool ga = ia.next(a, ea), gb = ib.next(b, eb);
-      f.ai = ia.i;
-      f.bi = ib.i;
+      bool ga = f.aa.next(a, ea), gb = f.ab.next(b, eb);
       if (ga != gb) return false;
       if (!ga) {
         --sp;

@@ -52,9 +52,14 @@ void launch_scan(const uint32_t* lens, uint32_t n, uint64_t* tile_tmp, uint64_t*
 size_t scan_tmp_bytes(uint32_t n);
 void launch_store_u64(const uint64_t* src, uint64_t* host_dst, cudaStream_t st);
 void launch_copy_u32(const uint32_t* src, uint32_t* dst, uint32_t n, cudaStream_t st);
+void launch_merge_status(const uint32_t* gen, uint32_t* pair, uint32_t n_pairs, uint32_t per, cudaStream_t st);
 void launch_emit(const Seg* segs, const uint32_t* nseg, const uint32_t* lens, const uint64_t* off,
                  uint32_t n_out, uint32_t cap, uint32_t nobj, const SrcBases& bases, char* out,
                  int sm_count, cudaStream_t st);
+
+// nbrm_tape_debug.cu
+void launch_tape_dump(const DevDocs& docs, uint32_t n, uint32_t cap, void* out, uint32_t* out_nt,
+                      uint32_t* out_flags, cudaStream_t st);
 
 // nbrm_plan_kernels.cu
 enum GenId { GEN_ID_NBC = 0, GEN_ID_ODH = 1, GEN_ID_COPY = 2, GEN_ID_STATUS = 3, GEN_ID_CULL = 4,

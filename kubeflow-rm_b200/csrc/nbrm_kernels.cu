@@ -134,6 +134,23 @@ void launch_copy_u32(const uint32_t* src, uint32_t* dst, uint32_t n, cudaStream_
   copy_u32_kernel<<<blocks, 256, 0, st>>>(src, dst, n);
 }
 
+// nbrm_nbc_reconcile: a Notebook the generators rejected (the reference would have panicked
+// on Containers[0] / Ports[0]) has no desired objects, so the compare stage sees "nothing
+// desired, nothing to do" for its three pairs.  Its generator status goes onto those pairs.
+__global__ void merge_status_kernel(const uint32_t* __restrict__ gen, uint32_t* __restrict__ pair,
+                                    uint32_t n_pairs, uint32_t per) {
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_pairs; i += gridDim.x * blockDim.x) {
+    const uint32_t g = gen[i / per];
+    if (g) pair[i] = g;
+  }
+}
+
+void launch_merge_status(const uint32_t* gen, uint32_t* pair, uint32_t n_pairs, uint32_t per, cudaStream_t st) {
+  if (!n_pairs) return;
+  const uint32_t blocks = (n_pairs + 255) / 256 < 592 ? (n_pairs + 255) / 256 : 592;
+  merge_status_kernel<<<blocks, 256, 0, st>>>(gen, pair, n_pairs, per);
+}
+
 size_t scan_tmp_bytes(uint32_t n) {
   return sizeof(uint64_t) * ((size_t)(n + SCAN_TILE - 1) / SCAN_TILE + 1);
 }

@@ -111,6 +111,104 @@ __global__ void plan_kernel(PlanIn in, PlanOut out, uint32_t smem_cap, uint32_t 
 
 static const uint32_t PLAN_SMEM = 100 * 1024;  // two blocks per SM
 
+#ifdef NBRM_WARP
+// ---------------------------------------------------------------- one tuple per WARP
+// Tape mode (nbrm_tape.cuh).  The warp reads each document of its tuple once, 16 bytes
+// per lane, coalesced, and leaves the structural index in its share of shared memory;
+// then all 32 lanes run the planner together on the same tuple — same branches, same
+// addresses, so a load is one transaction and the stores of the plan collapse into
+// one — hopping through the index instead of scanning.  Bulk byte work inside the
+// planner (span compares) is split across the lanes.  What a warp does depends on its
+// own tuple only: a batch of mixed shapes costs the sum of its tuples, not 32 times the
+// largest of every 32.
+static const uint32_t PLANW_WARPS = 4;
+
+template <class G>
+__global__ void __launch_bounds__(PLANW_WARPS * 32) plan_kernel_warp(PlanIn in, PlanOut out,
+                                                                       uint32_t tape_cap) {
+  extern __shared__ __align__(16) char plan_smem_w[];
+  const uint32_t warp = threadIdx.x >> 5;
+  const uint32_t i = blockIdx.x * PLANW_WARPS + warp;
+  if (i >= in.n) return;
+  TapeEnt* tape = reinterpret_cast<TapeEnt*>(plan_smem_w) + (size_t)warp * tape_cap;
+  TapeScratch* sc =
+      reinterpret_cast<TapeScratch*>(plan_smem_w + (size_t)PLANW_WARPS * tape_cap * sizeof(TapeEnt)) + warp;
+  DocCtx c;
+  uint32_t aux_abs = i * AUX_PAD, aux_cap = AUX_PAD, used = 0;
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    if (in.slot[k].data && !(G::SHARED1 && k == 1)) {
+      const uint64_t o0 = in.slot[k].off[i], o1 = in.slot[k].off[i + 1];
+      c.d[k].p = in.slot[k].data + o0;
+      c.d[k].n = (uint32_t)(o1 - o0);
+      c.base[k] = (uint32_t)o0;
+      aux_abs += (uint32_t)o0;
+      aux_cap += c.d[k].n;
+      uint32_t tf = DOC_WS;
+      const uint32_t nt = build_tape_warp(in.slot[k].data, o0, c.d[k].n, tape + used, tape_cap - used, sc,
+                                          TAPE_MAX_DEPTH, &tf);
+      c.d[k].tape = tape + used;
+      c.d[k].nt = nt;
+      c.d[k].tflags = tf;
+      c.d[k].dlim = TAPE_MAX_DEPTH;
+      used += nt;
+    } else {
+      c.d[k].p = nullptr;
+      c.d[k].n = 0;
+      c.base[k] = 0;
+    }
+  }
+  __syncwarp();
+  c.aux.abs = aux_abs;
+  c.aux.p = out.aux + aux_abs;
+  c.aux.cap = aux_cap;
+  c.aux.used = 0;
+  c.env = &in.env;
+  c.flags = in.flags;
+  c.index = i;
+  c.extra = in.extra;
+  c.now = in.now;
+  c.arg0 = in.arg0;
+  c.arg1 = in.arg1;
+  c.result = 0;
+  c.shared = G::SHARED1 ? in.slot[1].data : nullptr;
+  c.shared_off = G::SHARED1 ? in.slot[1].off : nullptr;
+  c.shared_n = G::SHARED1 ? in.shared_n : 0;
+  ObjSink s;
+  s.segs = out.segs + (size_t)i * G::NOBJ * out.cap;
+  s.nseg = out.nseg + (size_t)i * G::NOBJ;
+  s.lens = out.lens + (size_t)i * G::NOBJ;
+  s.cap = out.cap;
+  const uint32_t st = G::run(c, s);
+  if ((threadIdx.x & 31u) == 0) {
+    out.status[i] = st;
+    out.result[i] = c.result;
+  }
+}
+
+// Tape entries per warp: JSON of API objects has one structural character per 8 to 11
+// bytes; tuples whose kinds repeat with a period (one Notebook's StatefulSet, Service and
+// VirtualService) are far from their average size, hence the factor.  A tuple that does
+// not fit keeps the documents that did and walks the others as text.
+static uint32_t tape_cap_for(uint64_t in_bytes, uint32_t n, uint32_t period) {
+  const uint64_t avg = in_bytes / n + 64;
+  uint64_t cap = (period > 1 ? avg * 5 / 2 : avg * 3 / 2) / 8;
+  if (cap < 192) cap = 192;
+  if (cap > 1536) cap = 1536;
+  return (uint32_t)((cap + 31) & ~31ull);
+}
+
+template <class G>
+static void launch(const PlanIn& in, const PlanOut& out, uint64_t in_bytes, cudaStream_t st) {
+  if (!in.n) return;
+  const uint32_t cap = tape_cap_for(in_bytes, in.n, in.period);
+  const size_t smem = (size_t)PLANW_WARPS * (cap * sizeof(TapeEnt) + sizeof(TapeScratch));
+  cudaFuncSetAttribute(plan_kernel_warp<G>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  const uint32_t blocks = (in.n + PLANW_WARPS - 1) / PLANW_WARPS;
+  plan_kernel_warp<G><<<blocks, PLANW_WARPS * 32, smem, st>>>(in, out, cap);
+}
+#else
+
 template <class G>
 static void launch(const PlanIn& in, const PlanOut& out, uint64_t in_bytes, cudaStream_t st) {
   if (!in.n) return;
@@ -144,6 +242,8 @@ static void launch(const PlanIn& in, const PlanOut& out, uint64_t in_bytes, cuda
   uint32_t blocks = (in.n + threads - 1) / threads;
   plan_kernel<G><<<blocks, threads, PLAN_SMEM, st>>>(in, out, PLAN_SMEM, 1);
 }
+
+#endif  // NBRM_WARP
 
 // Defines the two entry points nbrm_plan_kernels.cu dispatches to.
 #define NBRM_DEFINE_GENERATOR(NAME, G)                                                        \

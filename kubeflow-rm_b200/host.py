@@ -33,7 +33,7 @@ def load_host_library():
     lib.nbrm_store_counters.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.c_int]
     lib.nbrm_store_size.argtypes = [C.c_void_p]
     lib.nbrm_store_size.restype = C.c_uint64
-    lib.nbrm_host_free.argtypes = [C.c_void_p]
+    lib.nbrm_store_free_string.argtypes = [C.c_void_p]
     lib.nbrm_reconciler_new.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int]
     lib.nbrm_reconciler_new.restype = C.c_void_p
     lib.nbrm_reconciler_free.argtypes = [C.c_void_p]
@@ -63,7 +63,7 @@ class Store:
         if rc != 0:
             return None
         b = C.string_at(out.value, n.value)
-        self.lib.nbrm_host_free(out)
+        self.lib.nbrm_store_free_string(out)
         return b
 
     def counters(self, reset=False):

@@ -44,7 +44,7 @@ void nbrm_store_counters(nbrm_store* s, uint64_t* c, int reset) {
   if (reset) s->s.reset_counters();
 }
 uint64_t nbrm_store_size(nbrm_store* s) { return s->s.size(); }
-void nbrm_host_free(void* p) { free(p); }
+void nbrm_store_free_string(char* p) { free(p); }
 
 nbrm_reconciler* nbrm_reconciler_new(nbrm_store* s, nbrm_ctx* ctx, int use_istio, int wic) {
   return new nbrm_reconciler{NotebookReconciler(&s->s, ctx, use_istio != 0, wic != 0)};

@@ -26,14 +26,19 @@ def wl(pkg):
     return importlib.import_module(graft.PKG_NAME + ".workload")
 
 
-@pytest.fixture(scope="session")
-def hostplan():
-    """The g++ build of the planner headers (tests/hostplan), built on demand."""
+@pytest.fixture(scope="session", params=["text", "tape"])
+def hostplan(request):
+    """The g++ build of the planner headers (tests/hostplan), built on demand: once walking
+    the JSON text, once walking the structural index of nbrm_tape.cuh (what the warp-per-tuple
+    kernels do on the GPU, with the scalar index builder in place of the warp's)."""
     import subprocess
     d = os.path.join(ROOT, "tests", "hostplan")
     subprocess.run(["make", "-C", d], check=True, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)
     import hostplan_binding
-    return hostplan_binding.HostPlan(os.path.join(d, "libhostplan.so"))
+    name = "libhostplan.so" if request.param == "text" else "libhostplan_tape.so"
+    hp = hostplan_binding.HostPlan(os.path.join(d, name))
+    assert hp.lib.hostplan_tape_mode() == (request.param == "tape")
+    return hp
 
 
 @pytest.fixture(scope="session")

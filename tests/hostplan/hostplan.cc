@@ -33,6 +33,9 @@ struct Out {
   std::vector<uint32_t> result;
 };
 Out g_out;
+#ifdef NBRM_TAPE
+uint32_t g_tape_cap = 65000;  // entries per document; hostplan_set_tape_cap shrinks it to test the fallback
+#endif
 
 template <class G>
 int run_host(const char* const data[3], const uint64_t* const off[3], uint64_t n, const nbrm_env* env,
@@ -56,6 +59,9 @@ int run_host(const char* const data[3], const uint64_t* const off[3], uint64_t n
   for (uint64_t i = 0; i < n; ++i) {
     DocCtx c;
     uint32_t aux_abs = (uint32_t)i * AUX_PAD, aux_cap = AUX_PAD;
+#ifdef NBRM_TAPE
+    std::vector<TapeEnt> tapes[3];
+#endif
     for (int k = 0; k < 3; ++k) {
       if (data[k] && !(G::SHARED1 && k == 1)) {
         c.d[k].p = data[k] + off[k][i];
@@ -63,6 +69,13 @@ int run_host(const char* const data[3], const uint64_t* const off[3], uint64_t n
         c.base[k] = (uint32_t)off[k][i];
         aux_abs += (uint32_t)off[k][i];
         aux_cap += c.d[k].n;
+#ifdef NBRM_TAPE
+        // tape mode: the scalar builder stands in for the warp's index pass
+        tapes[k].resize(c.d[k].n + 1);
+        c.d[k].nt = build_tape_scalar(c.d[k].p, c.d[k].n, tapes[k].data(), g_tape_cap, &c.d[k].tflags);
+        c.d[k].tape = tapes[k].data();
+        c.d[k].dlim = TAPE_MAX_DEPTH;
+#endif
       } else {
         c.d[k].p = nullptr;
         c.d[k].n = 0;
@@ -106,10 +119,39 @@ int run_host(const char* const data[3], const uint64_t* const off[3], uint64_t n
 }
 }  // namespace
 
+#define HP_API __attribute__((visibility("default")))
+
 extern "C" {
 
+HP_API int hostplan_tape_mode(void) {
+#ifdef NBRM_TAPE
+  return 1;
+#else
+  return 0;
+#endif
+}
+
+HP_API void hostplan_set_tape_cap(uint32_t cap) {
+#ifdef NBRM_TAPE
+  g_tape_cap = cap;
+#else
+  (void)cap;
+#endif
+}
+
+// The scalar index builder on one document (tape build only); returns the entry count.
+HP_API uint32_t hostplan_build_tape(const char* p, uint32_t n, uint64_t* out, uint32_t cap, uint32_t* flags) {
+#ifdef NBRM_TAPE
+  static_assert(sizeof(TapeEnt) == 8, "entries are 64-bit words");
+  return build_tape_scalar(p, n, reinterpret_cast<TapeEnt*>(out), cap, flags);
+#else
+  (void)p; (void)n; (void)out; (void)cap; (void)flags;
+  return 0;
+#endif
+}
+
 // gen: 0 notebook-controller (3 objects), 1 ODH reconcile (7), 2 Copy*Fields (1), 3 status (1), 4 culling (1)
-int hostplan_run(int gen, const char* d0, const uint64_t* o0, const char* d1, const uint64_t* o1,
+HP_API int hostplan_run(int gen, const char* d0, const uint64_t* o0, const char* d1, const uint64_t* o1,
                  const char* d2, const uint64_t* o2, uint64_t n, const nbrm_env* env, uint32_t flags,
                  const void* extra, uint64_t now, uint32_t arg0, uint32_t arg1, uint32_t shared_n,
                  uint32_t* nobj,

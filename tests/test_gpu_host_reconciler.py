@@ -131,11 +131,49 @@ def test_event_reissue(pkg, wl):
     store.create(wl.dumps({"apiVersion": "v1", "kind": "Event", "metadata": {"name": "ev-x", "namespace": ns},
                            "involvedObject": {"kind": "Node", "name": "n1"}, "type": "Normal", "reason": "r",
                            "message": "m"}))
-    rc, st = rec.reconcile(keys + [(ns, "ev-x")], NOW)
-    assert st["events_reissued"] == len(g["cases"]) and rc == 1 and st["reconciled"] == 0
+    # a message with quotes, a backslash and a newline: the re-issued Event is built from the
+    # stored text, escapes and all, and must stay valid JSON with the same decoded message
+    nasty = 'Back-off pulling image "quay.io/x:1" at C:\\dir\nretrying, said "no"'
+    store.create(wl.dumps({"apiVersion": "v1", "kind": "Event", "metadata": {"name": "ev-q", "namespace": ns},
+                           "involvedObject": {"kind": "StatefulSet", "name": "test-notebook", "namespace": ns},
+                           "type": "Warning", "reason": 'Back"Off', "message": nasty}))
+    rc, st = rec.reconcile(keys + [(ns, "ev-x"), (ns, "ev-q")], NOW)
+    assert st["events_reissued"] == len(g["cases"]) + 1 and rc == 1 and st["reconciled"] == 0
+    out = json.loads(store.get("Event", ns, "test-notebook.ev-q"))
+    assert out["message"] == "Reissued from statefulset/test-notebook: " + nasty and out["reason"] == 'Back"Off'
     for i, c in enumerate(g["cases"]):
         out = json.loads(store.get("Event", ns, "%s.ev-%d" % (c["expected"], i)))
         assert out["involvedObject"]["name"] == c["expected"] and out["involvedObject"]["kind"] == "Notebook"
         kind = c["involvedObject"]["kind"].lower()
         assert out["message"] == "Reissued from %s/%s: 0/1 nodes are available" % (kind, c["involvedObject"]["name"])
+    rec.close(); store.close(); ctx.close()
+
+
+def test_rejected_notebooks_stop_before_the_status_write(pkg, wl):
+    """`containers: []` and `ports: []`: the reference panics on Containers[0] / Ports[0]
+    (notebook_controller.go:455,491) and never reaches Status().Update.  ReconcileBatch
+    reports an error for those keys, writes nothing for them, and still reconciles the
+    healthy Notebook of the same batch."""
+    host = importlib.import_module(graft.PKG_NAME + ".host")
+    ctx = pkg.Context(0, env=ENV)
+    store = host.Store()
+    rec = host.NotebookReconciler(store, ctx, use_istio=True)
+    ns = "default"
+    good = wl.notebook_c1(1)
+    good["metadata"].update(name="good", namespace=ns)
+    empty = wl.notebook_c1(2)
+    empty["metadata"].update(name="no-containers", namespace=ns)
+    empty["spec"]["template"]["spec"]["containers"] = []
+    ports = wl.notebook_c1(3)
+    ports["metadata"].update(name="no-ports", namespace=ns)
+    ports["spec"]["template"]["spec"]["containers"][0]["ports"] = []
+    for nb in (good, empty, ports):
+        store.create(wl.dumps(nb))
+    rc, st = rec.reconcile([(ns, "no-containers"), (ns, "good"), (ns, "no-ports")], NOW)
+    assert rc == 2 and st["errors"] == 2 and st["reconciled"] == 3
+    assert st["status_updates"] == 1 and st["creates"] == 3
+    assert store.get("StatefulSet", ns, "good") is not None
+    for name in ("no-containers", "no-ports"):
+        assert store.get("StatefulSet", ns, name) is None and store.get("Service", ns, name) is None
+        assert "status" not in json.loads(store.get("Notebook", ns, name))
     rec.close(); store.close(); ctx.close()
