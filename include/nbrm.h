@@ -366,6 +366,20 @@ int nbrm_download_begin(nbrm_ctx* ctx, int lane);
 int nbrm_download_slot_begin(nbrm_ctx* ctx, int slot, int lane);
 int nbrm_download_wait(nbrm_ctx* ctx, int lane, nbrm_out* out);
 
+/* ---- resident documents: index once ------------------------------------------
+ * No counterpart in the reference as a function; it is what the reference's
+ * informer cache does for it: objects that stay around (the found StatefulSets,
+ * Services, Pods ... a reconcile compares against) are decoded when they arrive,
+ * not on every reconcile.  nbrm_slot_index runs the structural index pass
+ * (kubeflow-rm_b200/csrc/nbrm_tape.cuh) over the documents of a slot and keeps
+ * the result in device memory beside them; every later generator that reads
+ * the slot hops through that index instead of scanning the text.  Results are
+ * byte-identical with and without it.  The index is dropped when the slot's
+ * contents change (nbrm_upload, nbrm_upload_async, nbrm_result_to_slot);
+ * calling this again on an indexed slot does nothing.  Cost: about one pass
+ * over the slot's bytes, plus device memory of 1.6x the slot's bytes. */
+int nbrm_slot_index(nbrm_ctx* ctx, int slot);
+
 /* ---- inspection: the structural index --------------------------------------
  * No counterpart in the reference.  The plan kernels index every input document
  * before they walk it (kubeflow-rm_b200/csrc/nbrm_tape.cuh: position, kind and

@@ -93,6 +93,7 @@ def load_library():
     lib.nbrm_launch_count.argtypes = [C.c_void_p]
     lib.nbrm_launch_count.restype = C.c_uint64
     lib.nbrm_upload.argtypes = [C.c_void_p, C.c_int, C.POINTER(_Docs)]
+    lib.nbrm_slot_index.argtypes = [C.c_void_p, C.c_int]
     lib.nbrm_tape_dump.argtypes = [C.c_void_p, C.c_int, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.nbrm_download.argtypes = [C.c_void_p, C.POINTER(_Out)]
     lib.nbrm_nbc_generate.argtypes = [C.c_void_p, C.POINTER(_Docs), C.c_uint32, C.POINTER(_Out)]
@@ -366,6 +367,11 @@ class Context:
         o = _Out()
         self._check(self.lib.nbrm_download_slot(self.h, slot, C.byref(o)))
         return Result(o, copy)
+
+    def slot_index(self, slot):
+        """Index the slot's documents once (nbrm_slot_index): for documents that stay resident
+        while many batches are planned against them."""
+        self._check(self.lib.nbrm_slot_index(self.h, slot))
 
     def tape_dump(self, slot, n, cap):
         """The structural index of every document of `slot` as the plan kernels build it

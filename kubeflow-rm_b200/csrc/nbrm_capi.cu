@@ -70,6 +70,12 @@ struct Slot {
   // that read the slot (the next asynchronous copy into it waits for that one)
   cudaEvent_t uploaded = nullptr, last_read = nullptr;
   bool upload_pending = false, read_recorded = false;
+  // structural index of the slot's documents (nbrm_slot_index), valid until the contents change
+  DevBuf tape, tidx, tcursor;
+  bool indexed = false;
+  // views the producing generator left of the slot's documents (nbrm_plan.cuh), moved here by nbrm_result_to_slot
+  DevBuf views;
+  bool has_views = false;
 };
 
 // One download lane (nbrm_download_begin / _wait): the device buffers it took over
@@ -110,6 +116,9 @@ struct nbrm_ctx {
 
   Slot slot[NBRM_SLOTS];
   DevBuf segs, nseg, lens, status, result, aux, out_off, scan_tmp, out, extra;
+  DevBuf views;       // views of the last result's objects (generators that write them)
+  bool res_views = false;
+  size_t views_max = 0;  // view buffers rotate between the context and the slots: all grow to the largest asked for
   DevBuf gen_status;  // nbrm_nbc_reconcile: the generator stage's status words, kept across the compare
   uint64_t extra_bytes = 0;
   PinBuf h_out, h_off, h_status, h_result, h_total;
@@ -310,11 +319,15 @@ void nbrm_ctx_destroy(nbrm_ctx* c) {
   for (auto& s : c->slot) {
     s.data.release();
     s.off.release();
+    s.tape.release();
+    s.tidx.release();
+    s.tcursor.release();
+    s.views.release();
     if (s.uploaded) cudaEventDestroy(s.uploaded);
     if (s.last_read) cudaEventDestroy(s.last_read);
   }
   DevBuf* bufs[] = {&c->pool, &c->segs, &c->nseg, &c->lens, &c->status,
-                    &c->aux,  &c->out_off, &c->scan_tmp, &c->out, &c->extra, &c->result, &c->gen_status};
+                    &c->aux,  &c->out_off, &c->scan_tmp, &c->out, &c->extra, &c->result, &c->gen_status, &c->views};
   for (auto b : bufs) b->release();
   PinBuf* pins[] = {&c->h_out, &c->h_off, &c->h_status, &c->h_result, &c->h_total};
   for (auto b : pins) b->release();
@@ -404,6 +417,8 @@ int nbrm_upload(nbrm_ctx* c, int slot, const nbrm_docs* d) {
   if (int r = settle_slot_readers(c, slot)) return r;
   Slot& s = c->slot[slot];
   if (int r = order_after_upload(c, s)) return r;
+  s.indexed = false;
+  s.has_views = false;
   s.n = (uint32_t)d->n;
   s.period = 1;
   uint64_t base = d->n ? d->off[0] : 0;
@@ -446,6 +461,8 @@ int nbrm_upload_async(nbrm_ctx* c, int slot, const nbrm_docs* d) {
   }
   CK(s.data.reserve(bytes + 16));
   CK(s.off.reserve((d->n + 1) * sizeof(uint64_t)));
+  s.indexed = false;
+  s.has_views = false;
   s.n = (uint32_t)d->n;
   s.period = 1;
   s.bytes = bytes;
@@ -493,6 +510,11 @@ int run_generator(nbrm_ctx* c, int gen, const int (&map)[3], uint32_t flags, con
     }
     in.slot[k].data = s.data.as<char>();
     in.slot[k].off = s.off.as<uint64_t>();
+    if (s.indexed && !shared) {
+      in.slot[k].tape = s.tape.p;
+      in.slot[k].tidx = s.tidx.as<uint2>();
+    }
+    if (s.has_views && !shared) in.slot[k].views = s.views.as<ViewEnt>();
     in_bytes += s.bytes;
   }
   if (in_bytes + (uint64_t)n * AUX_PAD >= 0xffffffffull)
@@ -523,6 +545,15 @@ int run_generator(nbrm_ctx* c, int gen, const int (&map)[3], uint32_t flags, con
   po.result = c->result.as<uint32_t>();
   po.aux = c->aux.as<char>();
   po.cap = cap;
+  po.views = nullptr;
+  c->res_views = false;
+  if (gen_views(gen)) {
+    const size_t want = (size_t)n_out * VIEW_FIELDS * sizeof(ViewEnt) + 16;
+    if (want > c->views_max) c->views_max = want + want / 4;
+    CK(c->views.reserve_exact(c->views_max));
+    po.views = c->views.as<ViewEnt>();
+    c->res_views = true;
+  }
   {
     KScope k(c, K_PLAN, n ? 1 : 0, gen);
     launch_plan(gen, in, po, in_bytes, c->stream);
@@ -662,6 +693,10 @@ int nbrm_result_to_slot(nbrm_ctx* c, int slot) {
   if (int r = order_after_upload(c, s)) return r;
   std::swap(s.data, c->out);
   std::swap(s.off, c->out_off);
+  std::swap(s.views, c->views);
+  s.has_views = c->res_views;
+  c->res_views = false;
+  s.indexed = false;
   s.n = c->res_n_out;
   s.period = c->res_nobj;
   s.bytes = c->res_bytes;
@@ -911,6 +946,32 @@ int nbrm_download_wait(nbrm_ctx* c, int lane_id, nbrm_out* out) {
   return 0;
 }
 
+int nbrm_slot_index(nbrm_ctx* c, int slot) {
+  if (!c) return -2;
+  if (slot < 0 || slot >= NBRM_SLOTS) return fail_msg(c, "nbrm_slot_index: slot out of range");
+  Slot& s = c->slot[slot];
+  if (!s.off.p) return fail_msg(c, "nbrm_slot_index: the slot is empty");
+  CK(cudaSetDevice(c->device));
+  if (int r = order_after_upload(c, s)) return r;
+  if (s.indexed || !s.n) return 0;
+  // API objects have one structural character per 8 to 11 bytes of compact JSON; room for
+  // one per 5 bytes.  Documents that find the arena full simply stay without an index.
+  const uint64_t want = s.bytes / 5 + (uint64_t)s.n * 8 + 64;
+  const uint32_t arena_cap = want > 0xfffffff0ull ? 0xfffffff0u : (uint32_t)want;
+  CK(s.tape.reserve((size_t)arena_cap * 8));
+  CK(s.tidx.reserve((size_t)s.n * 8 + 16));
+  CK(s.tcursor.reserve(16));
+  DevDocs docs;
+  memset(&docs, 0, sizeof docs);
+  docs.data = s.data.as<char>();
+  docs.off = s.off.as<uint64_t>();
+  launch_index_slot(docs, s.n, s.tape.p, arena_cap, s.tcursor.as<uint32_t>(), s.tidx.p, c->stream);
+  c->launches += 1;
+  CK(cudaGetLastError());
+  s.indexed = true;
+  return 0;
+}
+
 int nbrm_tape_dump(nbrm_ctx* c, int slot, uint32_t cap, uint64_t* entries, uint32_t* counts, uint32_t* flags) {
   if (!c || !entries || !counts || !flags) return -2;
   if (slot < 0 || slot >= NBRM_SLOTS) return fail_msg(c, "nbrm_tape_dump: slot out of range");
@@ -926,6 +987,7 @@ int nbrm_tape_dump(nbrm_ctx* c, int slot, uint32_t cap, uint64_t* entries, uint3
   if (e == cudaSuccess) e = d_flg.reserve_exact((size_t)s.n * 4);
   if (e == cudaSuccess) {
     DevDocs docs;
+    memset(&docs, 0, sizeof docs);
     docs.data = s.data.as<char>();
     docs.off = s.off.as<uint64_t>();
     launch_tape_dump(docs, s.n, cap, d_ent.p, d_cnt.as<uint32_t>(), d_flg.as<uint32_t>(), c->stream);

@@ -364,18 +364,38 @@ NB_HD void plan_merged_metadata(Planner& P, const Doc& from, const ObjView& fv, 
   LIT(P, RBRACE);
 }
 
+// The spans a generator wrote down for an object it planned (nbrm_plan.cuh, views): what
+// view_object finds, without the walk.  Fields the generators do not record stay empty; the
+// compare below asks a desired object for none of them.
+NB_HD ObjView view_from_table(const ViewIn& r) {
+  ObjView v;
+  v.root = r.get(VF_ROOT);
+  v.kind = r.get(VF_KIND);
+  v.meta = r.get(VF_META);
+  v.labels = r.get(VF_LABELS);
+  v.annotations = r.get(VF_ANNOTATIONS);
+  v.spec = r.get(VF_SPEC);
+  v.replicas = r.get(VF_REPLICAS);
+  v.tlabels = r.get(VF_TLABELS);
+  v.tpod = r.get(VF_TPOD);
+  v.selector = r.get(VF_SELECTOR);
+  v.ports = r.get(VF_PORTS);
+  v.tmpl = v.tmeta = mk(0, 0);
+  return v;
+}
+
 template <uint32_t N>
 NB_HD bool kind_is(const Doc& d, Span rootv, const char (&k)[N]) {
   return str_eq(d, FIND(d, rootv, "kind"), k);
 }
 
 // The planner for one (desired, found) pair.
-NB_HD void plan_copy_fields(Planner& P, const Doc& from, const Doc& to) {
+NB_HD void plan_copy_fields(Planner& P, const Doc& from, const Doc& to, const ViewIn& from_view) {
   if (to.n == 0 || to.at(skip_ws(to, 0)) != '{') {  // NotFound -> Create(desired)
-    P.in(root(from), 0);
+    P.in(from_view.ok() ? from_view.get(VF_ROOT) : root(from), 0);
     return;
   }
-  ObjView fv = view_object(from), tv = view_object(to);
+  ObjView fv = from_view.ok() ? view_from_table(from_view) : view_object(from), tv = view_object(to);
   if (!is_object(from, fv.root)) {
     P.err = E_PARSE;
     return;
@@ -575,7 +595,7 @@ struct GenCopyFields {
   static const uint32_t CAP = 48;
   struct K {
     DocCtx& c;
-    NB_HD void operator()(Planner& P, uint32_t) { plan_copy_fields(P, c.d[0], c.d[1]); }
+    NB_HD void operator()(Planner& P, uint32_t) { plan_copy_fields(P, c.d[0], c.d[1], c.view[0]); }
   };
   NB_HD static uint32_t run(DocCtx& c, ObjSink s) {
     K k{c};

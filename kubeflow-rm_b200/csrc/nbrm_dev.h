@@ -20,6 +20,12 @@ struct SrcBases {
 struct DevDocs {
   const char* data;     // null when the slot is not used by the generator
   const uint64_t* off;  // n + 1 offsets into data
+  // the slot's structural index when it has one (nbrm_slot_index; nbrm_tape_index.cu):
+  // tidx[i] = (first entry of document i in tape, entry count | flags << 16)
+  const void* tape;
+  const uint2* tidx;
+  // the producing generator's views of the documents (field-major ViewTable), or null
+  ViewEnt* views;
 };
 
 // What a plan kernel reads: tuple i = document i of every slot in use.
@@ -44,6 +50,7 @@ struct PlanOut {
   uint32_t* result;   // one per input tuple, generator-specific
   char* aux;          // aux arena
   uint32_t cap;
+  ViewEnt* views;     // VIEW_FIELDS * n * NOBJ view entries of the planned objects (field-major), or null
 };
 
 // nbrm_kernels.cu
@@ -57,7 +64,9 @@ void launch_emit(const Seg* segs, const uint32_t* nseg, const uint32_t* lens, co
                  uint32_t n_out, uint32_t cap, uint32_t nobj, const SrcBases& bases, char* out,
                  int sm_count, cudaStream_t st);
 
-// nbrm_tape_debug.cu
+// nbrm_tape_index.cu
+void launch_index_slot(const DevDocs& docs, uint32_t n, void* arena, uint32_t arena_cap, uint32_t* cursor,
+                       void* tidx, cudaStream_t st);
 void launch_tape_dump(const DevDocs& docs, uint32_t n, uint32_t cap, void* out, uint32_t* out_nt,
                       uint32_t* out_flags, cudaStream_t st);
 
@@ -67,5 +76,6 @@ enum GenId { GEN_ID_NBC = 0, GEN_ID_ODH = 1, GEN_ID_COPY = 2, GEN_ID_STATUS = 3,
 void launch_plan(int gen, const PlanIn& in, const PlanOut& out, uint64_t in_bytes, cudaStream_t st);
 void gen_shape(int gen, uint32_t* nobj, uint32_t* cap);
 bool gen_shared1(int gen);
+bool gen_views(int gen);  // the generator leaves views of its objects (nbrm_plan.cuh)
 
 }  // namespace nbrm

@@ -21,6 +21,8 @@ struct ObjSink {
   uint32_t* nseg;  // n_obj
   uint32_t* lens;  // n_obj
   uint32_t cap;
+  ViewTable views = {nullptr, 0};  // where the generator's views of the planned objects go, when someone asked ...
+  uint32_t view_j = 0;             // ... and the index of this tuple's first object in that table
 };
 
 // Everything a generator sees for one input tuple.
@@ -39,6 +41,7 @@ struct DocCtx {
   const uint64_t* shared_off;
   uint32_t shared_n;
   uint32_t result;      // generator-specific per-tuple result word (0 when unused)
+  ViewIn view[3] = {{{nullptr, 0}, 0}, {{nullptr, 0}, 0}, {{nullptr, 0}, 0}};  // the producing generator's view of d[k], when it left one
 };
 
 // Plans n_obj objects with plan_k(P, k).  One failing object voids the whole

@@ -210,15 +210,24 @@ NB_HD void plan_nb_prefix_elem(Planner& P, const NbView& v) {
 
 // generateStatefulSet (+ SetControllerReference when asked).
 NB_HD void plan_statefulset(Planner& P, const Doc& d, const NbView& v, const EnvLits& env,
-                            uint32_t flags) {
+                            uint32_t flags, ViewOut vw) {
+  vw.clear();
   LIT(P, STS_HEAD);
+  vw.set(VF_KIND, LIT_AFTER(STS_HEAD, "\"kind\":"), LIT_AFTER(STS_HEAD, "\"kind\":\"StatefulSet\""));
+  vw.begin(VF_META, LIT_AFTER(STS_HEAD, "\"metadata\":"));
   put_str(P, v.name);
   plan_meta_tail(P, v, flags);
+  vw.end(VF_META, P.total + 1);  // the '}' that opens the next fragment
+  vw.begin(VF_SPEC, P.total + LIT_AFTER(STS_SPEC_REPLICAS, "\"spec\":"));
   LIT(P, STS_SPEC_REPLICAS);
+  vw.set(VF_REPLICAS, P.total, P.total + 1);
   if (v.a_stopped.ok()) LIT(P, ZERO);  // :410-412 metav1.HasAnnotation: presence only
   else LIT(P, ONE);
+  vw.begin(VF_SELECTOR, P.total + LIT_AFTER(STS_SELECTOR, "\"selector\":"));
   LIT(P, STS_SELECTOR);
   put_str(P, v.name);
+  vw.end(VF_SELECTOR, P.total + 2);
+  vw.begin(VF_TLABELS, P.total + LIT_LEN(STS_TEMPLATE_LABELS) - 1);
   LIT(P, STS_TEMPLATE_LABELS);
   {  // :428-432 defaults, :441-444 Notebook labels win
     Sep s;
@@ -246,10 +255,15 @@ NB_HD void plan_statefulset(Planner& P, const Doc& d, const NbView& v, const Env
     Member m;
     while (it.next(d, m)) {
       if (key_has_kubectl_or_notebook(d, inner(m.key))) continue;
-      if (s.first) LIT(P, STS_ANNOTATIONS);
+      if (s.first) {
+        vw.end(VF_TLABELS, P.total + 1);
+        LIT(P, STS_ANNOTATIONS);
+      }
       s.in(P, d, m.all);
     }
+    if (s.first) vw.end(VF_TLABELS, P.total + 1);  // no annotations: the labels close in the next fragment
   }
+  vw.begin(VF_TPOD, P.total + LIT_AFTER(STS_TEMPLATE_SPEC, "\"spec\":"));
   LIT(P, STS_TEMPLATE_SPEC);
   {  // PodSpec members, :435 deep copy with :454-482 edits
     Sep ps;
@@ -316,14 +330,23 @@ NB_HD void plan_statefulset(Planner& P, const Doc& d, const NbView& v, const Env
       LIT(P, KEY_FSGROUP_DEFAULT);
     }
   }
-  LIT(P, STS_TAIL);
+  LIT(P, STS_TAIL);  // }}}} closes the PodSpec, the template, the spec, the object
+  vw.end(VF_TPOD, P.total - 3);
+  vw.end(VF_SPEC, P.total - 1);
+  vw.set(VF_ROOT, 0, P.total);
 }
 
 // generateService.
-NB_HD void plan_service(Planner& P, const Doc& d, const NbView& v, uint32_t flags) {
+NB_HD void plan_service(Planner& P, const Doc& d, const NbView& v, uint32_t flags, ViewOut vw) {
+  vw.clear();
   LIT(P, SVC_HEAD);
+  vw.set(VF_KIND, LIT_AFTER(SVC_HEAD, "\"kind\":"), LIT_AFTER(SVC_HEAD, "\"kind\":\"Service\""));
+  vw.begin(VF_META, LIT_AFTER(SVC_HEAD, "\"metadata\":"));
   put_str(P, v.name);
   plan_meta_tail(P, v, flags);
+  vw.end(VF_META, P.total + 1);
+  vw.begin(VF_SPEC, P.total + LIT_AFTER(SVC_PORTS, "\"spec\":"));
+  vw.begin(VF_PORTS, P.total + LIT_AFTER(SVC_PORTS, "\"ports\":"));
   LIT(P, SVC_PORTS);
   P.in(inner(v.name));
   LIT(P, SVC_TARGETPORT);
@@ -341,9 +364,14 @@ NB_HD void plan_service(Planner& P, const Doc& d, const NbView& v, uint32_t flag
     if (cp.ok() && !is_null(d, cp)) P.in(cp);
     else LIT(P, ZERO);
   }
+  vw.end(VF_PORTS, P.total + 2);
+  vw.begin(VF_SELECTOR, P.total + LIT_AFTER(SVC_SELECTOR, "\"selector\":"));
   LIT(P, SVC_SELECTOR);
   put_str(P, v.name);
+  vw.end(VF_SELECTOR, P.total + 1);
   LIT(P, SVC_TAIL);
+  vw.end(VF_SPEC, P.total - 1);
+  vw.set(VF_ROOT, 0, P.total);
 }
 
 NB_HD int hexval(char c) {
@@ -519,13 +547,18 @@ NB_HD void plan_headers_set(Planner& P, const Doc& d, const NbView& v, Aux& aux)
 
 // generateVirtualService.
 NB_HD void plan_virtualservice(Planner& P, const Doc& d, const NbView& v, const EnvLits& env,
-                               uint32_t flags, Aux& aux) {
+                               uint32_t flags, Aux& aux, ViewOut vw) {
+  vw.clear();
   LIT(P, VS_HEAD);  // ... "name":"notebook-
+  vw.set(VF_KIND, LIT_AFTER(VS_HEAD, "\"kind\":"), LIT_AFTER(VS_HEAD, "\"kind\":\"VirtualService\""));
+  vw.begin(VF_META, LIT_AFTER(VS_HEAD, "\"metadata\":"));
   P.in(inner(v.ns));
   LIT(P, DASH);
   P.in(inner(v.name));
   LIT(P, QUOTE);
   plan_meta_tail(P, v, flags);
+  vw.end(VF_META, P.total + 1);
+  vw.begin(VF_SPEC, P.total + LIT_AFTER(VS_GATEWAYS, "\"spec\":"));
   LIT(P, VS_GATEWAYS);
   P.pool(env.istio_gateway.off, env.istio_gateway.len);
   LIT(P, VS_HOSTS);
@@ -554,28 +587,36 @@ NB_HD void plan_virtualservice(Planner& P, const Doc& d, const NbView& v, const 
   LIT(P, DOT_SVC_DOT);
   P.pool(env.cluster_domain.off, env.cluster_domain.len);
   LIT(P, VS_TAIL);
+  vw.end(VF_SPEC, P.total - 1);
+  vw.set(VF_ROOT, 0, P.total);
 }
 
 // The notebook-controller generator: StatefulSet, Service, VirtualService.
 struct GenNbc {
+  static const bool VIEWS = true;  // leaves a view of each object for the compare stage (nbrm_plan.cuh)
   static const uint32_t NOBJ = 3;
   static const bool SHARED1 = false;  // slot 1 is per-tuple, not one shared arena
   static const uint32_t CAP = 96;
   struct K {
     DocCtx& c;
     const NbView& v;
+    ViewTable views;
+    uint32_t view_j;
     NB_HD void operator()(Planner& P, uint32_t k) {
       if (!(c.flags & (1u << k))) return;
-      if (k == 0) plan_statefulset(P, c.d[0], v, *c.env, c.flags);
-      else if (k == 1) plan_service(P, c.d[0], v, c.flags);
-      else plan_virtualservice(P, c.d[0], v, *c.env, c.flags, c.aux);
+      ViewRec rec;
+      ViewOut vw{views.p ? &rec : nullptr};
+      if (k == 0) plan_statefulset(P, c.d[0], v, *c.env, c.flags, vw);
+      else if (k == 1) plan_service(P, c.d[0], v, c.flags, vw);
+      else plan_virtualservice(P, c.d[0], v, *c.env, c.flags, c.aux, vw);
+      if (views.p) views.store(view_j + k, rec);
     }
   };
   NB_HD static uint32_t run(DocCtx& c, ObjSink s) {
     NbView v = view_notebook(c.d[0]);
     uint32_t st = v.err;
     if (!st && (!is_object(c.d[0], v.podspec) || !v.c0.ok())) st = E_NO_CONTAINERS;
-    K k{c, v};
+    K k{c, v, s.views, s.view_j};
     return plan_objects(c, s, NOBJ, st, k);
   }
 };

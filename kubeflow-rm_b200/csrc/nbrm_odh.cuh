@@ -35,18 +35,22 @@ NB_HD bool mesh_enabled(const Doc& d, const NbView& v) {
   return annotation_true(d, v.a_mesh);
 }
 
-NB_HD void plan_labels_notebook_name(Planner& P, const NbView& v) {
+NB_HD void plan_labels_notebook_name(Planner& P, const NbView& v, ViewOut vw) {
+  vw.begin(VF_LABELS, P.total + LIT_AFTER(LABELS_NOTEBOOK_NAME, "\"labels\":"));
   LIT(P, LABELS_NOTEBOOK_NAME);
   put_str(P, v.name);
+  vw.end(VF_LABELS, P.total + 1);  // the next fragment starts with the closing brace
 }
 
 NB_HD void plan_network_policy(Planner& P, const NbView& v, const EnvLits& env, uint32_t flags,
-                               bool oauth_np) {
+                               bool oauth_np, ViewOut vw) {
   LIT(P, NP_HEAD);
+  vw.set(VF_KIND, LIT_AFTER(NP_HEAD, "\"kind\":"), LIT_AFTER(NP_HEAD, "\"kind\":\"NetworkPolicy\""));
   P.in(inner(v.name));
   if (oauth_np) LIT(P, NP_OAUTH_SUFFIX);
   else LIT(P, NP_CTRL_SUFFIX);
   plan_meta_tail(P, v, flags);
+  vw.begin(VF_SPEC, P.total + LIT_AFTER(NP_SPEC, "\"spec\":"));
   LIT(P, NP_SPEC);
   put_str(P, v.name);
   if (oauth_np) {
@@ -56,45 +60,56 @@ NB_HD void plan_network_policy(Planner& P, const NbView& v, const EnvLits& env, 
     P.pool(env.ctrl_namespace.off, env.ctrl_namespace.len);
     LIT(P, NP_CTRL_TAIL);
   }
+  vw.end(VF_SPEC, P.total - 1);
+  vw.set(VF_ROOT, 0, P.total);
 }
 
-NB_HD void plan_route(Planner& P, const NbView& v, uint32_t flags, bool oauth_route) {
+NB_HD void plan_route(Planner& P, const NbView& v, uint32_t flags, bool oauth_route, ViewOut vw) {
   LIT(P, ROUTE_HEAD);
+  vw.set(VF_KIND, LIT_AFTER(ROUTE_HEAD, "\"kind\":"), LIT_AFTER(ROUTE_HEAD, "\"kind\":\"Route\""));
   put_str(P, v.name);
   plan_meta_tail(P, v, flags);
-  plan_labels_notebook_name(P, v);
+  plan_labels_notebook_name(P, v, vw);
+  vw.begin(VF_SPEC, P.total + LIT_AFTER(ROUTE_SPEC_TO, "\"spec\":"));
   LIT(P, ROUTE_SPEC_TO);
   P.in(inner(v.name));
   if (oauth_route) {
+    vw.end(VF_SPEC, P.total + LIT_AFTER(ROUTE_OAUTH_TAIL, "\"wildcardPolicy\":\"None\"}"));
     LIT(P, ROUTE_OAUTH_TAIL);
   } else {
     LIT(P, ROUTE_PLAIN_PORT);
     P.in(inner(v.name));
+    vw.end(VF_SPEC, P.total + LIT_AFTER(ROUTE_PLAIN_TAIL, "\"wildcardPolicy\":\"None\"}"));
     LIT(P, ROUTE_PLAIN_TAIL);
   }
+  vw.set(VF_ROOT, 0, P.total);
 }
 
-NB_HD void plan_service_account(Planner& P, const NbView& v, uint32_t flags) {
+NB_HD void plan_service_account(Planner& P, const NbView& v, uint32_t flags, ViewOut vw) {
   LIT(P, SA_HEAD);
+  vw.set(VF_KIND, LIT_AFTER(SA_HEAD, "\"kind\":"), LIT_AFTER(SA_HEAD, "\"kind\":\"ServiceAccount\""));
   put_str(P, v.name);
   plan_meta_tail(P, v, flags);
-  plan_labels_notebook_name(P, v);
+  plan_labels_notebook_name(P, v, vw);
   LIT(P, SA_ANNOTATION);
   P.in(inner(v.name));
   LIT(P, SA_TAIL);
+  vw.set(VF_ROOT, 0, P.total);
 }
 
-NB_HD void plan_oauth_service(Planner& P, const NbView& v, uint32_t flags) {
+NB_HD void plan_oauth_service(Planner& P, const NbView& v, uint32_t flags, ViewOut vw) {
   LIT(P, TLSSVC_HEAD);
+  vw.set(VF_KIND, LIT_AFTER(TLSSVC_HEAD, "\"kind\":"), LIT_AFTER(TLSSVC_HEAD, "\"kind\":\"Service\""));
   P.in(inner(v.name));
   LIT(P, TLS_SUFFIX);
   plan_meta_tail(P, v, flags);
-  plan_labels_notebook_name(P, v);
+  plan_labels_notebook_name(P, v, vw);
   LIT(P, TLSSVC_ANNOTATION);
   P.in(inner(v.name));
   LIT(P, TLSSVC_SPEC);
   put_str(P, v.name);
   LIT(P, RBRACE3);
+  vw.set(VF_ROOT, 0, P.total);
 }
 
 NB_HD char b64c(uint32_t x) {
@@ -130,12 +145,13 @@ NB_HD uint32_t base64(const unsigned char* in, uint32_t n, char* out) {
 // cookie_secret = base64(base64(16 seed bytes)), 32 characters (:192-195).  The
 // seed comes from the caller's CSPRNG; nothing random is drawn on the device.
 NB_HD void plan_oauth_secret(Planner& P, const NbView& v, uint32_t flags, const unsigned char* seed16,
-                             Aux& aux) {
+                             Aux& aux, ViewOut vw) {
   LIT(P, SECRET_HEAD);
+  vw.set(VF_KIND, LIT_AFTER(SECRET_HEAD, "\"kind\":"), LIT_AFTER(SECRET_HEAD, "\"kind\":\"Secret\""));
   P.in(inner(v.name));
   LIT(P, SECRET_SUFFIX);
   plan_meta_tail(P, v, flags);
-  plan_labels_notebook_name(P, v);
+  plan_labels_notebook_name(P, v, vw);
   LIT(P, SECRET_DATA);
   if (aux.used + 64 <= aux.cap) {
     char tmp[24];
@@ -150,41 +166,48 @@ NB_HD void plan_oauth_secret(Planner& P, const NbView& v, uint32_t flags, const 
     P.err = E_LIMIT;
   }
   LIT(P, SECRET_TAIL);
+  vw.set(VF_ROOT, 0, P.total);
 }
 
-NB_HD void plan_rolebinding(Planner& P, const NbView& v, uint32_t flags) {
+NB_HD void plan_rolebinding(Planner& P, const NbView& v, uint32_t flags, ViewOut vw) {
   LIT(P, RB_HEAD);
+  vw.set(VF_KIND, LIT_AFTER(RB_HEAD, "\"kind\":"), LIT_AFTER(RB_HEAD, "\"kind\":\"RoleBinding\""));
   P.in(inner(v.name));
   LIT(P, QUOTE);
   plan_meta_tail(P, v, flags);
-  plan_labels_notebook_name(P, v);
+  plan_labels_notebook_name(P, v, vw);
+  vw.begin(VF_SUBJECTS, P.total + LIT_AFTER(RB_SUBJECTS, "\"subjects\":"));
   LIT(P, RB_SUBJECTS);
   put_str(P, v.name);
   if (v.ns.ok()) {
     LIT(P, NAMESPACE_KEY);
     P.in(v.ns);
   }
+  vw.end(VF_SUBJECTS, P.total + 2);  // "}]" opens the last fragment
   LIT(P, RB_TAIL);
+  vw.set(VF_ROOT, 0, P.total);
 }
 
 // One ODH reconcile's objects; slot k of ODH_OUT_PER_DOC, or nothing when the
 // reference would not build that object for this Notebook.
 NB_HD void plan_odh_object(Planner& P, const Doc& d, const NbView& v, const EnvLits& env,
                            uint32_t flags, uint32_t k, bool oauth, bool mesh,
-                           const unsigned char* seed16, Aux& aux) {
+                           const unsigned char* seed16, Aux& aux, ViewOut vw) {
+  vw.clear();
   switch (k) {
-    case 0: plan_network_policy(P, v, env, flags, false); break;
-    case 1: if (!mesh) plan_network_policy(P, v, env, flags, true); break;
-    case 2: if (!mesh) plan_route(P, v, flags, oauth); break;
-    case 3: if (!mesh && oauth) plan_service_account(P, v, flags); break;
-    case 4: if (!mesh && oauth) plan_oauth_service(P, v, flags); break;
-    case 5: if (!mesh && oauth) plan_oauth_secret(P, v, flags, seed16, aux); break;
-    case 6: if (flags & ODH_RBAC) plan_rolebinding(P, v, flags); break;
+    case 0: plan_network_policy(P, v, env, flags, false, vw); break;
+    case 1: if (!mesh) plan_network_policy(P, v, env, flags, true, vw); break;
+    case 2: if (!mesh) plan_route(P, v, flags, oauth, vw); break;
+    case 3: if (!mesh && oauth) plan_service_account(P, v, flags, vw); break;
+    case 4: if (!mesh && oauth) plan_oauth_service(P, v, flags, vw); break;
+    case 5: if (!mesh && oauth) plan_oauth_secret(P, v, flags, seed16, aux, vw); break;
+    case 6: if (flags & ODH_RBAC) plan_rolebinding(P, v, flags, vw); break;
   }
 }
 
 // The ODH reconcile generator.  extra = 16 seed bytes per Notebook (or null).
 struct GenOdh {
+  static const bool VIEWS = true;  // leaves a view of each object for the write decision (nbrm_plan.cuh)
   static const uint32_t NOBJ = ODH_OUT_PER_DOC;
   static const bool SHARED1 = false;  // slot 1 is per-tuple, not one shared arena
   static const uint32_t CAP = 32;
@@ -192,15 +215,20 @@ struct GenOdh {
     DocCtx& c;
     const NbView& v;
     bool oauth, mesh;
+    ViewTable views;
+    uint32_t view_j;
     NB_HD void operator()(Planner& P, uint32_t k) {
       const unsigned char* seed =
           c.extra ? (const unsigned char*)c.extra + (size_t)c.index * 16 : nullptr;
-      plan_odh_object(P, c.d[0], v, *c.env, c.flags, k, oauth, mesh, seed, c.aux);
+      ViewRec rec;
+      plan_odh_object(P, c.d[0], v, *c.env, c.flags, k, oauth, mesh, seed, c.aux,
+                      ViewOut{views.p ? &rec : nullptr});
+      if (views.p) views.store(view_j + k, rec);
     }
   };
   NB_HD static uint32_t run(DocCtx& c, ObjSink s) {
     NbView v = view_notebook(c.d[0]);
-    K k{c, v, false, false};
+    K k{c, v, false, false, s.views, s.view_j};
     if (!v.err) {
       k.oauth = oauth_enabled(c.d[0], v);
       k.mesh = mesh_enabled(c.d[0], v);

@@ -119,8 +119,8 @@ NB_HD void plan_without_owner(Planner& P, const Doc& from) {
   LIT(P, RBRACE);
 }
 
-NB_HD uint32_t plan_odh_decide(Planner& P, const Doc& from, const Doc& to) {
-  const Span fr = root(from);
+NB_HD uint32_t plan_odh_decide(Planner& P, const Doc& from, const Doc& to, const ViewIn& fview) {
+  const Span fr = fview.ok() ? fview.get(VF_ROOT) : root(from);
   if (!is_object(from, fr)) {
     P.err = E_PARSE;
     return ODH_NONE;
@@ -130,8 +130,15 @@ NB_HD uint32_t plan_odh_decide(Planner& P, const Doc& from, const Doc& to) {
     return ODH_CREATE;
   }
   // one walk over each root: kind, metadata, spec, subjects
-  Span kind = mk(0, 0), fmeta = mk(0, 0), fspec = mk(0, 0), fsubj = mk(0, 0);
-  {
+  Span kind = mk(0, 0), fmeta = mk(0, 0), fspec = mk(0, 0), fsubj = mk(0, 0), flabels = mk(0, 0);
+  if (fview.ok()) {  // the generator of the desired object wrote down where these lie (nbrm_plan.cuh, views)
+    kind = fview.get(VF_KIND);
+    if (!str_eq(from, kind, "Route") && !str_eq(from, kind, "NetworkPolicy") && !str_eq(from, kind, "RoleBinding"))
+      return ODH_NONE;
+    fspec = fview.get(VF_SPEC);
+    fsubj = fview.get(VF_SUBJECTS);
+    flabels = fview.get(VF_LABELS);
+  } else {
     ObjIter it(from, fr);
     Member m;
     while (it.next(from, m)) {
@@ -145,6 +152,7 @@ NB_HD uint32_t plan_odh_decide(Planner& P, const Doc& from, const Doc& to) {
       else if (KEY_IS(from, m, "spec")) fspec = m.val;
       else if (KEY_IS(from, m, "subjects")) fsubj = m.val;
     }
+    flabels = FIND(from, fmeta, "labels");
   }
   const bool is_route = str_eq(from, kind, "Route");
   const bool is_np = !is_route && str_eq(from, kind, "NetworkPolicy");
@@ -165,7 +173,6 @@ NB_HD uint32_t plan_odh_decide(Planner& P, const Doc& from, const Doc& to) {
     plan_without_owner(P, from);
     return ODH_UPDATE;
   }
-  const Span flabels = FIND(from, fmeta, "labels");
   const Span tlabels = FIND(to, tmeta, "labels");
   bool same = json_equal(from, flabels, to, tlabels);
   if (same) same = is_route ? route_spec_equal(from, fspec, to, tspec) : json_equal(from, fspec, to, tspec);
@@ -181,7 +188,7 @@ struct GenOdhDecide {
   static const uint32_t CAP = 48;
   struct K {
     DocCtx& c;
-    NB_HD void operator()(Planner& P, uint32_t) { c.result = plan_odh_decide(P, c.d[0], c.d[1]); }
+    NB_HD void operator()(Planner& P, uint32_t) { c.result = plan_odh_decide(P, c.d[0], c.d[1], c.view[0]); }
   };
   NB_HD static uint32_t run(DocCtx& c, ObjSink s) {
     K k{c};

@@ -24,8 +24,12 @@ namespace nbrm {
 
 enum PdErr : uint32_t { E_SELECTOR = 9 };  // label selector conversion failed (:77-79)
 
-static const uint32_t PD_MAX_MATCH = 32;   // PodDefaults applied to one Pod
-static const uint32_t PD_MAX_ADDED = 32;   // items one merge may append to a list
+// Fixed room per Pod.  BASELINE.json's admission config lists up to 100 PodDefaults per
+// namespace; the reference applies however many match (main.go:72-97 has no limit), so the
+// room covers every one of them matching, with slack: a Pod beyond it is rejected with
+// NBRM_E_LIMIT, never mutated partially.
+static const uint32_t PD_MAX_MATCH = 128;  // PodDefaults applied to one Pod
+static const uint32_t PD_MAX_ADDED = 256;  // items one merge may append to a list
 
 NB_HD Doc pd_doc(const DocCtx& c, uint32_t j) {
   Doc d;
@@ -670,7 +674,7 @@ NB_HD void plan_poddefault(Planner& P, DocCtx& c) {
 struct GenPodDefault {
   static const uint32_t NOBJ = 1;
   static const bool SHARED1 = true;  // slot 1 = the PodDefault arena, shared by every Pod
-  static const uint32_t CAP = 512;
+  static const uint32_t CAP = 4096;  // 128 PodDefaults x (volume + mount per container + marker + ...) segments
   struct K {
     DocCtx& c;
     NB_HD void operator()(Planner& P, uint32_t) { plan_poddefault(P, c); }

@@ -108,19 +108,113 @@ enum LitOff : uint32_t {
 
 #define LIT(P, name) (P).pool(::nbrm::L_##name, ::nbrm::L_##name##_END - ::nbrm::L_##name)
 
+// The fragments' text at compile time (LT_name), for planners that must know where
+// something lies inside a fragment they emit (views, below).
+#define X(name, text) static constexpr char LT_##name[] = text;
+NBRM_LITS(X)
+#undef X
+
+// Index just after the first occurrence of `needle` in `text` (compile time).
+template <uint32_t N, uint32_t M>
+constexpr uint32_t lit_after(const char (&text)[N], const char (&needle)[M]) {
+  for (uint32_t i = 0; i + (M - 1) <= N - 1; ++i) {
+    bool hit = true;
+    for (uint32_t k = 0; k + 1 < M; ++k)
+      if (text[i + k] != needle[k]) {
+        hit = false;
+        break;
+      }
+    if (hit) return i + M - 1;
+  }
+  return 0xffffffffu;
+}
+#define LIT_AFTER(name, needle) (::nbrm::lit_after(::nbrm::LT_##name, needle))
+#define LIT_LEN(name) ((uint32_t)sizeof(::nbrm::LT_##name) - 1u)
+
+// ---------------------------------------------------------------- views
+// A generator knows where it puts things.  For the objects a later stage compares
+// (notebook-controller's three, the ODH objects), it writes down where the parts that
+// stage looks for lie in the object it planned — exactly the spans view_object
+// (nbrm_cmp.cuh) would find by walking the emitted text — so the compare stage of the same
+// pass starts from them instead of parsing what the library itself just wrote.  A slot
+// filled by nbrm_upload has no views and is walked as before.
+enum ViewField : uint32_t {
+  VF_ROOT, VF_KIND, VF_META, VF_LABELS, VF_ANNOTATIONS, VF_SPEC, VF_REPLICAS, VF_TLABELS, VF_TPOD,
+  VF_SELECTOR, VF_PORTS, VF_SUBJECTS, VIEW_FIELDS
+};
+struct ViewRec {
+  uint32_t off[VIEW_FIELDS];
+  uint32_t len[VIEW_FIELDS];
+};
+// A planner fills a ViewRec of its own (registers) while it plans ...
+struct ViewOut {
+  ViewRec* r;  // null: nobody asked
+  NB_HD void clear() {
+    if (r)
+      for (uint32_t f = 0; f < VIEW_FIELDS; ++f) r->off[f] = r->len[f] = 0;
+  }
+  NB_HD void set(uint32_t f, uint32_t off, uint32_t end) {
+    if (r) {
+      r->off[f] = off;
+      r->len[f] = end - off;
+    }
+  }
+  NB_HD void begin(uint32_t f, uint32_t off) {
+    if (r) r->off[f] = off;
+  }
+  NB_HD void end(uint32_t f, uint32_t e) {
+    if (r) r->len[f] = e - r->off[f];
+  }
+};
+// ... and the views of a batch are kept field-major: (off, len) of field f of object j at
+// p[f * n + j].  Threads that plan or read neighbouring objects then touch neighbouring
+// words, where an array of records would put every lane in a cache line of its own.
+struct alignas(8) ViewEnt {
+  uint32_t off, len;
+};
+struct ViewTable {
+  ViewEnt* p;  // VIEW_FIELDS * n entries, or null
+  uint32_t n;  // objects in the batch
+  NB_HD void store(uint32_t j, const ViewRec& r) const {
+    for (uint32_t f = 0; f < VIEW_FIELDS; ++f) {
+      ViewEnt e;
+      e.off = r.off[f];
+      e.len = r.len[f];
+      p[(size_t)f * n + j] = e;
+    }
+  }
+  NB_HD Span get(uint32_t j, uint32_t f) const {
+    const ViewEnt e = p[(size_t)f * n + j];
+    return mk(e.off, e.len);
+  }
+};
+// The views of one input document, as a planner receives them.
+struct ViewIn {
+  ViewTable t;
+  uint32_t j;
+  NB_HD bool ok() const { return t.p != nullptr; }
+  NB_HD Span get(uint32_t f) const { return t.get(j, f); }
+};
+
 // Strings that come from the reference's process environment / flags.  The
 // host JSON-escapes them and appends them to the pool after L__TOTAL.
+// A piece of the literal pool.  Not a Span: this struct travels inside the kernel
+// arguments between units compiled with and without the tape (a Span then carries a tape
+// index), so its layout must not depend on that.
+struct PoolSpan {
+  uint32_t off, len;
+};
 struct EnvLits {
-  Span istio_host;      // ISTIO_HOST or "*"            (notebook_controller.go:548-551)
-  Span istio_gateway;   // ISTIO_GATEWAY or default     (:557-560)
-  Span cluster_domain;  // CLUSTER_DOMAIN or default    (:537-539)
-  Span ctrl_namespace;  // ODH controller namespace     (odh main.go:63-72)
-  Span oauth_image;     // --oauth-proxy-image          (odh main.go:80)
+  PoolSpan istio_host;      // ISTIO_HOST or "*"            (notebook_controller.go:548-551)
+  PoolSpan istio_gateway;   // ISTIO_GATEWAY or default     (:557-560)
+  PoolSpan cluster_domain;  // CLUSTER_DOMAIN or default    (:537-539)
+  PoolSpan ctrl_namespace;  // ODH controller namespace     (odh main.go:63-72)
+  PoolSpan oauth_image;     // --oauth-proxy-image          (odh main.go:80)
   // profile-controller (profile_controller.go:419-504, :127-137)
-  Span prof_when_key;   // "request.headers[<userid header>]" (quoted)
-  Span prof_prefix;     // userid prefix (unquoted, escaped)
-  Span prof_igw, prof_kfp, prof_nbc;  // principals (quoted)
-  Span prof_ns_labels;  // members of the Namespace's labels map, rendered by the host
+  PoolSpan prof_when_key;   // "request.headers[<userid header>]" (quoted)
+  PoolSpan prof_prefix;     // userid prefix (unquoted, escaped)
+  PoolSpan prof_igw, prof_kfp, prof_nbc;  // principals (quoted)
+  PoolSpan prof_ns_labels;  // members of the Namespace's labels map, rendered by the host
   uint32_t add_fsgroup; // ADD_FSGROUP unset or "true"  (notebook_controller.go:475)
   uint32_t use_istio;   // USE_ISTIO == "true"          (:213)
 };

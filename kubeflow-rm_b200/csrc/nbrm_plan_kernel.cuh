@@ -2,6 +2,9 @@
 // generator instantiates it in a translation unit of its own (gen_*.cu) so the
 // generators compile in parallel: in one unit the build took 28 minutes.
 #pragma once
+#include <stdlib.h>
+#include <string.h>
+
 #include "nbrm_dev.h"
 
 namespace nbrm {
@@ -79,6 +82,15 @@ __global__ void plan_kernel(PlanIn in, PlanOut out, uint32_t smem_cap, uint32_t 
       c.base[k] = (uint32_t)o0;
       aux_abs += (uint32_t)o0;
       aux_cap += c.d[k].n;
+#ifdef NBRM_TAPE
+      if (in.slot[k].tidx) {  // the slot was indexed when it became resident (nbrm_slot_index)
+        const uint2 ti = in.slot[k].tidx[i];
+        c.d[k].tape = reinterpret_cast<const TapeEnt*>(in.slot[k].tape) + ti.x;
+        c.d[k].nt = ti.y & 0xffffu;
+        c.d[k].tflags = c.d[k].nt ? (ti.y >> 16) : DOC_WS;
+        c.d[k].dlim = TAPE_MAX_DEPTH;
+      }
+#endif
     } else {
       c.d[k].p = nullptr;
       c.d[k].n = 0;
@@ -105,6 +117,15 @@ __global__ void plan_kernel(PlanIn in, PlanOut out, uint32_t smem_cap, uint32_t 
   s.nseg = out.nseg + (size_t)i * G::NOBJ;
   s.lens = out.lens + (size_t)i * G::NOBJ;
   s.cap = out.cap;
+  s.views.p = out.views;
+  s.views.n = in.n * G::NOBJ;
+  s.view_j = i * G::NOBJ;
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    c.view[k].t.p = (G::SHARED1 && k == 1) ? nullptr : in.slot[k].views;
+    c.view[k].t.n = in.n;
+    c.view[k].j = i;
+  }
   out.status[i] = G::run(c, s);
   out.result[i] = c.result;
 }
@@ -122,6 +143,7 @@ static const uint32_t PLAN_SMEM = 100 * 1024;  // two blocks per SM
 // own tuple only: a batch of mixed shapes costs the sum of its tuples, not 32 times the
 // largest of every 32.
 static const uint32_t PLANW_WARPS = 4;
+static const uint32_t NBRM_WARP_MAX_TUPLES = 32768;
 
 template <class G>
 __global__ void __launch_bounds__(PLANW_WARPS * 32) plan_kernel_warp(PlanIn in, PlanOut out,
@@ -144,14 +166,21 @@ __global__ void __launch_bounds__(PLANW_WARPS * 32) plan_kernel_warp(PlanIn in, 
       c.base[k] = (uint32_t)o0;
       aux_abs += (uint32_t)o0;
       aux_cap += c.d[k].n;
-      uint32_t tf = DOC_WS;
-      const uint32_t nt = build_tape_warp(in.slot[k].data, o0, c.d[k].n, tape + used, tape_cap - used, sc,
-                                          TAPE_MAX_DEPTH, &tf);
-      c.d[k].tape = tape + used;
-      c.d[k].nt = nt;
-      c.d[k].tflags = tf;
       c.d[k].dlim = TAPE_MAX_DEPTH;
-      used += nt;
+      if (in.slot[k].tidx) {  // indexed when it became resident (nbrm_slot_index)
+        const uint2 ti = in.slot[k].tidx[i];
+        c.d[k].tape = reinterpret_cast<const TapeEnt*>(in.slot[k].tape) + ti.x;
+        c.d[k].nt = ti.y & 0xffffu;
+        c.d[k].tflags = (c.d[k].nt ? (ti.y >> 16) : DOC_WS) | DOC_COOP;
+      } else {
+        uint32_t tf = DOC_WS;
+        const uint32_t nt = build_tape_warp(in.slot[k].data, o0, c.d[k].n, tape + used, tape_cap - used, sc,
+                                            TAPE_MAX_DEPTH, &tf);
+        c.d[k].tape = tape + used;
+        c.d[k].nt = nt;
+        c.d[k].tflags = tf | DOC_COOP;
+        used += nt;
+      }
     } else {
       c.d[k].p = nullptr;
       c.d[k].n = 0;
@@ -179,6 +208,15 @@ __global__ void __launch_bounds__(PLANW_WARPS * 32) plan_kernel_warp(PlanIn in, 
   s.nseg = out.nseg + (size_t)i * G::NOBJ;
   s.lens = out.lens + (size_t)i * G::NOBJ;
   s.cap = out.cap;
+  s.views.p = out.views;
+  s.views.n = in.n * G::NOBJ;
+  s.view_j = i * G::NOBJ;
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    c.view[k].t.p = (G::SHARED1 && k == 1) ? nullptr : in.slot[k].views;
+    c.view[k].t.n = in.n;
+    c.view[k].j = i;
+  }
   const uint32_t st = G::run(c, s);
   if ((threadIdx.x & 31u) == 0) {
     out.status[i] = st;
@@ -199,7 +237,7 @@ static uint32_t tape_cap_for(uint64_t in_bytes, uint32_t n, uint32_t period) {
 }
 
 template <class G>
-static void launch(const PlanIn& in, const PlanOut& out, uint64_t in_bytes, cudaStream_t st) {
+static void launch_warp(const PlanIn& in, const PlanOut& out, uint64_t in_bytes, cudaStream_t st) {
   if (!in.n) return;
   const uint32_t cap = tape_cap_for(in_bytes, in.n, in.period);
   const size_t smem = (size_t)PLANW_WARPS * (cap * sizeof(TapeEnt) + sizeof(TapeScratch));
@@ -207,10 +245,10 @@ static void launch(const PlanIn& in, const PlanOut& out, uint64_t in_bytes, cuda
   const uint32_t blocks = (in.n + PLANW_WARPS - 1) / PLANW_WARPS;
   plan_kernel_warp<G><<<blocks, PLANW_WARPS * 32, smem, st>>>(in, out, cap);
 }
-#else
+#endif  // NBRM_WARP
 
 template <class G>
-static void launch(const PlanIn& in, const PlanOut& out, uint64_t in_bytes, cudaStream_t st) {
+static void launch_thread(const PlanIn& in, const PlanOut& out, uint64_t in_bytes, cudaStream_t st) {
   if (!in.n) return;
   // opt in to 100 KB of dynamic shared memory; the attribute belongs to the current
   // device's context, so it is set on every launch (a process may drive several GPUs)
@@ -243,7 +281,21 @@ static void launch(const PlanIn& in, const PlanOut& out, uint64_t in_bytes, cuda
   plan_kernel<G><<<blocks, threads, PLAN_SMEM, st>>>(in, out, PLAN_SMEM, 1);
 }
 
-#endif  // NBRM_WARP
+// A thread per tuple does 32 tuples' worth of work per instruction once the GPU is full of
+// them, a warp per tuple finishes one tuple 30 times sooner: small batches (a latency
+// question) go to the warp kernel, large ones (throughput) to the thread kernel.
+// NBRM_PLAN_MODE=warp|thread overrides the choice (experiments, tests).
+template <class G>
+static void launch(const PlanIn& in, const PlanOut& out, uint64_t in_bytes, cudaStream_t st) {
+#ifdef NBRM_WARP
+  static const int mode = [] {
+    const char* e = getenv("NBRM_PLAN_MODE");
+    return !e ? 0 : !strcmp(e, "warp") ? 1 : !strcmp(e, "thread") ? 2 : 0;
+  }();
+  if (mode == 1 || (mode == 0 && in.n <= NBRM_WARP_MAX_TUPLES)) return launch_warp<G>(in, out, in_bytes, st);
+#endif
+  launch_thread<G>(in, out, in_bytes, st);
+}
 
 // Defines the two entry points nbrm_plan_kernels.cu dispatches to.
 #define NBRM_DEFINE_GENERATOR(NAME, G)                                                        \

@@ -74,7 +74,9 @@ inline void build_pool_host(const nbrm_env* env, std::string& pool, EnvLits& L) 
   NBRM_LITS(X)
 #undef X
   auto add = [&](const std::string& s) {
-    Span sp = mk((uint32_t)pool.size(), (uint32_t)s.size());
+    PoolSpan sp;
+    sp.off = (uint32_t)pool.size();
+    sp.len = (uint32_t)s.size();
     pool += s;
     pool += '\0';
     return sp;

@@ -33,7 +33,8 @@ static const uint32_t TAPE_POS_MASK = (1u << 21) - 1;
 static const uint32_t TAPE_MAX_DOC = 1u << 21;
 static const uint32_t TAPE_MAX_DEPTH = 63;
 static const uint32_t TAPE_NOLINK = 0xffffu;
-static const uint32_t DOC_WS = 1u;  // Doc::tflags: whitespace (or control bytes) between tokens
+static const uint32_t DOC_WS = 1u;    // Doc::tflags: whitespace (or control bytes) between tokens
+static const uint32_t DOC_COOP = 2u;  // all 32 lanes of the warp walk this document together (plan_kernel_warp)
 
 NB_HD uint32_t tpos(uint32_t w) { return w & TAPE_POS_MASK; }
 NB_HD uint32_t tkind(uint32_t w) { return (w >> 21) & 7u; }

@@ -37,7 +37,7 @@ class ReconcilePass:
         self.odh_flags = capi.GEN_OWNER_REF | capi.GEN_OWNER_V1
         self.odh_decide = False
 
-    def set_cluster_state(self, found, stss, pods, odh_found=None):
+    def set_cluster_state(self, found, stss, pods, odh_found=None, index=True):
         """The informer-cache side: found objects (3 per Notebook), StatefulSets and Pods;
         optionally the found ODH objects (7 per Notebook, empty = NotFound): with them the
         "odh" result is what the ODH reconcilers write (create / update / nothing) instead
@@ -48,6 +48,10 @@ class ReconcilePass:
         self.odh_decide = odh_found is not None
         if self.odh_decide:
             self.ctx.upload(SLOT_ODH_FOUND, odh_found)
+        if index:
+            # the informer-cache analogue: resident objects are indexed once, when they arrive
+            for slot in (SLOT_FOUND, SLOT_STS, SLOT_PODS) + ((SLOT_ODH_FOUND,) if self.odh_decide else ()):
+                self.ctx.slot_index(slot)
 
     def upload_requests(self, requests, seeds=None):
         self.ctx.upload(SLOT_REQUESTS, requests)

@@ -484,12 +484,15 @@ def poddefaults_for_namespace(rng, ns, count):
     return out
 
 
-def admission_pod(rng, i, ns, n_pds, match_rate=0.3):
+def admission_pod(rng, i, ns, n_pds, match_rate=0.3, per_poddefault=False):
     """Pod of one admission request, shaped like a Notebook StatefulSet's pod
-    (1-3 containers, 0-8 env, 0-4 mounts, 3-8 labels)."""
+    (1-3 containers, 0-8 env, 0-4 mounts, 3-8 labels).  match_rate: per_poddefault=True reads
+    SURVEY.md 8(d)'s "match rate 30 %" literally, every PodDefault of the namespace matches a
+    Pod with that probability (30 of 100 on average); False thins it by sqrt(n) so that a Pod
+    matches about three at every n (a cluster whose PodDefaults are opt-in features)."""
     labels = {"statefulset": "nb-%06d" % i, "notebook-name": "nb-%06d" % i, "app": "nb"}
     for j in range(n_pds):
-        if rng.random() < match_rate / max(1, n_pds ** 0.5):
+        if rng.random() < (match_rate if per_poddefault else match_rate / max(1, n_pds ** 0.5)):
             labels["pd-%d" % j] = "true"
     if rng.random() < 0.3:
         labels["tier"] = rng.choice(["gpu", "cpu", "other"])
@@ -526,7 +529,7 @@ def admission_pod(rng, i, ns, n_pds, match_rate=0.3):
     return {"apiVersion": "v1", "kind": "Pod", "metadata": md, "spec": spec}
 
 
-def admission_workload(n_pods, pds_per_ns, seed=SEED, pods_per_ns=20):
+def admission_workload(n_pods, pds_per_ns, seed=SEED, pods_per_ns=20, per_poddefault=False):
     """C3: (pods, poddefaults, ranges) — ranges[i] = [begin, end) of pods[i]'s
     namespace inside the PodDefault list."""
     rng = random.Random(seed + pds_per_ns)
@@ -539,7 +542,7 @@ def admission_workload(n_pods, pds_per_ns, seed=SEED, pods_per_ns=20):
     pods, ranges = [], []
     for i in range(n_pods):
         k = i // pods_per_ns
-        pods.append(admission_pod(rng, i, "ns-%03d" % k, pds_per_ns))
+        pods.append(admission_pod(rng, i, "ns-%03d" % k, pds_per_ns, per_poddefault=per_poddefault))
         ranges.append(ns_range[k])
     return pods, pds, ranges
 

@@ -20,12 +20,14 @@ ctx.run(5, 0, flags=1)           # mutate
 ctx.result_to_slot(0)
 ctx.run(0, 0, flags=7 | 8)       # nbc
 desired = ctx.download().docs()
-out = {}
+out = {"mode": os.environ.get("NBRM_PLAN_MODE", "auto"), "index_found": os.environ.get("PROBE_INDEX", "0")}
 for name, sel in (("sts", [0]), ("svc", [1]), ("vs", [2]), ("mix", [0, 1, 2])):
     d = [desired[3 * i + k] for i in range(N) for k in sel]
     f = [found[3 * i + k] for i in range(N) for k in sel]
     ctx.upload(0, pkg.Docs(d))
     ctx.upload(1, pkg.Docs(f))
+    if out["index_found"] == "1":
+        ctx.slot_index(1)
     for _ in range(2):
         ctx.run(2, 0, 1)
     ctx.sync()

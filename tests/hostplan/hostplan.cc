@@ -31,6 +31,7 @@ struct Out {
   std::vector<uint64_t> off;
   std::vector<uint32_t> status;
   std::vector<uint32_t> result;
+  std::vector<ViewRec> views;  // NOBJ per tuple, as the generator recorded them
 };
 Out g_out;
 #ifdef NBRM_TAPE
@@ -55,6 +56,8 @@ int run_host(const char* const data[3], const uint64_t* const off[3], uint64_t n
   const uint32_t cap = G::CAP;
   std::vector<Seg> segs((size_t)G::NOBJ * cap);
   std::vector<uint32_t> nseg(G::NOBJ), lens(G::NOBJ);
+  std::vector<ViewEnt> views((size_t)G::NOBJ * VIEW_FIELDS);
+  g_out.views.clear();
   const char* bases[SRC_COUNT] = {data[0], data[1], data[2], pool.data(), aux.data()};
   for (uint64_t i = 0; i < n; ++i) {
     DocCtx c;
@@ -102,7 +105,19 @@ int run_host(const char* const data[3], const uint64_t* const off[3], uint64_t n
     s.nseg = nseg.data();
     s.lens = lens.data();
     s.cap = cap;
+    memset(views.data(), 0, views.size() * sizeof(ViewEnt));
+    s.views.p = views.data();
+    s.views.n = G::NOBJ;
+    s.view_j = 0;
     uint32_t st = G::run(c, s);
+    for (uint32_t k = 0; k < G::NOBJ; ++k) {  // back to one record per object for the tests
+      ViewRec r;
+      for (uint32_t f = 0; f < VIEW_FIELDS; ++f) {
+        r.off[f] = views[(size_t)f * G::NOBJ + k].off;
+        r.len[f] = views[(size_t)f * G::NOBJ + k].len;
+      }
+      g_out.views.push_back(r);
+    }
     g_out.status[i] = st;
     g_out.result[i] = c.result;
     for (uint32_t k = 0; k < G::NOBJ; ++k) {
@@ -137,6 +152,25 @@ HP_API void hostplan_set_tape_cap(uint32_t cap) {
 #else
   (void)cap;
 #endif
+}
+
+// The views the last hostplan_run's generator recorded (VIEW_FIELDS offsets then VIEW_FIELDS
+// lengths per object), and what view_object finds by walking a document, in the same layout.
+HP_API const uint32_t* hostplan_views(uint32_t* fields) {
+  *fields = VIEW_FIELDS;
+  return reinterpret_cast<const uint32_t*>(g_out.views.data());
+}
+HP_API void hostplan_view_object(const char* p, uint32_t n, uint32_t* out) {
+  Doc d;
+  d.p = p;
+  d.n = n;
+  const ObjView v = view_object(d);
+  const Span f[VIEW_FIELDS] = {v.root, v.kind, v.meta, v.labels, v.annotations, v.spec, v.replicas,
+                               v.tlabels, v.tpod, v.selector, v.ports, find(d, v.root, "subjects")};
+  for (uint32_t k = 0; k < VIEW_FIELDS; ++k) {
+    out[k] = f[k].off;
+    out[VIEW_FIELDS + k] = f[k].len;
+  }
 }
 
 // The scalar index builder on one document (tape build only); returns the entry count.

@@ -65,12 +65,14 @@ def check_odh_generate(nbs, outs, status, ctrl_ns, seeds, flags):
     return n_checked
 
 
-def check_copy_fields(desired, found, outs, status):
-    """desired/found: trees (found None = NotFound, desired None = nothing desired)."""
+def check_copy_fields(desired, found, outs, status, rejected=False):
+    """desired/found: trees (found None = NotFound, desired None = nothing desired).
+    rejected=True: a missing desired object means the generators rejected the Notebook (the
+    reference panics), and the fused pass reports that on the pair (nbrm_nbc_reconcile)."""
     n_update = n_create = n_none = 0
     for i, (d, f) in enumerate(zip(desired, found)):
         if d is None:
-            assert outs[i] == b"" and status[i] == 0
+            assert outs[i] == b"" and (status[i] != 0 if rejected else status[i] == 0), (i, status[i])
             continue
         try:
             exp = nbc.create_or_update(d, f)

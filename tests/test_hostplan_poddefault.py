@@ -41,3 +41,16 @@ def test_c3_workload(hostplan, wl):
         assert seen["patched"] > 30 and seen["none"] > 30, (per_ns, seen)
         if per_ns >= 10:
             assert seen["conflict"] > 0, (per_ns, seen)
+
+
+def test_c3_literal_match_rate(hostplan, wl):
+    """SURVEY.md 8(d) read literally: each of the 100 PodDefaults of a namespace matches a Pod
+    with probability 0.3, i.e. 30 applied PodDefaults per Pod on average and 45 at the tail.
+    The reference has no limit on how many it applies; nor may the library at these sizes."""
+    pods, pds, ranges = wl.admission_workload(240, 100, per_poddefault=True)
+    pd_docs = pack(wl, pods, pds)
+    outs, st, res = hostplan.poddefault(pd_docs[0], pd_docs[1], ranges)
+    assert not (st == 8).any(), "NBRM_E_LIMIT at BASELINE sizes"
+    seen = check_poddefault(pods, pds, ranges, outs, st, res)
+    applied = [int(r) for r, s_ in zip(res, st) if s_ == 0 and r]
+    assert seen["patched"] + seen["conflict"] > 150 and max(applied + [0]) > 32, (seen, max(applied + [0]))

@@ -26,14 +26,14 @@ def test_limits_cpu_build(hostplan, wl):
     assert list(st) == [3, 0] and outs[0] == outs[1] == outs[2] == b"" and outs[3] != b""
     outs, st = hostplan.nbc_generate([_fragmented_notebook(wl, 20)], {}, 7)        # still fits
     assert list(st) == [0] and json.loads(outs[0])["spec"]["template"]["metadata"]["labels"]["k019"] == "v"
-    pod, pds = _many_poddefaults(wl, 33)
+    pod, pds = _many_poddefaults(wl, 129)
     outs, st, res = hostplan.poddefault([pod], pds)
-    assert list(st) == [8] and outs == [b""]                                       # 33 > 32 applied PodDefaults
-    pod, pds = _many_poddefaults(wl, 32)
+    assert list(st) == [8] and outs == [b""]                                       # 129 > 128 applied PodDefaults
+    pod, pds = _many_poddefaults(wl, 128)
     outs, st, res = hostplan.poddefault([pod], pds)
-    assert list(st) == [0] and int(res[0]) == 32
+    assert list(st) == [0] and int(res[0]) == 128
     env = json.loads(outs[0])[1]["value"]["containers"][0]["env"]
-    assert [e["name"] for e in env] == ["E%d" % i for i in range(32)]
+    assert [e["name"] for e in env] == ["E%d" % i for i in range(128)]
 
 
 @pytest.mark.gpu
@@ -41,9 +41,9 @@ def test_limits_gpu(ctx, pkg, wl):
     ctx.set_env({})
     res = ctx.nbc_generate(pkg.Docs([_fragmented_notebook(wl, 300), wl.dumps(wl.notebook_c2(4))]), 7)
     assert list(res.status) == [3, 0] and res.doc(0) == b"" and res.doc(3) != b""
-    pod, pds = _many_poddefaults(wl, 33)
+    pod, pds = _many_poddefaults(wl, 129)
     res = ctx.poddefault_mutate(pkg.Docs([pod]), pkg.Docs(pds))
     assert list(res.status) == [8] and res.doc(0) == b""
-    pod, pds = _many_poddefaults(wl, 32)
+    pod, pds = _many_poddefaults(wl, 128)
     res = ctx.poddefault_mutate(pkg.Docs([pod]), pkg.Docs(pds))
-    assert list(res.status) == [0] and int(res.result[0]) == 32
+    assert list(res.status) == [0] and int(res.result[0]) == 128
