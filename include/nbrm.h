@@ -93,7 +93,7 @@ typedef struct nbrm_out {
 
 /* Accumulated device time per kernel class since nbrm_profile_enable(ctx, 1),
  * measured with CUDA events on the context's stream. */
-#define NBRM_GENERATORS 16 /* size of the per-generator arrays below; ids 0..9 are in use */
+#define NBRM_GENERATORS 16 /* size of the per-generator arrays below; ids 0..12 are in use */
 typedef struct nbrm_profile {
   double plan_ms, scan_ms, emit_ms;
   uint64_t plan_launches, scan_launches, emit_launches;
@@ -365,6 +365,40 @@ int nbrm_upload_async(nbrm_ctx* ctx, int slot, const nbrm_docs* docs);
 int nbrm_download_begin(nbrm_ctx* ctx, int lane);
 int nbrm_download_slot_begin(nbrm_ctx* ctx, int slot, int lane);
 int nbrm_download_wait(nbrm_ctx* ctx, int lane, nbrm_out* out);
+
+/* ---- wire formats of the two webhooks -----------------------------------------
+ * nbrm_json_diff: the RFC 6902 patch that turns originals[i] into mutated[i]
+ * (length 0 when they are equal) — what admission.PatchResponseFromRaw
+ * (odh-notebook-controller/controllers/notebook_webhook.go:301) and
+ * jsonpatch.CreatePatch (admission-webhook/main.go:693) compute.  Both Go
+ * libraries order their operations by map iteration, so a patch is defined by
+ * its effect: applied to the original it gives the mutated document.  Arrays
+ * that only grew get one "add .../-" per new element.
+ *
+ * nbrm_notebook_webhook_review: NotebookWebhook.Handle end to end for a batch of
+ * AdmissionReview requests (notebook_webhook.go:234-302 and controller-runtime's
+ * response writer): request.object is mutated as by nbrm_odh_mutate (flags
+ * NBRM_MUT_*; is_update as there, with request.oldObject), and each output is
+ * the AdmissionReview response: kind / apiVersion echoed, response.uid echoed,
+ * allowed, patch (base64 of the JSON patch) and patchType when there is one;
+ * admission.Denied as allowed:false with status code 403 and the reference's
+ * message.  The caller sends reviews of one operation per call.
+ *
+ * nbrm_poddefault_review: serve(mutatePods) (admission-webhook/main.go:599-749)
+ * for a batch of AdmissionReview requests: the Pod's namespace falls back to
+ * request.namespace (:617-620), PodDefaults are applied as by
+ * nbrm_poddefault_mutate, and each output is {"response":{"uid":..,"allowed":..
+ * [,"patch":<base64>,"patchType":"JSONPatch"]}}; a conflict or a bad selector
+ * gives allowed:false with a status message (the reference's text carries
+ * Go-syntax dumps and is not reproduced); a request for anything but core/v1
+ * pods gives "{}" — a review without a response, as the reference writes it
+ * (:602-605, :733-737).  The Content-Type check of serve (:718-721: no body at
+ * all on a mismatch) is the HTTP server's and stays with the caller. */
+int nbrm_json_diff(nbrm_ctx* ctx, const nbrm_docs* originals, const nbrm_docs* mutated, nbrm_out* out);
+int nbrm_notebook_webhook_review(nbrm_ctx* ctx, const nbrm_docs* reviews, uint32_t flags, int is_update,
+                                 nbrm_out* out);
+int nbrm_poddefault_review(nbrm_ctx* ctx, const nbrm_docs* reviews, const nbrm_docs* poddefaults,
+                           const uint32_t* ranges, nbrm_out* out);
 
 /* ---- resident documents: index once ------------------------------------------
  * No counterpart in the reference as a function; it is what the reference's

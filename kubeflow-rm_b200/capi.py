@@ -94,6 +94,9 @@ def load_library():
     lib.nbrm_launch_count.restype = C.c_uint64
     lib.nbrm_upload.argtypes = [C.c_void_p, C.c_int, C.POINTER(_Docs)]
     lib.nbrm_slot_index.argtypes = [C.c_void_p, C.c_int]
+    lib.nbrm_json_diff.argtypes = [C.c_void_p, C.POINTER(_Docs), C.POINTER(_Docs), C.POINTER(_Out)]
+    lib.nbrm_notebook_webhook_review.argtypes = [C.c_void_p, C.POINTER(_Docs), C.c_uint32, C.c_int, C.POINTER(_Out)]
+    lib.nbrm_poddefault_review.argtypes = [C.c_void_p, C.POINTER(_Docs), C.POINTER(_Docs), C.c_void_p, C.POINTER(_Out)]
     lib.nbrm_tape_dump.argtypes = [C.c_void_p, C.c_int, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.nbrm_download.argtypes = [C.c_void_p, C.POINTER(_Out)]
     lib.nbrm_nbc_generate.argtypes = [C.c_void_p, C.POINTER(_Docs), C.c_uint32, C.POINTER(_Out)]
@@ -353,6 +356,26 @@ class Context:
         if ranges is not None:
             r = np.ascontiguousarray(np.asarray(ranges, dtype=np.uint32).reshape(-1))
         self._check(self.lib.nbrm_poddefault_mutate(self.h, C.byref(a), C.byref(b),
+                                                    r.ctypes.data if r is not None else None, C.byref(o)))
+        return Result(o, copy)
+
+    # --- wire formats: JSON patches and AdmissionReview responses
+    def json_diff(self, originals, mutated, copy=True):
+        a, b, o = originals.c_struct(), mutated.c_struct(), _Out()
+        self._check(self.lib.nbrm_json_diff(self.h, C.byref(a), C.byref(b), C.byref(o)))
+        return Result(o, copy)
+
+    def notebook_webhook_review(self, reviews, flags=MUT_CREATE, is_update=False, copy=True):
+        a, o = reviews.c_struct(), _Out()
+        self._check(self.lib.nbrm_notebook_webhook_review(self.h, C.byref(a), flags, 1 if is_update else 0, C.byref(o)))
+        return Result(o, copy)
+
+    def poddefault_review(self, reviews, poddefaults, ranges=None, copy=True):
+        a, b, o = reviews.c_struct(), poddefaults.c_struct(), _Out()
+        r = None
+        if ranges is not None:
+            r = np.ascontiguousarray(np.asarray(ranges, dtype=np.uint32).reshape(-1))
+        self._check(self.lib.nbrm_poddefault_review(self.h, C.byref(a), C.byref(b),
                                                     r.ctypes.data if r is not None else None, C.byref(o)))
         return Result(o, copy)
 

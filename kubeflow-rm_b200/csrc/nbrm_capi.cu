@@ -263,6 +263,8 @@ int check_docs(nbrm_ctx* c, const nbrm_docs* d) {
   if (d->n) {
     if (d->off[d->n] - d->off[0] >= 0xffffffffull - d->n * AUX_PAD)
       return fail_msg(c, "nbrm_docs: batch holds 4 GiB or more; split it");
+    for (uint64_t i = 0; i < d->n; ++i)
+      if (d->off[i + 1] < d->off[i]) return fail_msg(c, "nbrm_docs: offsets must not decrease");
   }
   return 0;
 }
@@ -294,6 +296,14 @@ int nbrm_ctx_create(int device, nbrm_ctx** out) {
     return -1;
   }
   cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device);
+  for (auto& s : c->slot) {  // nbrm_upload_async orders itself against readers through these
+    if (cudaEventCreateWithFlags(&s.uploaded, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&s.last_read, cudaEventDisableTiming) != cudaSuccess) {
+      fprintf(stderr, "libnbrm: cannot create events on device %d\n", device);
+      nbrm_ctx_destroy(c);
+      return -1;
+    }
+  }
   if (build_pool(c, nullptr) != 0) {
     fprintf(stderr, "libnbrm: %s\n", c->err.c_str());
     delete c;
@@ -447,10 +457,6 @@ int nbrm_upload_async(nbrm_ctx* c, int slot, const nbrm_docs* d) {
   if (int r = settle_slot_readers(c, slot)) return r;
   Slot& s = c->slot[slot];
   if (!c->up_stream) CK(cudaStreamCreateWithFlags(&c->up_stream, cudaStreamNonBlocking));
-  if (!s.uploaded) {
-    CK(cudaEventCreateWithFlags(&s.uploaded, cudaEventDisableTiming));
-    CK(cudaEventCreateWithFlags(&s.last_read, cudaEventDisableTiming));
-  }
   // generators already launched may still read the slot's old contents
   if (s.read_recorded) CK(cudaStreamWaitEvent(c->up_stream, s.last_read, 0));
   const uint64_t bytes = d->n ? d->off[d->n] : 0;
@@ -595,10 +601,8 @@ int run_generator(nbrm_ctx* c, int gen, const int (&map)[3], uint32_t flags, con
   for (int k = 0; k < 3; ++k) {  // for nbrm_upload_async: this generator read these slots
     if (map[k] < 0) continue;
     Slot& s = c->slot[map[k]];
-    if (s.last_read) {
-      CK(cudaEventRecord(s.last_read, c->stream));
-      s.read_recorded = true;
-    }
+    CK(cudaEventRecord(s.last_read, c->stream));
+    s.read_recorded = true;
   }
   c->res_n_in = n;
   c->res_n_out = n_out;
@@ -697,6 +701,10 @@ int nbrm_result_to_slot(nbrm_ctx* c, int slot) {
   s.has_views = c->res_views;
   c->res_views = false;
   s.indexed = false;
+  // the buffer now in the slot is still being written by the emit kernel, and the one that left
+  // it may still be read: an asynchronous upload into this slot waits for the compute stream
+  CK(cudaEventRecord(s.last_read, c->stream));
+  s.read_recorded = true;
   s.n = c->res_n_out;
   s.period = c->res_nobj;
   s.bytes = c->res_bytes;
@@ -832,8 +840,23 @@ int nbrm_run(nbrm_ctx* c, int generator, int slot_a, int slot_b, int slot_c, uin
   for (int k = 0; k < 3; ++k)
     if (map[k] >= NBRM_SLOTS) return fail_msg(c, "nbrm_run: slot out of range");
   if (slot_a < 0) return fail_msg(c, "nbrm_run: the first input slot is required");
-  return run_generator(c, generator, map, flags, use_side_input && c->extra_bytes ? c->extra.p : nullptr,
-                       now_unix, arg0, arg1);
+  const void* side = nullptr;
+  if (use_side_input && c->extra_bytes) {
+    // the side input is read at a generator-specific stride: check it against this batch
+    const uint64_t n = c->slot[slot_a].n;
+    uint64_t want = 0;
+    switch (generator) {
+      case GEN_ID_ODH: want = n * 16; break;        // 16 seed bytes per Notebook
+      case GEN_ID_CULL: want = n; break;            // pod_exists, one byte per Notebook
+      case GEN_ID_PODDEFAULT: want = n * 8; break;  // [begin, end) per Pod
+      default: return fail_msg(c, "nbrm_run: this generator takes no side input");
+    }
+    if (c->extra_bytes != want)
+      return fail_msg(c, "nbrm_run: the side input uploaded with nbrm_upload_bytes does not fit this batch");
+    side = c->extra.p;
+  }
+  // the bytes stay until nbrm_upload_bytes replaces them (a resident batch is planned many times)
+  return run_generator(c, generator, map, flags, side, now_unix, arg0, arg1);
 }
 
 int nbrm_download_slot(nbrm_ctx* c, int slot, nbrm_out* out) {
@@ -944,6 +967,78 @@ int nbrm_download_wait(nbrm_ctx* c, int lane_id, nbrm_out* out) {
   for (uint32_t i = 0; i < l.n_in; ++i)
     if (out->status[i]) return 1;
   return 0;
+}
+
+// ---- wire formats (nbrm_patch.cuh)
+static int status_to_extra(nbrm_ctx* c, const uint32_t* keep) {
+  // the status words of the stage that made the patches become the side input of the
+  // envelope stage; `keep` (earlier stage, may be null) wins where it is not 0
+  const uint32_t n = c->res_n_in;
+  if (keep) {
+    launch_merge_status(keep, c->status.as<uint32_t>(), n, 1, c->stream);
+    c->launches += n ? 1 : 0;
+  }
+  CK(c->extra.reserve((size_t)n * 4 + 16));
+  launch_copy_u32(c->status.as<uint32_t>(), c->extra.as<uint32_t>(), n, c->stream);
+  c->launches += n ? 1 : 0;
+  c->extra_bytes = (uint64_t)n * 4;
+  CK(cudaGetLastError());
+  return 0;
+}
+
+int nbrm_json_diff(nbrm_ctx* c, const nbrm_docs* originals, const nbrm_docs* mutated, nbrm_out* out) {
+  if (!c || !out) return -2;
+  if (int r = nbrm_upload(c, 0, originals)) return r;
+  if (int r = nbrm_upload(c, 1, mutated)) return r;
+  if (int r = run_generator(c, GEN_ID_DIFF, {0, 1, -1}, 0, nullptr, 0)) return r;
+  return nbrm_download(c, out);
+}
+
+int nbrm_notebook_webhook_review(nbrm_ctx* c, const nbrm_docs* reviews, uint32_t flags, int is_update,
+                                 nbrm_out* out) {
+  if (!c || !out) return -2;
+  const int S_REVIEWS = 9, S_MUTATED = 10, S_PATCH = 11;
+  if (int r = nbrm_upload(c, S_REVIEWS, reviews)) return r;
+  if (int r = run_generator(c, GEN_ID_REVIEW_OPEN, {S_REVIEWS, -1, -1}, 0, nullptr, 0)) return r;
+  if (int r = nbrm_result_to_slot(c, 1)) return r;  // request.object: what the mutation reads
+  if (is_update) {
+    if (int r = run_generator(c, GEN_ID_REVIEW_OPEN, {S_REVIEWS, -1, -1}, 2u /* REVIEW_OLD */, nullptr, 0)) return r;
+    if (int r = nbrm_result_to_slot(c, 2)) return r;
+  }
+  if (int r = nbrm_odh_mutate_resident(c, flags, is_update)) return r;
+  const uint32_t n = c->res_n_in;
+  CK(c->gen_status.reserve((size_t)n * 4 + 16));
+  launch_copy_u32(c->status.as<uint32_t>(), c->gen_status.as<uint32_t>(), n, c->stream);
+  c->launches += n ? 1 : 0;
+  if (int r = nbrm_result_to_slot(c, S_MUTATED)) return r;
+  // admission.PatchResponseFromRaw(req.Object.Raw, marshaledNotebook) (notebook_webhook.go:301)
+  if (int r = run_generator(c, GEN_ID_DIFF, {1, S_MUTATED, -1}, 0, nullptr, 0)) return r;
+  if (int r = status_to_extra(c, c->gen_status.as<uint32_t>())) return r;
+  if (int r = nbrm_result_to_slot(c, S_PATCH)) return r;
+  if (int r = run_generator(c, GEN_ID_REVIEW_CLOSE, {S_REVIEWS, S_PATCH, -1}, 1u /* REVIEW_CTRL_RUNTIME */,
+                            c->extra.p, 0))
+    return r;
+  c->extra_bytes = 0;
+  return nbrm_download(c, out);
+}
+
+int nbrm_poddefault_review(nbrm_ctx* c, const nbrm_docs* reviews, const nbrm_docs* poddefaults,
+                           const uint32_t* ranges, nbrm_out* out) {
+  if (!c || !out) return -2;
+  const int S_REVIEWS = 9, S_PATCH = 11;
+  if (int r = nbrm_upload(c, S_REVIEWS, reviews)) return r;
+  if (int r = nbrm_upload(c, 1, poddefaults)) return r;
+  if (int r = run_generator(c, GEN_ID_REVIEW_OPEN, {S_REVIEWS, -1, -1}, 0, nullptr, 0)) return r;
+  if (int r = nbrm_result_to_slot(c, 0)) return r;  // the Pods, namespace filled from the request
+  if (int r = nbrm_upload_bytes(c, ranges, ranges ? reviews->n * 8 : 0)) return r;
+  if (int r = nbrm_poddefault_mutate_resident(c)) return r;
+  if (int r = status_to_extra(c, nullptr)) return r;
+  if (int r = nbrm_result_to_slot(c, S_PATCH)) return r;
+  // serve: uid echoed, patch base64, no response at all for anything but core/v1 pods (main.go:708-749)
+  if (int r = run_generator(c, GEN_ID_REVIEW_CLOSE, {S_REVIEWS, S_PATCH, -1}, 4u /* REVIEW_PODS_ONLY */, c->extra.p, 0))
+    return r;
+  c->extra_bytes = 0;
+  return nbrm_download(c, out);
 }
 
 int nbrm_slot_index(nbrm_ctx* c, int slot) {

@@ -233,11 +233,11 @@ NB_HD bool json_equal_t(const Doc& a, Span x, const Doc& b, Span y, bool* overfl
   }
 }
 
-NB_HD bool json_equal(const Doc& a, Span x, const Doc& b, Span y) {
-  return json_equal_t<false>(a, x, b, y);
+NB_HD bool json_equal(const Doc& a, Span x, const Doc& b, Span y, bool* overflow = nullptr) {
+  return json_equal_t<false>(a, x, b, y, overflow);
 }
-NB_HD bool semantic_equal(const Doc& a, Span x, const Doc& b, Span y) {
-  return json_equal_t<true>(a, x, b, y);
+NB_HD bool semantic_equal(const Doc& a, Span x, const Doc& b, Span y, bool* overflow = nullptr) {
+  return json_equal_t<true>(a, x, b, y, overflow);
 }
 
 // ---------------------------------------------------------------- Copy*Fields
@@ -400,13 +400,15 @@ NB_HD void plan_copy_fields(Planner& P, const Doc& from, const Doc& to, const Vi
     P.err = E_PARSE;
     return;
   }
+  bool deep = false;  // set when a compare met nesting beyond EQ_MAX_DEPTH
   bool require = map_field_differs(from, fv.labels, to, tv.labels);        // util.go:109-113
   require |= map_field_differs(from, fv.annotations, to, tv.annotations);  // :116-120
 
   if (str_eq(from, fv.kind, "VirtualService")) {  // CopyVirtualService, util.go:199-219
     if (!is_object(from, fv.spec)) return;         // :200-206 from has no spec map: false
-    bool upd = !is_object(to, tv.spec) || !json_equal(from, fv.spec, to, tv.spec);
-    if (!upd) return;
+    bool upd = !is_object(to, tv.spec) || !json_equal(from, fv.spec, to, tv.spec, &deep);
+    if (deep) P.err = E_LIMIT;  // nested deeper than the compare follows: no answer, not "differs"
+    if (!upd || deep) return;
     LIT(P, LBRACE);
     Sep s;
     ObjIter it(to, tv.root);
@@ -425,9 +427,10 @@ NB_HD void plan_copy_fields(Planner& P, const Doc& from, const Doc& to, const Vi
   if (str_eq(from, fv.kind, "Service")) {  // CopyServiceFields, util.go:166-195
     Span fsel = fv.selector, fports = fv.ports;
     Span tsel = tv.selector, tports = tv.ports;
-    if (!json_equal(from, fsel, to, tsel)) require = true;      // :184
-    if (!json_equal(from, fports, to, tports)) require = true;  // :189
-    if (!require) return;
+    if (!json_equal(from, fsel, to, tsel, &deep)) require = true;      // :184
+    if (!json_equal(from, fports, to, tports, &deep)) require = true;  // :189
+    if (deep) P.err = E_LIMIT;
+    if (!require || deep) return;
     LIT(P, LBRACE);
     Sep s;
     bool had_spec = false;
@@ -496,10 +499,11 @@ NB_HD void plan_copy_fields(Planner& P, const Doc& from, const Doc& to, const Vi
   Span fpod = fv.tpod, tpod = tv.tpod;
   const bool replicas_differ = !spans_eq(from, frep, to, trep);
   // pre-copy: template labels follow only when the replica counts differ
-  const bool copy_tlabels = replicas_differ && !json_equal(from, ftlabels, to, ttlabels);
-  if (replicas_differ) require = true;                      // :123-126
-  if (!json_equal(from, fpod, to, tpod)) require = true;    // :128-130
-  if (!require) return;
+  const bool copy_tlabels = replicas_differ && !json_equal(from, ftlabels, to, ttlabels, &deep);
+  if (replicas_differ) require = true;                             // :123-126
+  if (!json_equal(from, fpod, to, tpod, &deep)) require = true;    // :128-130
+  if (deep) P.err = E_LIMIT;
+  if (!require || deep) return;
 
   LIT(P, LBRACE);
   Sep s;

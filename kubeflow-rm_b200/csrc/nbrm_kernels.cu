@@ -210,9 +210,16 @@ struct Writer {
 };
 
 __device__ __forceinline__ void copy_segment(const char* src, uint32_t len, Writer& W) {
+  if (!len) return;
   unsigned long long a = (unsigned long long)src;
+  const unsigned long long last = (a + len - 1) & ~15ull;  // the aligned block that holds the last byte
+  uint4 w = *reinterpret_cast<const uint4*>(a & ~15ull);
   while (len) {
-    const uint4 w = *reinterpret_cast<const uint4*>(a & ~15ull);
+    // the next block is on its way while this one is written out (a thread's loads are
+    // otherwise a chain: descriptor -> source block -> source block ...)
+    const unsigned long long nb = (a & ~15ull) + 16;
+    uint4 wn = w;
+    if (nb <= last) wn = *reinterpret_cast<const uint4*>(nb);
     const uint32_t k = (uint32_t)a & 15u;
     const uint32_t avail = min(16u - k, len);
     uint32_t done = 0;
@@ -220,12 +227,13 @@ __device__ __forceinline__ void copy_segment(const char* src, uint32_t len, Writ
       const uint32_t kk = k + done;
       const uint32_t word = (kk & 8u) ? ((kk & 4u) ? w.w : w.z) : ((kk & 4u) ? w.y : w.x);
       const uint32_t sh = kk & 3u;
-      const uint32_t nb = min(4u - sh, avail - done);
-      W.put(word >> (8u * sh), nb);
-      done += nb;
+      const uint32_t nb4 = min(4u - sh, avail - done);
+      W.put(word >> (8u * sh), nb4);
+      done += nb4;
     }
     a += avail;
     len -= avail;
+    w = wn;
   }
 }
 
@@ -248,8 +256,10 @@ __global__ void __launch_bounds__(EMIT_THREADS) emit_objects(const Seg* __restri
   const Seg* s = segs + (size_t)obj * cap;
   Writer W;
   W.init(out + off[obj]);
+  Seg next = s[0];
   for (uint32_t j = 0; j < ns; ++j) {
-    const Seg sg = s[j];
+    const Seg sg = next;
+    if (j + 1 < ns) next = s[j + 1];  // the next descriptor loads while this segment is copied
     copy_segment(bases.p[sg.len_src >> 28] + sg.off, sg.len_src & SEG_LEN_MASK, W);
   }
   W.finish();
@@ -353,17 +363,18 @@ extern "C" int nbrm_scan_lengths_noalloc(const uint32_t* d_lens, uint64_t n, uin
     return noalloc_fail(err, err_cap, -2, "device ordinal out of range", nullptr);
   uint64_t* tiles = nullptr;
   {
-    // Set-up: once per device, done by the first call made with that device
-    // current (it is current here: cudaGetDevice just reported it).
+    // Set-up: the device address of the array, looked up with that device current (it is
+    // current here: cudaGetDevice just reported it).  The first call on a device is the one
+    // that may load the module; later calls repeat the lookup, which is then a table read
+    // and allocates nothing, because an address remembered from before a cudaDeviceReset
+    // would point into a context that no longer exists.
     std::lock_guard<std::mutex> lock(g_noalloc_mu);
-    if (!g_noalloc_dev_ptr[dev]) {
-      uint64_t* p = nullptr;
-      e = cudaGetSymbolAddress((void**)&p, g_noalloc_tile_sums);
-      if (e != cudaSuccess || !p)
-        return noalloc_fail(err, err_cap, -1, "cudaGetSymbolAddress", cudaGetErrorString(e));
-      g_noalloc_dev_ptr[dev] = p;
-    }
-    tiles = g_noalloc_dev_ptr[dev];
+    uint64_t* p = nullptr;
+    e = cudaGetSymbolAddress((void**)&p, g_noalloc_tile_sums);
+    if (e != cudaSuccess || !p)
+      return noalloc_fail(err, err_cap, -1, "cudaGetSymbolAddress", cudaGetErrorString(e));
+    g_noalloc_dev_ptr[dev] = p;
+    tiles = p;
   }
   nbrm::launch_scan(d_lens, (uint32_t)n, tiles, d_off, (cudaStream_t)stream);
   e = cudaGetLastError();

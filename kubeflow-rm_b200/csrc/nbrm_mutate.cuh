@@ -424,7 +424,14 @@ struct GenRestartGuard {
       if (!mv.a_stopped.ok() && !mv.a_restart.ok()) {
         const Span up = FIND(upd, FIND(upd, FIND(upd, root(upd), "spec"), "template"), "spec");
         const Span op = FIND(old, FIND(old, FIND(old, root(old), "spec"), "template"), "spec");
-        if (semantic_equal(old, op, upd, up) && !semantic_equal(old, op, mut, mv.podspec)) {  // :353-362
+        bool deep = false;
+        const bool changed_by_webhook =
+            semantic_equal(old, op, upd, up, &deep) && !semantic_equal(old, op, mut, mv.podspec, &deep);  // :353-362
+        if (deep) {  // nested deeper than the compare follows: no answer, not "differs"
+          P.err = E_LIMIT;
+          return;
+        }
+        if (changed_by_webhook) {
           mp.pending = 2;          // :290
           mp.podspec_k = 1;        // :368 keep the pod template the request carried
           mp.podspec_src = up;

@@ -27,9 +27,9 @@ namespace nbrm {
 enum OdhWrite : uint32_t { ODH_NONE = 0, ODH_CREATE = 1, ODH_UPDATE = 2 };
 
 // DeepEqual of two Route specs with spec.host left out on both sides (:67).
-NB_HD bool route_spec_equal(const Doc& a, Span x, const Doc& b, Span y) {
+NB_HD bool route_spec_equal(const Doc& a, Span x, const Doc& b, Span y, bool* deep) {
   const bool xo = is_object(a, x), yo = is_object(b, y);
-  if (!xo || !yo) return json_equal(a, x, b, y);
+  if (!xo || !yo) return json_equal(a, x, b, y, deep);
   uint32_t na = 0, nb = 0;
   {
     ObjIter it(b, y);
@@ -43,7 +43,7 @@ NB_HD bool route_spec_equal(const Doc& a, Span x, const Doc& b, Span y) {
     if (KEY_IS(a, m, "host") || is_nil(a, m.val)) continue;
     ++na;
     const Span bv = find_key(b, y, a, m.key);
-    if (is_nil(b, bv) || !json_equal(a, m.val, b, bv)) return false;
+    if (is_nil(b, bv) || !json_equal(a, m.val, b, bv, deep)) return false;
   }
   return na == nb;
 }
@@ -168,14 +168,23 @@ NB_HD uint32_t plan_odh_decide(Planner& P, const Doc& from, const Doc& to, const
       else if (KEY_IS(to, m, "subjects")) tsubj = m.val;
     }
   }
+  bool deep = false;
   if (is_rb) {
-    if (json_equal(from, fsubj, to, tsubj)) return ODH_NONE;
+    if (json_equal(from, fsubj, to, tsubj, &deep)) return ODH_NONE;
+    if (deep) {
+      P.err = E_LIMIT;
+      return ODH_NONE;
+    }
     plan_without_owner(P, from);
     return ODH_UPDATE;
   }
   const Span tlabels = FIND(to, tmeta, "labels");
-  bool same = json_equal(from, flabels, to, tlabels);
-  if (same) same = is_route ? route_spec_equal(from, fspec, to, tspec) : json_equal(from, fspec, to, tspec);
+  bool same = json_equal(from, flabels, to, tlabels, &deep);
+  if (same) same = is_route ? route_spec_equal(from, fspec, to, tspec, &deep) : json_equal(from, fspec, to, tspec, &deep);
+  if (deep) {
+    P.err = E_LIMIT;  // nested deeper than the compare follows: no answer, not "differs"
+    return ODH_NONE;
+  }
   if (same) return ODH_NONE;
   plan_spec_labels_update(P, from, fspec, flabels, to);
   return ODH_UPDATE;

@@ -22,7 +22,6 @@
 
 namespace nbrm {
 
-enum PdErr : uint32_t { E_SELECTOR = 9 };  // label selector conversion failed (:77-79)
 
 // Fixed room per Pod.  BASELINE.json's admission config lists up to 100 PodDefaults per
 // namespace; the reference applies however many match (main.go:72-97 has no limit), so the
@@ -42,7 +41,9 @@ NB_HD Doc pd_doc(const DocCtx& c, uint32_t j) {
 // Out-of-line doors to the deep compare and the key lookup of nbrm_cmp.cuh: the
 // merges below call them from many places, and one copy each keeps this kernel's
 // compile time in seconds (inlined everywhere it took twenty minutes).
-NB_FN bool pd_equal(const Doc& a, Span x, const Doc& b, Span y) { return json_equal(a, x, b, y); }
+NB_FN bool pd_equal(const Doc& a, Span x, const Doc& b, Span y, bool* overflow) {
+  return json_equal(a, x, b, y, overflow);
+}
 NB_FN Span pd_find_key(const Doc& d, Span obj, const Doc& kd, Span key) { return find_key(d, obj, kd, key); }
 
 // String value or "" when the member is missing / not a string.
@@ -173,7 +174,7 @@ NB_FN void merge_keyed(PdCtx& x, Span existing, const char (&field)[NF], const c
           if (strval_equal(pod, find(pod, e, key), pd, vk)) held = e;
       }
       if (held.ok()) {
-        if (!pd_equal(pod, held, pd, v)) x.conflict = true;
+        if (!pd_equal(pod, held, pd, v, &x.overflow)) x.conflict = true;
         continue;
       }
       // ... or the first appended item with it
@@ -182,7 +183,7 @@ NB_FN void merge_keyed(PdCtx& x, Span existing, const char (&field)[NF], const c
         const Doc od = pd_doc(*x.c, out.a[k].pd);
         if (strval_equal(od, find(od, out.a[k].s, key), pd, vk)) {
           found = true;
-          if (!pd_equal(od, out.a[k].s, pd, v)) x.conflict = true;
+          if (!pd_equal(od, out.a[k].s, pd, v, &x.overflow)) x.conflict = true;
         }
       }
       if (found) continue;
@@ -219,7 +220,7 @@ NB_FN void merge_volume_mounts(PdCtx& x, Span existing, AddList& out, AddList& p
           if (strval_equal(pod, ek, pd, vk)) held = e;
         }
         if (held.ok()) {
-          if (!pd_equal(pod, held, pd, v)) x.conflict = true;
+          if (!pd_equal(pod, held, pd, v, &x.overflow)) x.conflict = true;
           continue;
         }
         bool found = false;
@@ -228,7 +229,7 @@ NB_FN void merge_volume_mounts(PdCtx& x, Span existing, AddList& out, AddList& p
           const Span ok = pass ? find(od, tab.a[k].s, "mountPath") : find(od, tab.a[k].s, "name");
           if (strval_equal(od, ok, pd, vk)) {
             found = true;
-            if (!pd_equal(od, tab.a[k].s, pd, v)) x.conflict = true;
+            if (!pd_equal(od, tab.a[k].s, pd, v, &x.overflow)) x.conflict = true;
           }
         }
         if (found) continue;

@@ -30,6 +30,7 @@ enum Err : uint32_t {
   E_DENIED = 6,         // admission denied by the reference's own rule
   E_CONFLICT = 7,       // PodDefault merge conflict (admission-webhook/main.go:671-679)
   E_LIMIT = 8,          // a documented fixed limit of this implementation was exceeded
+  E_SELECTOR = 9,       // a PodDefault's label selector does not convert (admission-webhook/main.go:77-79)
 };
 
 struct Seg {
@@ -72,6 +73,11 @@ struct Planner {
   }
   NB_HD void put(uint32_t src, uint32_t off, uint32_t len) {
     if (!len) return;
+    while (len > SEG_LEN_MASK) {  // a span of 256 MiB or more goes out as several segments
+      put(src, off, SEG_LEN_MASK);
+      off += SEG_LEN_MASK;
+      len -= SEG_LEN_MASK;
+    }
     total += len;
     if (cur_len && cur_src == src && cur_off + cur_len == off && cur_len + len <= SEG_LEN_MASK) {
       cur_len += len;

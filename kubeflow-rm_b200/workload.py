@@ -259,6 +259,98 @@ def found_variant(rng, desired):
     return f
 
 
+# ---------------------------------------------------------------- API-server-shaped objects
+# What a Get returns after the object went through an API server: members in the order of
+# the Go structs' fields (k8s.io/api, recalled from v0.29 — nothing asserts it here, and the
+# library does not depend on it: DeepEqual is order-free), the fields defaulting adds to a
+# StatefulSet / Service, server-side metadata with managedFields, and a status.
+_GO_ORDER = {
+    "": ["kind", "apiVersion", "metadata", "spec", "status"],
+    "metadata": ["name", "generateName", "namespace", "uid", "resourceVersion", "generation", "creationTimestamp",
+                 "deletionTimestamp", "labels", "annotations", "ownerReferences", "finalizers", "managedFields"],
+    "sts.spec": ["replicas", "selector", "template", "volumeClaimTemplates", "serviceName", "podManagementPolicy",
+                 "updateStrategy", "revisionHistoryLimit", "minReadySeconds", "persistentVolumeClaimRetentionPolicy"],
+    "podspec": ["volumes", "initContainers", "containers", "ephemeralContainers", "restartPolicy",
+                "terminationGracePeriodSeconds", "activeDeadlineSeconds", "dnsPolicy", "nodeSelector",
+                "serviceAccountName", "serviceAccount", "automountServiceAccountToken", "nodeName", "hostNetwork",
+                "hostPID", "hostIPC", "shareProcessNamespace", "securityContext", "imagePullSecrets", "hostname",
+                "subdomain", "affinity", "schedulerName", "tolerations", "hostAliases", "priorityClassName", "priority"],
+    "container": ["name", "image", "command", "args", "workingDir", "ports", "envFrom", "env", "resources",
+                  "resizePolicy", "restartPolicy", "volumeMounts", "volumeDevices", "livenessProbe", "readinessProbe",
+                  "startupProbe", "lifecycle", "terminationMessagePath", "terminationMessagePolicy", "imagePullPolicy",
+                  "securityContext", "stdin", "stdinOnce", "tty"],
+    "svc.spec": ["ports", "selector", "clusterIP", "clusterIPs", "type", "externalIPs", "sessionAffinity",
+                 "loadBalancerIP", "ipFamilies", "ipFamilyPolicy", "internalTrafficPolicy"],
+}
+
+
+def _ordered(d, which):
+    first = [k for k in _GO_ORDER[which] if k in d]
+    return {k: d[k] for k in first + [k for k in d if k not in first]}
+
+
+def server_shaped(desired, i=0):
+    """`desired` (StatefulSet, Service or an unstructured object such as a VirtualService)
+    as the API server would hand it back on the next Get."""
+    import copy
+    f = copy.deepcopy(desired)
+    kind = f.get("kind")
+    md = f.setdefault("metadata", {})
+    md.update({"uid": "%08x-aaaa-4bbb-8ccc-%012x" % (i & 0xffffffff, i), "resourceVersion": str(70000 + i),
+               "generation": 1, "creationTimestamp": "2026-11-06T00:00:00Z",
+               "managedFields": [{"manager": "manager", "operation": "Update", "apiVersion": f.get("apiVersion"),
+                                  "time": "2026-11-06T00:00:00Z", "fieldsType": "FieldsV1",
+                                  "fieldsV1": {"f:metadata": {"f:ownerReferences": {".": {}}}, "f:spec": {}}}]})
+    f["metadata"] = _ordered(md, "metadata")
+    if kind == "StatefulSet":
+        sp = f["spec"]
+        sp.update({"serviceName": "", "podManagementPolicy": "OrderedReady",
+                   "updateStrategy": {"type": "RollingUpdate", "rollingUpdate": {"partition": 0}},
+                   "revisionHistoryLimit": 10,
+                   "persistentVolumeClaimRetentionPolicy": {"whenDeleted": "Retain", "whenScaled": "Retain"}})
+        t = sp["template"]
+        t["metadata"] = _ordered(dict(t.get("metadata") or {}, creationTimestamp=None), "metadata")
+        ps = t["spec"]
+        ps.update({"restartPolicy": "Always", "terminationGracePeriodSeconds": 30, "dnsPolicy": "ClusterFirst",
+                   "schedulerName": "default-scheduler"})
+        ps.setdefault("securityContext", {})
+        if ps.get("serviceAccountName"):
+            ps["serviceAccount"] = ps["serviceAccountName"]
+        for c in ps.get("containers") or []:
+            c.setdefault("resources", {})
+            c.update({"terminationMessagePath": "/dev/termination-log", "terminationMessagePolicy": "File",
+                      "imagePullPolicy": "Always" if str(c.get("image", "")).endswith(":latest") or ":" not in str(c.get("image", "")) else "IfNotPresent"})
+            for p in c.get("ports") or []:
+                if isinstance(p, dict):
+                    p.setdefault("protocol", "TCP")
+        ps["containers"] = [_ordered(c, "container") for c in ps.get("containers") or []]
+        for v in ps.get("volumes") or []:
+            if isinstance(v.get("secret"), dict):
+                v["secret"].setdefault("defaultMode", 420)
+        t["spec"] = _ordered(ps, "podspec")
+        f["spec"] = _ordered(sp, "sts.spec")
+        f["status"] = {"observedGeneration": 1, "replicas": 1, "readyReplicas": 1, "currentReplicas": 1,
+                       "updatedReplicas": 1, "currentRevision": "%s-5d8c9f7b6" % md.get("name", ""),
+                       "updateRevision": "%s-5d8c9f7b6" % md.get("name", ""), "collisionCount": 0, "availableReplicas": 1}
+    elif kind == "Service":
+        sp = f["spec"]
+        ip = "10.%d.%d.%d" % ((i >> 16) & 255, (i >> 8) & 255, i & 255)
+        sp.update({"clusterIP": ip, "clusterIPs": [ip], "sessionAffinity": "None", "ipFamilies": ["IPv4"],
+                   "ipFamilyPolicy": "SingleStack", "internalTrafficPolicy": "Cluster"})
+        f["spec"] = _ordered(sp, "svc.spec")
+        f["status"] = {"loadBalancer": {}}
+    else:  # a custom resource: stored as it was sent, Go maps print their keys sorted
+        def srt(x):
+            if isinstance(x, dict):
+                return {k: srt(x[k]) for k in sorted(x)}
+            if isinstance(x, list):
+                return [srt(v) for v in x]
+            return x
+        if "spec" in f:
+            f["spec"] = srt(f["spec"])
+    return _ordered(f, "")
+
+
 def _stamp(t):
     import datetime
     return datetime.datetime.fromtimestamp(t, datetime.timezone.utc).strftime("%Y-%m-%dT%H:%M:%SZ")

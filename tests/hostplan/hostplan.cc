@@ -7,6 +7,7 @@
 #include <string.h>
 
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/nbrm.h"
@@ -19,6 +20,7 @@
 #include "../../kubeflow-rm_b200/csrc/nbrm_mutate.cuh"
 #include "../../kubeflow-rm_b200/csrc/nbrm_pd.cuh"
 #include "../../kubeflow-rm_b200/csrc/nbrm_profile.cuh"
+#include "../../kubeflow-rm_b200/csrc/nbrm_patch.cuh"
 #include "../../kubeflow-rm_b200/csrc/nbrm_pool.h"
 
 using namespace nbrm;
@@ -39,9 +41,9 @@ uint32_t g_tape_cap = 65000;  // entries per document; hostplan_set_tape_cap shr
 #endif
 
 template <class G>
-int run_host(const char* const data[3], const uint64_t* const off[3], uint64_t n, const nbrm_env* env,
+int run_host(Out& g_out, const char* const data[3], const uint64_t* const off[3], uint64_t n, const nbrm_env* env,
              uint32_t flags, const void* extra, uint64_t now, uint32_t arg0, uint32_t arg1,
-             uint32_t shared_n) {
+             uint32_t shared_n, uint64_t first = 0) {
   std::string pool;
   EnvLits L;
   build_pool_host(env, pool, L);
@@ -91,7 +93,7 @@ int run_host(const char* const data[3], const uint64_t* const off[3], uint64_t n
     c.aux.used = 0;
     c.env = &L;
     c.flags = flags;
-    c.index = (uint32_t)i;
+    c.index = (uint32_t)(first + i);
     c.extra = extra;
     c.now = now;
     c.arg0 = arg0;
@@ -173,6 +175,113 @@ HP_API void hostplan_view_object(const char* p, uint32_t n, uint32_t* out) {
   }
 }
 
+// The full reconcile pass of kubeflow-rm_b200/reconcile.py (webhook -> ODH objects -> ODH
+// write decision -> status -> notebook-controller objects -> create-or-update decision) on
+// the CPU, one shard of Notebooks per thread: the native CPU baseline bench.py reports beside
+// the Python oracle.  Inputs are packed documents: n requests, 3n found objects, n
+// StatefulSets, n Pods, 7n found ODH objects, 16n seed bytes.  Returns the bytes of every
+// result (mutated Notebooks, ODH write set, statuses, write set) in out_bytes[4], and the
+// number of tuples any stage rejected.
+namespace {
+struct Packed {
+  std::string data;
+  std::vector<uint64_t> off;
+};
+void take(Packed& p, const Out& o) {
+  p.data = o.data;
+  p.off = o.off;
+}
+struct PassShard {
+  uint64_t bytes[4] = {0, 0, 0, 0};
+  uint64_t rejected = 0;
+};
+void pass_shard(const char* const d[5], const uint64_t* const o[5], const unsigned char* seeds, uint64_t lo,
+                uint64_t hi, const nbrm_env* env, uint64_t now, uint32_t nbc_flags, uint32_t odh_flags,
+                PassShard* res) {
+  const uint64_t n = hi - lo;
+  if (!n) return;
+  Out out;
+  // rebase a slice [a, b) of packed documents to offsets that start at 0
+  auto slice = [](const char* data, const uint64_t* off, uint64_t a, uint64_t b, Packed& p) {
+    p.data.assign(data + off[a], off[b] - off[a]);
+    p.off.resize(b - a + 1);
+    for (uint64_t k = a; k <= b; ++k) p.off[k - a] = off[k] - off[a];
+  };
+  Packed req, found, sts, pod, ofound, nbs, odh, desired;
+  slice(d[0], o[0], lo, hi, req);
+  slice(d[1], o[1], 3 * lo, 3 * hi, found);
+  slice(d[2], o[2], lo, hi, sts);
+  slice(d[3], o[3], lo, hi, pod);
+  slice(d[4], o[4], 7 * lo, 7 * hi, ofound);
+  auto count = [&](const Out& x) {
+    for (uint32_t v : x.status) res->rejected += v != 0;
+  };
+  {  // NotebookWebhook.Handle (CREATE)
+    const char* dd[3] = {req.data.data(), nullptr, nullptr};
+    const uint64_t* oo[3] = {req.off.data(), nullptr, nullptr};
+    run_host<GenMutate>(out, dd, oo, n, env, 1u, nullptr, 0, 0, 0, 0);
+    count(out);
+    res->bytes[0] += out.data.size();
+    take(nbs, out);
+  }
+  {  // ODH desired objects, then what the ODH reconcilers write
+    const char* dd[3] = {nbs.data.data(), nullptr, nullptr};
+    const uint64_t* oo[3] = {nbs.off.data(), nullptr, nullptr};
+    run_host<GenOdh>(out, dd, oo, n, env, odh_flags, seeds, 0, 0, 0, 0);  // seeds already point at this shard
+    count(out);
+    take(odh, out);
+    const char* d2[3] = {odh.data.data(), ofound.data.data(), nullptr};
+    const uint64_t* o2[3] = {odh.off.data(), ofound.off.data(), nullptr};
+    run_host<GenOdhDecide>(out, d2, o2, 7 * n, env, 0, nullptr, 0, 0, 0, 0);
+    count(out);
+    res->bytes[1] += out.data.size();
+  }
+  {  // createNotebookStatus
+    const char* dd[3] = {nbs.data.data(), sts.data.data(), pod.data.data()};
+    const uint64_t* oo[3] = {nbs.off.data(), sts.off.data(), pod.off.data()};
+    run_host<GenStatus>(out, dd, oo, n, env, 0, nullptr, now, 0, 0, 0);
+    count(out);
+    res->bytes[2] += out.data.size();
+  }
+  {  // generateStatefulSet / Service / VirtualService, then Copy*Fields against the found objects
+    const char* dd[3] = {nbs.data.data(), nullptr, nullptr};
+    const uint64_t* oo[3] = {nbs.off.data(), nullptr, nullptr};
+    run_host<GenNbc>(out, dd, oo, n, env, nbc_flags, nullptr, 0, 0, 0, 0);
+    count(out);
+    take(desired, out);
+    const char* d2[3] = {desired.data.data(), found.data.data(), nullptr};
+    const uint64_t* o2[3] = {desired.off.data(), found.off.data(), nullptr};
+    run_host<GenCopyFields>(out, d2, o2, 3 * n, env, 0, nullptr, 0, 0, 0, 0);
+    count(out);
+    res->bytes[3] += out.data.size();
+  }
+}
+}  // namespace
+
+HP_API int hostplan_full_pass(const char* req, const uint64_t* req_off, const char* found, const uint64_t* found_off,
+                              const char* sts, const uint64_t* sts_off, const char* pod, const uint64_t* pod_off,
+                              const char* ofound, const uint64_t* ofound_off, const unsigned char* seeds,
+                              uint64_t n, const nbrm_env* env, uint64_t now, uint32_t nbc_flags,
+                              uint32_t odh_flags, uint32_t threads, uint64_t* out_bytes, uint64_t* rejected) {
+  if (threads < 1) threads = 1;
+  const char* d[5] = {req, found, sts, pod, ofound};
+  const uint64_t* o[5] = {req_off, found_off, sts_off, pod_off, ofound_off};
+  std::vector<PassShard> res(threads);
+  std::vector<std::thread> pool;
+  for (uint32_t t = 0; t < threads; ++t) {
+    const uint64_t lo = n * t / threads, hi = n * (t + 1) / threads;
+    pool.emplace_back(pass_shard, d, o, seeds + 16 * lo, lo, hi, env, now, nbc_flags, odh_flags, &res[t]);
+  }
+  for (auto& th : pool) th.join();
+  for (int k = 0; k < 4; ++k) out_bytes[k] = 0;
+  *rejected = 0;
+  for (auto& r : res) {
+    for (int k = 0; k < 4; ++k) out_bytes[k] += r.bytes[k];
+    *rejected += r.rejected;
+  }
+  return 0;
+}
+
 // The scalar index builder on one document (tape build only); returns the entry count.
 HP_API uint32_t hostplan_build_tape(const char* p, uint32_t n, uint64_t* out, uint32_t cap, uint32_t* flags) {
 #ifdef NBRM_TAPE
@@ -195,16 +304,19 @@ HP_API int hostplan_run(int gen, const char* d0, const uint64_t* o0, const char*
   const uint64_t* off[3] = {o0, o1, o2};
   int rc = -9;
   switch (gen) {
-    case 0: rc = run_host<GenNbc>(data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenNbc::NOBJ; break;
-    case 1: rc = run_host<GenOdh>(data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenOdh::NOBJ; break;
-    case 2: rc = run_host<GenCopyFields>(data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenCopyFields::NOBJ; break;
-    case 3: rc = run_host<GenStatus>(data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenStatus::NOBJ; break;
-    case 4: rc = run_host<GenCull>(data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenCull::NOBJ; break;
-    case 5: rc = run_host<GenMutate>(data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenMutate::NOBJ; break;
-    case 6: rc = run_host<GenRestartGuard>(data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenRestartGuard::NOBJ; break;
-    case 7: rc = run_host<GenPodDefault>(data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenPodDefault::NOBJ; break;
-    case 9: rc = run_host<GenOdhDecide>(data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenOdhDecide::NOBJ; break;
-    case 8: rc = run_host<GenProfile>(data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenProfile::NOBJ; break;
+    case 0: rc = run_host<GenNbc>(g_out, data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenNbc::NOBJ; break;
+    case 1: rc = run_host<GenOdh>(g_out, data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenOdh::NOBJ; break;
+    case 2: rc = run_host<GenCopyFields>(g_out, data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenCopyFields::NOBJ; break;
+    case 3: rc = run_host<GenStatus>(g_out, data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenStatus::NOBJ; break;
+    case 4: rc = run_host<GenCull>(g_out, data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenCull::NOBJ; break;
+    case 5: rc = run_host<GenMutate>(g_out, data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenMutate::NOBJ; break;
+    case 6: rc = run_host<GenRestartGuard>(g_out, data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenRestartGuard::NOBJ; break;
+    case 7: rc = run_host<GenPodDefault>(g_out, data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenPodDefault::NOBJ; break;
+    case 9: rc = run_host<GenOdhDecide>(g_out, data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenOdhDecide::NOBJ; break;
+    case 10: rc = run_host<GenJsonDiff>(g_out, data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenJsonDiff::NOBJ; break;
+    case 11: rc = run_host<GenReviewOpen>(g_out, data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenReviewOpen::NOBJ; break;
+    case 12: rc = run_host<GenReviewClose>(g_out, data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenReviewClose::NOBJ; break;
+    case 8: rc = run_host<GenProfile>(g_out, data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenProfile::NOBJ; break;
   }
   *out_data = g_out.data.data();
   *out_off = g_out.off.data();

@@ -6,6 +6,7 @@ import numpy as np
 
 GEN_NBC, GEN_ODH, GEN_COPY, GEN_STATUS, GEN_CULL, GEN_MUTATE, GEN_GUARD, GEN_PD, GEN_PROFILE = 0, 1, 2, 3, 4, 5, 6, 7, 8
 GEN_ODH_DECIDE = 9
+GEN_DIFF, GEN_REVIEW_OPEN, GEN_REVIEW_CLOSE = 10, 11, 12
 
 
 def _pack(docs_list):
@@ -103,3 +104,14 @@ class HostPlan:
 
     def profile(self, profiles, env=None):
         return self.run(GEN_PROFILE, [profiles], env)
+
+    def json_diff(self, originals, mutated):
+        return self.run(GEN_DIFF, [originals, mutated])
+
+    def review_open(self, reviews, flags=0):
+        return self.run(GEN_REVIEW_OPEN, [reviews], flags=flags, want_result=True)
+
+    def review_close(self, reviews, patches, statuses, flags=0):
+        import numpy as np
+        return self.run(GEN_REVIEW_CLOSE, [reviews, patches], flags=flags,
+                        extra=np.asarray(statuses, dtype=np.uint32).tobytes())

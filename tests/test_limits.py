@@ -36,6 +36,33 @@ def test_limits_cpu_build(hostplan, wl):
     assert [e["name"] for e in env] == ["E%d" % i for i in range(128)]
 
 
+def _deep_pair(depth):
+    """A VirtualService pair whose specs differ only below `depth` levels of nesting."""
+    def nest(leaf):
+        v = leaf
+        for _ in range(depth):
+            v = {"k": v}
+        return v
+    d = {"apiVersion": "networking.istio.io/v1alpha3", "kind": "VirtualService", "metadata": {"name": "a", "namespace": "n"},
+         "spec": {"deep": nest(1)}}
+    f = {"apiVersion": "networking.istio.io/v1alpha3", "kind": "VirtualService", "metadata": {"name": "a", "namespace": "n"},
+         "spec": {"deep": nest(2)}}
+    return d, f
+
+
+def test_compare_depth_limit_is_reported(hostplan, wl):
+    """DeepEqual follows 24 levels of nesting; beyond that the pair gets NBRM_E_LIMIT, not a
+    silent "differs" (which would be an Update on every reconcile)."""
+    d, f = _deep_pair(10)
+    outs, st = hostplan.copy_fields([wl.dumps(d)], [wl.dumps(f)])
+    assert list(st) == [0] and json.loads(outs[0])["spec"] == d["spec"]            # a real difference: update
+    d, f = _deep_pair(40)
+    outs, st = hostplan.copy_fields([wl.dumps(d)], [wl.dumps(f)])
+    assert list(st) == [8] and outs == [b""]
+    outs, st = hostplan.copy_fields([wl.dumps(d)], [wl.dumps(d)])                  # same text: equal at any depth
+    assert list(st) == [0] and outs == [b""]
+
+
 @pytest.mark.gpu
 def test_limits_gpu(ctx, pkg, wl):
     ctx.set_env({})
@@ -47,3 +74,6 @@ def test_limits_gpu(ctx, pkg, wl):
     pod, pds = _many_poddefaults(wl, 128)
     res = ctx.poddefault_mutate(pkg.Docs([pod]), pkg.Docs(pds))
     assert list(res.status) == [0] and int(res.result[0]) == 128
+    d, f = _deep_pair(40)
+    res = ctx.copy_fields(pkg.Docs([wl.dumps(d)]), pkg.Docs([wl.dumps(f)]))
+    assert list(res.status) == [8] and res.doc(0) == b""

@@ -48,6 +48,26 @@ def test_noalloc_scan_matches_generate_offsets_twice_in_a_row(ctx, pkg, wl):
         assert got.dtype == res.off.dtype and np.array_equal(got, res.off)
 
 
+def test_noalloc_scan_leaves_device_memory_alone(pkg):
+    """The claim in the name: the amount of free device memory is the same before and after a
+    call (the first call on a device may load the library's module, so one call is made first)."""
+    import torch
+    lens = np.arange(1, 300001, dtype=np.uint32)
+    d_lens = torch.from_numpy(lens.view(np.int32).copy()).cuda()
+    d_off = torch.zeros(len(lens) + 1, dtype=torch.int64, device="cuda")
+    stream = torch.cuda.current_stream().cuda_stream
+    rc, msg = pkg.scan_lengths_noalloc(d_lens.data_ptr(), len(lens), d_off.data_ptr(), stream)
+    assert rc == 0, msg
+    torch.cuda.synchronize()
+    free_before = torch.cuda.mem_get_info()[0]
+    for _ in range(3):
+        rc, msg = pkg.scan_lengths_noalloc(d_lens.data_ptr(), len(lens), d_off.data_ptr(), stream)
+        assert rc == 0, msg
+    torch.cuda.synchronize()
+    assert torch.cuda.mem_get_info()[0] == free_before
+    assert int(d_off[-1].item()) == int(lens.astype(np.uint64).sum())
+
+
 def test_noalloc_scan_edges_and_limit(pkg):
     import torch
     assert list(_offsets_via_noalloc(pkg, np.zeros(0, dtype=np.uint32))) == [0]
