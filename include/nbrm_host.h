@@ -31,6 +31,44 @@ void nbrm_store_counters(nbrm_store* s, uint64_t* counters, int reset);
 uint64_t nbrm_store_size(nbrm_store* s);
 void nbrm_store_free_string(char* p);
 
+/* r.Patch(ctx, obj, client.RawPatch(...)): json_patch == 0 applies an RFC 7386 merge patch
+ * (what RemoveReconciliationLock sends, odh-notebook-controller/controllers/
+ * notebook_controller.go:141-145), json_patch != 0 an RFC 6902 JSON patch (what the webhooks
+ * answer with).  0 ok, 1 NotFound, 4 the patch does not apply. */
+int nbrm_store_patch(nbrm_store* s, const char* kind, const char* ns, const char* name, const char* patch,
+                     uint64_t len, int json_patch);
+
+/* OpenshiftNotebookReconciler (odh-notebook-controller/controllers/notebook_controller.go:150-247):
+ * NetworkPolicies, Route or the OAuth objects, RoleBinding when rbac, Update conflicts retried
+ * as retry.RetryOnConflict does, then RemoveReconciliationLock (:118-146) as a merge patch.
+ * stats[9] = keys, reconciled, not_found, creates, updates, conflicts_retried, locks_removed,
+ * pull_secret_waits, errors.  *slept_seconds: what the wait for the ServiceAccount's pull
+ * secret would have slept (1 s + 5 s per locked Notebook whose secret never came); nothing
+ * actually sleeps.  Returns the number of keys that ended in an error. */
+typedef struct nbrm_odh_reconciler nbrm_odh_reconciler;
+nbrm_odh_reconciler* nbrm_odh_reconciler_new(nbrm_store* s, nbrm_ctx* ctx, int rbac);
+void nbrm_odh_reconciler_free(nbrm_odh_reconciler* r);
+int nbrm_odh_reconciler_reconcile(nbrm_odh_reconciler* r, const char* keys, uint64_t* stats, double* slept_seconds);
+
+/* The work queue between watch events and the reconcilers (controller-runtime's workqueue
+ * semantics; kubeflow-rm_b200/host/workqueue.h): a key waits at most once, is never handed
+ * out while it is being reconciled, comes back after `seconds` (ctrl.Result{RequeueAfter},
+ * notebook-controller/controllers/culling_controller.go:143,168) or after the per-key
+ * back-off 5 ms * 2^failures capped at 1000 s.  Times are the caller's clock in seconds.
+ * nbrm_workqueue_take: up to max ready keys as "ns/name\n" lines (release with
+ * nbrm_store_free_string); every key taken must be given back with nbrm_workqueue_done. */
+typedef struct nbrm_workqueue nbrm_workqueue;
+nbrm_workqueue* nbrm_workqueue_new(void);
+void nbrm_workqueue_free(nbrm_workqueue* q);
+void nbrm_workqueue_add(nbrm_workqueue* q, const char* ns, const char* name);
+void nbrm_workqueue_add_after(nbrm_workqueue* q, const char* ns, const char* name, double now, double seconds);
+double nbrm_workqueue_add_rate_limited(nbrm_workqueue* q, const char* ns, const char* name, double now);
+void nbrm_workqueue_forget(nbrm_workqueue* q, const char* ns, const char* name);
+void nbrm_workqueue_done(nbrm_workqueue* q, const char* ns, const char* name);
+uint64_t nbrm_workqueue_len(nbrm_workqueue* q);
+double nbrm_workqueue_next_ready(nbrm_workqueue* q);
+uint64_t nbrm_workqueue_take(nbrm_workqueue* q, uint64_t max, double now, char** out);
+
 /* NotebookReconciler.  keys = "namespace/name" entries separated by '\n'.
  * stats[11] = keys, reconciled, not_found, terminating, creates, updates,
  * status_updates, status_unchanged, pod_restarts, errors, events_reissued.  Returns 0, or the

@@ -73,17 +73,20 @@ struct Planner {
   }
   NB_HD void put(uint32_t src, uint32_t off, uint32_t len) {
     if (!len) return;
-    while (len > SEG_LEN_MASK) {  // a span of 256 MiB or more goes out as several segments
-      put(src, off, SEG_LEN_MASK);
-      off += SEG_LEN_MASK;
-      len -= SEG_LEN_MASK;
-    }
     total += len;
     if (cur_len && cur_src == src && cur_off + cur_len == off && cur_len + len <= SEG_LEN_MASK) {
       cur_len += len;
       return;
     }
     flush();
+    while (len > SEG_LEN_MASK) {  // a span of 256 MiB or more goes out as several segments
+      cur_src = src;
+      cur_off = off;
+      cur_len = SEG_LEN_MASK;
+      flush();
+      off += SEG_LEN_MASK;
+      len -= SEG_LEN_MASK;
+    }
     cur_src = src;
     cur_off = off;
     cur_len = len;

@@ -38,6 +38,28 @@ def load_host_library():
     lib.nbrm_reconciler_new.restype = C.c_void_p
     lib.nbrm_reconciler_free.argtypes = [C.c_void_p]
     lib.nbrm_reconciler_reconcile.argtypes = [C.c_void_p, C.c_char_p, C.c_uint64, C.POINTER(C.c_uint64)]
+    lib.nbrm_store_patch.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_uint64, C.c_int]
+    lib.nbrm_odh_reconciler_new.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
+    lib.nbrm_odh_reconciler_new.restype = C.c_void_p
+    lib.nbrm_odh_reconciler_free.argtypes = [C.c_void_p]
+    lib.nbrm_odh_reconciler_free.restype = None
+    lib.nbrm_odh_reconciler_reconcile.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.c_uint64), C.POINTER(C.c_double)]
+    lib.nbrm_workqueue_new.restype = C.c_void_p
+    for fn in ("free", "add", "forget", "done"):
+        getattr(lib, "nbrm_workqueue_" + fn).restype = None
+    lib.nbrm_workqueue_free.argtypes = [C.c_void_p]
+    lib.nbrm_workqueue_add.argtypes = lib.nbrm_workqueue_forget.argtypes = lib.nbrm_workqueue_done.argtypes = \
+        [C.c_void_p, C.c_char_p, C.c_char_p]
+    lib.nbrm_workqueue_add_after.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_double, C.c_double]
+    lib.nbrm_workqueue_add_after.restype = None
+    lib.nbrm_workqueue_add_rate_limited.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_double]
+    lib.nbrm_workqueue_add_rate_limited.restype = C.c_double
+    lib.nbrm_workqueue_len.argtypes = [C.c_void_p]
+    lib.nbrm_workqueue_len.restype = C.c_uint64
+    lib.nbrm_workqueue_next_ready.argtypes = [C.c_void_p]
+    lib.nbrm_workqueue_next_ready.restype = C.c_double
+    lib.nbrm_workqueue_take.argtypes = [C.c_void_p, C.c_uint64, C.c_double, C.POINTER(C.c_void_p)]
+    lib.nbrm_workqueue_take.restype = C.c_uint64
     _lib = lib
     return lib
 
@@ -65,6 +87,11 @@ class Store:
         b = C.string_at(out.value, n.value)
         self.lib.nbrm_store_free_string(out)
         return b
+
+    def patch(self, kind, ns, name, patch_bytes, json_patch=False):
+        """RFC 7386 merge patch (default) or RFC 6902 JSON patch on a stored object."""
+        return self.lib.nbrm_store_patch(self.h, kind.encode(), ns.encode(), name.encode(), patch_bytes,
+                                         len(patch_bytes), 1 if json_patch else 0)
 
     def counters(self, reset=False):
         c = (C.c_uint64 * 6)()
@@ -103,4 +130,73 @@ class NotebookReconciler:
     def close(self):
         if self.h:
             self.lib.nbrm_reconciler_free(self.h)
+            self.h = None
+
+
+ODH_STAT_NAMES = ("keys", "reconciled", "not_found", "creates", "updates", "conflicts_retried", "locks_removed",
+                  "pull_secret_waits", "errors")
+
+
+class OpenshiftNotebookReconciler:
+    """OpenshiftNotebookReconciler (odh-notebook-controller/controllers/notebook_controller.go:150-247)."""
+
+    def __init__(self, store, ctx, rbac=False):
+        self.lib = load_host_library()
+        self.store, self.ctx = store, ctx
+        self.h = self.lib.nbrm_odh_reconciler_new(store.h, ctx.h, 1 if rbac else 0)
+
+    def reconcile(self, keys):
+        """keys: iterable of (namespace, name).  Returns (n_errors, stats dict, simulated seconds slept)."""
+        text = "\n".join("%s/%s" % k for k in keys).encode()
+        st = (C.c_uint64 * 9)()
+        slept = C.c_double()
+        rc = self.lib.nbrm_odh_reconciler_reconcile(self.h, text, st, C.byref(slept))
+        return rc, dict(zip(ODH_STAT_NAMES, list(st))), slept.value
+
+    def close(self):
+        if self.h:
+            self.lib.nbrm_odh_reconciler_free(self.h)
+            self.h = None
+
+
+class WorkQueue:
+    """controller-runtime's workqueue semantics (kubeflow-rm_b200/host/workqueue.h)."""
+
+    def __init__(self):
+        self.lib = load_host_library()
+        self.h = self.lib.nbrm_workqueue_new()
+
+    def add(self, ns, name):
+        self.lib.nbrm_workqueue_add(self.h, ns.encode(), name.encode())
+
+    def add_after(self, ns, name, now, seconds):
+        self.lib.nbrm_workqueue_add_after(self.h, ns.encode(), name.encode(), now, seconds)
+
+    def add_rate_limited(self, ns, name, now):
+        return self.lib.nbrm_workqueue_add_rate_limited(self.h, ns.encode(), name.encode(), now)
+
+    def forget(self, ns, name):
+        self.lib.nbrm_workqueue_forget(self.h, ns.encode(), name.encode())
+
+    def done(self, ns, name):
+        self.lib.nbrm_workqueue_done(self.h, ns.encode(), name.encode())
+
+    def take(self, max_keys, now):
+        out = C.c_void_p()
+        n = self.lib.nbrm_workqueue_take(self.h, max_keys, now, C.byref(out))
+        text = C.string_at(out.value).decode()
+        self.lib.nbrm_store_free_string(out)
+        keys = [tuple(line.split("/", 1)) for line in text.splitlines() if line]
+        assert len(keys) == n
+        return keys
+
+    def __len__(self):
+        return int(self.lib.nbrm_workqueue_len(self.h))
+
+    def next_ready(self):
+        return self.lib.nbrm_workqueue_next_ready(self.h)
+
+    def close(self):
+        if self.h:
+            self.lib.nbrm_workqueue_free(self.h)
             self.h = None

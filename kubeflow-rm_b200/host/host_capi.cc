@@ -4,6 +4,8 @@
 
 #include "../../include/nbrm_host.h"
 #include "notebook_reconciler.h"
+#include "odh_reconciler.h"
+#include "workqueue.h"
 
 using namespace nbrm_host;
 
@@ -13,6 +15,29 @@ struct nbrm_store {
 struct nbrm_reconciler {
   NotebookReconciler r;
 };
+struct nbrm_odh_reconciler {
+  double slept = 0;  // seconds the lock wait asked for (simulated: nothing sleeps)
+  OpenshiftNotebookReconciler r;
+  nbrm_odh_reconciler(Store* s, nbrm_ctx* c, bool rbac)
+      : r(s, c, rbac, [this](double sec) { slept += sec; }) {}
+};
+struct nbrm_workqueue {
+  WorkQueue q;
+};
+
+static std::vector<Request> parse_keys(const char* keys) {
+  std::vector<Request> reqs;
+  const char* p = keys;
+  while (p && *p) {
+    const char* e = strchr(p, '\n');
+    std::string line = e ? std::string(p, e - p) : std::string(p);
+    size_t slash = line.find('/');
+    if (slash != std::string::npos) reqs.push_back(Request{line.substr(0, slash), line.substr(slash + 1)});
+    if (!e) break;
+    p = e + 1;
+  }
+  return reqs;
+}
 
 extern "C" {
 
@@ -45,6 +70,54 @@ void nbrm_store_counters(nbrm_store* s, uint64_t* c, int reset) {
 }
 uint64_t nbrm_store_size(nbrm_store* s) { return s->s.size(); }
 void nbrm_store_free_string(char* p) { free(p); }
+
+int nbrm_store_patch(nbrm_store* s, const char* kind, const char* ns, const char* name, const char* patch,
+                     uint64_t len, int json_patch) {
+  const Key k{kind, ns, name};
+  return (int)(json_patch ? s->s.PatchJson(k, std::string(patch, len)) : s->s.Patch(k, std::string(patch, len)));
+}
+
+nbrm_odh_reconciler* nbrm_odh_reconciler_new(nbrm_store* s, nbrm_ctx* ctx, int rbac) {
+  return new nbrm_odh_reconciler(&s->s, ctx, rbac != 0);
+}
+void nbrm_odh_reconciler_free(nbrm_odh_reconciler* r) { delete r; }
+int nbrm_odh_reconciler_reconcile(nbrm_odh_reconciler* r, const char* keys, uint64_t* stats, double* slept_seconds) {
+  OdhStats st;
+  std::vector<std::string> errs;
+  r->slept = 0;
+  r->r.ReconcileBatch(parse_keys(keys), &st, &errs);
+  if (stats) {
+    stats[0] = st.keys; stats[1] = st.reconciled; stats[2] = st.not_found; stats[3] = st.creates;
+    stats[4] = st.updates; stats[5] = st.conflicts_retried; stats[6] = st.locks_removed;
+    stats[7] = st.pull_secret_waits; stats[8] = st.errors;
+  }
+  if (slept_seconds) *slept_seconds = r->slept;
+  return (int)st.errors;
+}
+
+nbrm_workqueue* nbrm_workqueue_new(void) { return new nbrm_workqueue(); }
+void nbrm_workqueue_free(nbrm_workqueue* q) { delete q; }
+void nbrm_workqueue_add(nbrm_workqueue* q, const char* ns, const char* name) { q->q.Add(Request{ns, name}); }
+void nbrm_workqueue_add_after(nbrm_workqueue* q, const char* ns, const char* name, double now, double seconds) {
+  q->q.AddAfter(Request{ns, name}, now, seconds);
+}
+double nbrm_workqueue_add_rate_limited(nbrm_workqueue* q, const char* ns, const char* name, double now) {
+  return q->q.AddRateLimited(Request{ns, name}, now);
+}
+void nbrm_workqueue_forget(nbrm_workqueue* q, const char* ns, const char* name) { q->q.Forget(Request{ns, name}); }
+void nbrm_workqueue_done(nbrm_workqueue* q, const char* ns, const char* name) { q->q.Done(Request{ns, name}); }
+uint64_t nbrm_workqueue_len(nbrm_workqueue* q) { return q->q.Len(); }
+double nbrm_workqueue_next_ready(nbrm_workqueue* q) { return q->q.NextReady(); }
+// keys out as "ns/name\n..." in a malloc'ed string (nbrm_store_free_string); returns the count
+uint64_t nbrm_workqueue_take(nbrm_workqueue* q, uint64_t max, double now, char** out) {
+  std::vector<Request> reqs;
+  q->q.Take(max, now, &reqs);
+  std::string text;
+  for (auto& r : reqs) text += r.ns + "/" + r.name + "\n";
+  *out = (char*)malloc(text.size() + 1);
+  memcpy(*out, text.c_str(), text.size() + 1);
+  return reqs.size();
+}
 
 nbrm_reconciler* nbrm_reconciler_new(nbrm_store* s, nbrm_ctx* ctx, int use_istio, int wic) {
   return new nbrm_reconciler{NotebookReconciler(&s->s, ctx, use_istio != 0, wic != 0)};

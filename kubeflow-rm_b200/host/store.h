@@ -31,7 +31,7 @@ struct Key {
 };
 
 struct Counters {
-  uint64_t gets = 0, creates = 0, updates = 0, status_updates = 0, deletes = 0, conflicts = 0;
+  uint64_t gets = 0, creates = 0, updates = 0, status_updates = 0, deletes = 0, conflicts = 0, patches = 0;
 };
 
 // Fields of an object's JSON text the store and the reconciler need.
@@ -52,12 +52,23 @@ std::string with_status(const std::string& json, const std::string& raw);
 // The same object without metadata.annotations[key].
 std::string without_annotation(const std::string& json, const std::string& key);
 
+// RFC 7386: `target` with the JSON merge patch applied (null deletes a member, objects merge
+// member by member, anything else replaces).  What client.RawPatch(types.MergePatchType, ...)
+// makes the API server do (odh-notebook-controller/controllers/notebook_controller.go:141-145).
+std::string apply_merge_patch(const std::string& target, const std::string& patch);
+// RFC 6902: `target` with the operations of `patch` applied in order (add / remove / replace;
+// paths are JSON pointers, "-" appends to an array).  ok is false when a path does not resolve.
+std::string apply_json_patch(const std::string& target, const std::string& patch, bool* ok);
+
 class Store {
  public:
   Err Get(const Key& k, std::string* out);
   Err Create(const std::string& json, std::string* stored = nullptr);
   Err Update(const std::string& json, std::string* stored = nullptr);
   Err UpdateStatus(const Key& k, const std::string& status_json);
+  // r.Patch(ctx, obj, client.RawPatch(types.MergePatchType, patch)) / (types.JSONPatchType, patch)
+  Err Patch(const Key& k, const std::string& merge_patch_json);
+  Err PatchJson(const Key& k, const std::string& json_patch);
   Err Delete(const Key& k);
   size_t size() const;
   Counters counters() const;
