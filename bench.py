@@ -418,6 +418,82 @@ def traffic_from_profiles(kernel, batch):
     return None, None
 
 
+def other_configs(pkg, wl, ctx):
+    """BASELINE.json configs[0], [2], [3], [4] through the same C ABI, host buffers in and out
+    (wall clock around the call: what a caller sees).  Small fixed sizes as BASELINE states them,
+    plus one large batch each for the throughput the path sustains."""
+    import importlib
+    import json as js
+    import random
+    import __graft_entry__ as graft
+    from oracle import wire
+    host = importlib.import_module(graft.PKG_NAME + ".host")
+
+    def timed(fn, reps, warm=3):
+        for _ in range(warm):
+            fn()
+        lat = []
+        for _ in range(reps):
+            t0 = time.perf_counter()
+            fn()
+            lat.append(1e3 * (time.perf_counter() - t0))
+        lat.sort()
+        return {"p50_ms": lat[len(lat) // 2], "p99_ms": lat[min(len(lat) - 1, int(len(lat) * 0.99))]}
+
+    out = {}
+    # configs[2]: 1k pod admission requests, P PodDefaults per namespace, AdmissionReview in and out
+    c3 = {}
+    for P in (1, 10, 100):
+        pods, pds, ranges = wl.admission_workload(1000, P)
+        reviews = pkg.Docs([wl.dumps(wire.review_request(p, "u%d" % i, namespace=p["metadata"]["namespace"]))
+                            for i, p in enumerate(pods)], pinned=True)
+        pdd = pkg.Docs([wl.dumps(x) for x in pds])
+        r = timed(lambda: ctx.poddefault_review(reviews, pdd, ranges, copy=False), 40)
+        r["requests_per_s"] = 1000 / (r["p50_ms"] / 1e3)
+        c3["P=%d" % P] = r
+    pods, pds, ranges = wl.admission_workload(65536, 10)
+    reviews = pkg.Docs([wl.dumps(wire.review_request(p, "u%d" % i, namespace=p["metadata"]["namespace"]))
+                        for i, p in enumerate(pods)], pinned=True)
+    pdd = pkg.Docs([wl.dumps(x) for x in pds])
+    r = timed(lambda: ctx.poddefault_review(reviews, pdd, ranges, copy=False), 5, warm=2)
+    c3["batch_65536_P=10"] = {"ms": r["p50_ms"], "requests_per_s": 65536 / (r["p50_ms"] / 1e3)}
+    out["configs[2] admission-webhook: 1k AdmissionReviews per call (p50/p99 of the call)"] = c3
+    # configs[3]: 500 Profiles -> 8 objects each
+    rng = random.Random(wl.SEED)
+    profs = pkg.Docs([wl.dumps(wl.profile_cr(rng, i)) for i in range(500)], pinned=True)
+    r = timed(lambda: ctx.profile_generate(profs, copy=False), 40)
+    r["profiles_per_s"] = 500 / (r["p50_ms"] / 1e3)
+    out["configs[3] profile-controller: 500 Profiles per call"] = r
+    # configs[4] (restated, SURVEY 8d): one culling pass over 100 000 Notebooks with their Jupyter answers
+    rng = random.Random(19)
+    cases = [wl.culling_case(rng, i, NOW) for i in range(20000)]
+    nbs = [wl.dumps(c[0]) for c in cases] * 5
+    ks = [b"" if c[2] is None else js.dumps(c[2]).encode() for c in cases] * 5
+    ts = [b"" if c[3] is None else js.dumps(c[3]).encode() for c in cases] * 5
+    pe = bytes(1 if c[1] else 0 for c in cases) * 5
+    d = [pkg.Docs(x, pinned=True) for x in (nbs, ks, ts)]
+    r = timed(lambda: ctx.culling_pass(d[0], d[1], d[2], pe, NOW, 5, 1, copy=False), 5, warm=2)
+    out["configs[4] culling pass over 100 000 Notebooks (CULL_IDLE_TIME 5, IDLENESS_CHECK_PERIOD 1)"] = {
+        "ms": r["p50_ms"], "notebooks_per_s": 100000 / (r["p50_ms"] / 1e3)}
+    # configs[0]: the envtest Notebook through the C++ reconciler over the in-memory store
+    store = host.Store()
+    rec = host.NotebookReconciler(store, ctx, use_istio=True)
+    nb = wl.notebook_c1(0)
+    store.create(wl.dumps(nb))
+    key = [(nb["metadata"]["namespace"], nb["metadata"]["name"])]
+
+    def cold():
+        for kind, name in (("StatefulSet", "test-notebook"), ("Service", "test-notebook"),
+                           ("VirtualService", "notebook-default-test-notebook")):
+            store.delete(kind, "default", name)
+        rec.reconcile(key, NOW)
+    c1 = {"cold_create": timed(cold, 200), "steady_no_op": timed(lambda: rec.reconcile(key, NOW), 200)}
+    out["configs[0] notebook-controller: reconcile 1 Notebook (C++ reconciler, in-memory store)"] = c1
+    rec.close()
+    store.close()
+    return out
+
+
 def main():
     args = parse_args()
     if args.impl == "reference":
@@ -608,6 +684,11 @@ def main():
     nat = native_cpu_baseline(pkg, head["w"], nat_n, cores)
     nat1 = native_cpu_baseline(pkg, head["w"], min(4096, n_mine), 1)
 
+    try:
+        others = other_configs(pkg, wl, ctx)
+    except Exception as e:          # the headline must not die with a side measurement
+        others = {"error": repr(e)}
+
     print(json.dumps({
         "metric": METRIC, "value": results[variants[0]]["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": head["ms"] / args.steps, "higher_is_better": True,
@@ -617,7 +698,8 @@ def main():
                    "sharding": "key hash over %d ranks (shard.py), no data-path collective" % world,
                    "l2": head["l2"], "variants": results,
                    "literal_100": {"p50_ms": lat[len(lat) // 2], "p99_ms": lat[98], "max_ms": lat[-1],
-                                   "reconciles_per_s": 100 / (lat[len(lat) // 2] / 1e3)}},
+                                   "reconciles_per_s": 100 / (lat[len(lat) // 2] / 1e3)},
+                   "other_configs": others},
         "e2e": head["e2e"],
         "gpu_launches": head["launches"], "clocks": head["clocks"], "roofline": roofline,
         "cpu_baseline": {"value": cb, "unit": UNIT, "cores": 1, "kind": "port",

@@ -93,7 +93,7 @@ typedef struct nbrm_out {
 
 /* Accumulated device time per kernel class since nbrm_profile_enable(ctx, 1),
  * measured with CUDA events on the context's stream. */
-#define NBRM_GENERATORS 16 /* size of the per-generator arrays below; ids 0..12 are in use */
+#define NBRM_GENERATORS 16 /* size of the per-generator arrays below; ids 0..13 are in use */
 typedef struct nbrm_profile {
   double plan_ms, scan_ms, emit_ms;
   uint64_t plan_launches, scan_launches, emit_launches;
@@ -365,6 +365,19 @@ int nbrm_upload_async(nbrm_ctx* ctx, int slot, const nbrm_docs* docs);
 int nbrm_download_begin(nbrm_ctx* ctx, int lane);
 int nbrm_download_slot_begin(nbrm_ctx* ctx, int slot, int lane);
 int nbrm_download_wait(nbrm_ctx* ctx, int lane, nbrm_out* out);
+
+/* ---- Notebook version conversion ------------------------------------------------
+ * ConvertTo / ConvertFrom of the v1 and v1alpha1 spokes around the v1beta1 hub
+ * (notebook-controller/api/v1/notebook_conversion.go:25-69, api/v1alpha1 likewise).
+ * to_version: 0 kubeflow.org/v1beta1, 1 kubeflow.org/v1, 2 kubeflow.org/v1alpha1.
+ * As in the reference only spec.template.spec, status.readyReplicas,
+ * status.containerState and each condition's type / lastProbeTime / reason /
+ * message cross over: a condition's status comes out "" and its
+ * lastTransitionTime is dropped (:30-38, :56-64).  The reference's functions do
+ * not touch ObjectMeta; NBRM_CONVERT_KEEP_METADATA carries the source's through. */
+enum { NBRM_CONVERT_KEEP_METADATA = 1 };
+int nbrm_notebook_convert(nbrm_ctx* ctx, const nbrm_docs* notebooks, int to_version, uint32_t flags,
+                          nbrm_out* out);
 
 /* ---- wire formats of the two webhooks -----------------------------------------
  * nbrm_json_diff: the RFC 6902 patch that turns originals[i] into mutated[i]

@@ -69,6 +69,28 @@ uint64_t nbrm_workqueue_len(nbrm_workqueue* q);
 double nbrm_workqueue_next_ready(nbrm_workqueue* q);
 uint64_t nbrm_workqueue_take(nbrm_workqueue* q, uint64_t max, double now, char** out);
 
+/* The pure part of the trusted-CA bundle path (odh-notebook-controller/controllers/
+ * notebook_controller.go): CreateNotebookCertConfigMap :254-357 decides from the bytes of
+ * odh-trusted-ca-bundle (ca-bundle.crt, odh-ca-bundle.crt) and kube-root-ca.crt (ca.crt) what
+ * goes into workbench-trusted-ca-bundle["ca-bundle.crt"].  A file pointer NULL = the key is
+ * absent; *_configmap_found 0 = the Get returned NotFound.  x509_ok: NULL, or three verdicts
+ * of the caller's x509.ParseCertificate for the first block of each file in the order above
+ * (1 parses, 0 does not, -1 no verdict: the DER's outer structure is checked instead).
+ * Returns 1 with *out = the bundle (malloc'ed, nbrm_store_free_string), 0 when the reference
+ * writes no ConfigMap.  The reads and the Create / Update stay with the caller. */
+int nbrm_ca_bundle(const char* ca_bundle_crt, const char* odh_ca_bundle_crt, int odh_configmap_found,
+                   const char* ca_crt, int kube_configmap_found, const int8_t* x509_ok, char** out,
+                   uint64_t* len);
+/* CERTIFICATE blocks in a bundle, as the reference's checkCertConfigMap counts them
+ * (notebook_controller_test.go:1134-1159). */
+uint64_t nbrm_pem_count_certificates(const char* bundle, uint64_t len);
+/* UnsetNotebookCertConfig :390-455 on a Notebook's JSON: the five CA environment variables and
+ * the trusted-ca mount leave the notebook's own container, the workbench-trusted-ca-bundle
+ * volume leaves the pod.  1: *out is the Notebook to patch to; 0: nothing to change; -1: the
+ * reference panics (its delete-while-ranging loop :411-415 slices past the shortened list
+ * when a variable is listed twice and the second one is last); -2: not a Notebook object. */
+int nbrm_unset_notebook_cert_config(const char* notebook, uint64_t nlen, char** out, uint64_t* len);
+
 /* NotebookReconciler.  keys = "namespace/name" entries separated by '\n'.
  * stats[11] = keys, reconciled, not_found, terminating, creates, updates,
  * status_updates, status_unchanged, pod_restarts, errors, events_reissued.  Returns 0, or the

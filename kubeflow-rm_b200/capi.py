@@ -94,6 +94,7 @@ def load_library():
     lib.nbrm_launch_count.restype = C.c_uint64
     lib.nbrm_upload.argtypes = [C.c_void_p, C.c_int, C.POINTER(_Docs)]
     lib.nbrm_slot_index.argtypes = [C.c_void_p, C.c_int]
+    lib.nbrm_notebook_convert.argtypes = [C.c_void_p, C.POINTER(_Docs), C.c_int, C.c_uint32, C.POINTER(_Out)]
     lib.nbrm_json_diff.argtypes = [C.c_void_p, C.POINTER(_Docs), C.POINTER(_Docs), C.POINTER(_Out)]
     lib.nbrm_notebook_webhook_review.argtypes = [C.c_void_p, C.POINTER(_Docs), C.c_uint32, C.c_int, C.POINTER(_Out)]
     lib.nbrm_poddefault_review.argtypes = [C.c_void_p, C.POINTER(_Docs), C.POINTER(_Docs), C.c_void_p, C.POINTER(_Out)]
@@ -357,6 +358,12 @@ class Context:
             r = np.ascontiguousarray(np.asarray(ranges, dtype=np.uint32).reshape(-1))
         self._check(self.lib.nbrm_poddefault_mutate(self.h, C.byref(a), C.byref(b),
                                                     r.ctypes.data if r is not None else None, C.byref(o)))
+        return Result(o, copy)
+
+    def notebook_convert(self, notebooks, to_version, flags=0, copy=True):
+        """ConvertTo / ConvertFrom (0 v1beta1, 1 v1, 2 v1alpha1)."""
+        a, o = notebooks.c_struct(), _Out()
+        self._check(self.lib.nbrm_notebook_convert(self.h, C.byref(a), to_version, flags, C.byref(o)))
         return Result(o, copy)
 
     # --- wire formats: JSON patches and AdmissionReview responses

@@ -1,5 +1,7 @@
-// gen_mutate.cu — plan kernel of GenMutate, in a unit of its own (see nbrm_plan_kernel.cuh).
-#define NBRM_WIDE_SKIP 2  // container skip: 8-byte-word scanner inlined (nbrm_json.cuh; measured in profiles/README.md)
+// gen_mutate.cu — plan kernels of GenMutate, in a unit of its own (see nbrm_plan_kernel.cuh).
+#define NBRM_TAPE 1       // planners hop through the structural index of a document that has one (nbrm_tape.cuh)
+#define NBRM_WARP 1       // small batches: one tuple per warp (plan_kernel_warp)
+#define NBRM_WIDE_SKIP 2  // text walk: 8-byte-word container skip (nbrm_json.cuh; measured in profiles/README.md)
 #include "nbrm_mutate.cuh"
 #include "nbrm_plan_kernel.cuh"
 

@@ -1,5 +1,7 @@
-// gen_nbc.cu — plan kernel of GenNbc, in a unit of its own (see nbrm_plan_kernel.cuh).
-#define NBRM_WIDE_SKIP 1  // container skip: one out-of-line 8-byte-word scanner (nbrm_json.cuh; measured in profiles/README.md)
+// gen_nbc.cu — plan kernels of GenNbc, in a unit of its own (see nbrm_plan_kernel.cuh).
+#define NBRM_TAPE 1       // planners hop through the structural index of a document that has one (nbrm_tape.cuh)
+#define NBRM_WARP 1       // small batches: one tuple per warp (plan_kernel_warp)
+#define NBRM_WIDE_SKIP 1  // text walk: 8-byte-word container skip (nbrm_json.cuh; measured in profiles/README.md)
 #include "nbrm_nbc.cuh"
 #include "nbrm_plan_kernel.cuh"
 

@@ -558,6 +558,8 @@ int run_generator(nbrm_ctx* c, int gen, const int (&map)[3], uint32_t flags, con
     if (want > c->views_max) c->views_max = want + want / 4;
     CK(c->views.reserve_exact(c->views_max));
     po.views = c->views.as<ViewEnt>();
+    // planners store only the fields an object has; everything else reads as an empty span
+    CK(cudaMemsetAsync(c->views.p, 0, (size_t)n_out * VIEW_FIELDS * sizeof(ViewEnt), c->stream));
     c->res_views = true;
   }
   {
@@ -1038,6 +1040,14 @@ int nbrm_poddefault_review(nbrm_ctx* c, const nbrm_docs* reviews, const nbrm_doc
   if (int r = run_generator(c, GEN_ID_REVIEW_CLOSE, {S_REVIEWS, S_PATCH, -1}, 4u /* REVIEW_PODS_ONLY */, c->extra.p, 0))
     return r;
   c->extra_bytes = 0;
+  return nbrm_download(c, out);
+}
+
+int nbrm_notebook_convert(nbrm_ctx* c, const nbrm_docs* notebooks, int to_version, uint32_t flags, nbrm_out* out) {
+  if (!c || !out) return -2;
+  if (to_version < 0 || to_version > 2) return fail_msg(c, "nbrm_notebook_convert: to_version is 0 (v1beta1), 1 (v1) or 2 (v1alpha1)");
+  if (int r = nbrm_upload(c, 0, notebooks)) return r;
+  if (int r = run_generator(c, GEN_ID_CONVERT, {0, -1, -1}, flags, nullptr, 0, (uint32_t)to_version, 0)) return r;
   return nbrm_download(c, out);
 }
 

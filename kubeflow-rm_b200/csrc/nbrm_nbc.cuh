@@ -210,14 +210,12 @@ NB_HD void plan_nb_prefix_elem(Planner& P, const NbView& v) {
 
 // generateStatefulSet (+ SetControllerReference when asked).
 NB_HD void plan_statefulset(Planner& P, const Doc& d, const NbView& v, const EnvLits& env,
-                            uint32_t flags, ViewOut vw) {
+                            uint32_t flags, ViewOut& vw) {
   vw.clear();
   LIT(P, STS_HEAD);
   vw.set(VF_KIND, LIT_AFTER(STS_HEAD, "\"kind\":"), LIT_AFTER(STS_HEAD, "\"kind\":\"StatefulSet\""));
-  vw.begin(VF_META, LIT_AFTER(STS_HEAD, "\"metadata\":"));
   put_str(P, v.name);
   plan_meta_tail(P, v, flags);
-  vw.end(VF_META, P.total + 1);  // the '}' that opens the next fragment
   vw.begin(VF_SPEC, P.total + LIT_AFTER(STS_SPEC_REPLICAS, "\"spec\":"));
   LIT(P, STS_SPEC_REPLICAS);
   vw.set(VF_REPLICAS, P.total, P.total + 1);
@@ -337,14 +335,12 @@ NB_HD void plan_statefulset(Planner& P, const Doc& d, const NbView& v, const Env
 }
 
 // generateService.
-NB_HD void plan_service(Planner& P, const Doc& d, const NbView& v, uint32_t flags, ViewOut vw) {
+NB_HD void plan_service(Planner& P, const Doc& d, const NbView& v, uint32_t flags, ViewOut& vw) {
   vw.clear();
   LIT(P, SVC_HEAD);
   vw.set(VF_KIND, LIT_AFTER(SVC_HEAD, "\"kind\":"), LIT_AFTER(SVC_HEAD, "\"kind\":\"Service\""));
-  vw.begin(VF_META, LIT_AFTER(SVC_HEAD, "\"metadata\":"));
   put_str(P, v.name);
   plan_meta_tail(P, v, flags);
-  vw.end(VF_META, P.total + 1);
   vw.begin(VF_SPEC, P.total + LIT_AFTER(SVC_PORTS, "\"spec\":"));
   vw.begin(VF_PORTS, P.total + LIT_AFTER(SVC_PORTS, "\"ports\":"));
   LIT(P, SVC_PORTS);
@@ -547,17 +543,15 @@ NB_HD void plan_headers_set(Planner& P, const Doc& d, const NbView& v, Aux& aux)
 
 // generateVirtualService.
 NB_HD void plan_virtualservice(Planner& P, const Doc& d, const NbView& v, const EnvLits& env,
-                               uint32_t flags, Aux& aux, ViewOut vw) {
+                               uint32_t flags, Aux& aux, ViewOut& vw) {
   vw.clear();
   LIT(P, VS_HEAD);  // ... "name":"notebook-
   vw.set(VF_KIND, LIT_AFTER(VS_HEAD, "\"kind\":"), LIT_AFTER(VS_HEAD, "\"kind\":\"VirtualService\""));
-  vw.begin(VF_META, LIT_AFTER(VS_HEAD, "\"metadata\":"));
   P.in(inner(v.ns));
   LIT(P, DASH);
   P.in(inner(v.name));
   LIT(P, QUOTE);
   plan_meta_tail(P, v, flags);
-  vw.end(VF_META, P.total + 1);
   vw.begin(VF_SPEC, P.total + LIT_AFTER(VS_GATEWAYS, "\"spec\":"));
   LIT(P, VS_GATEWAYS);
   P.pool(env.istio_gateway.off, env.istio_gateway.len);
@@ -604,12 +598,12 @@ struct GenNbc {
     uint32_t view_j;
     NB_HD void operator()(Planner& P, uint32_t k) {
       if (!(c.flags & (1u << k))) return;
-      ViewRec rec;
-      ViewOut vw{views.p ? &rec : nullptr};
+      ViewOut vw;
+      vw.t = views;
+      vw.j = view_j + k;
       if (k == 0) plan_statefulset(P, c.d[0], v, *c.env, c.flags, vw);
       else if (k == 1) plan_service(P, c.d[0], v, c.flags, vw);
       else plan_virtualservice(P, c.d[0], v, *c.env, c.flags, c.aux, vw);
-      if (views.p) views.store(view_j + k, rec);
     }
   };
   NB_HD static uint32_t run(DocCtx& c, ObjSink s) {

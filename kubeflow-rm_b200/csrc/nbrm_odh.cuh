@@ -35,7 +35,7 @@ NB_HD bool mesh_enabled(const Doc& d, const NbView& v) {
   return annotation_true(d, v.a_mesh);
 }
 
-NB_HD void plan_labels_notebook_name(Planner& P, const NbView& v, ViewOut vw) {
+NB_HD void plan_labels_notebook_name(Planner& P, const NbView& v, ViewOut& vw) {
   vw.begin(VF_LABELS, P.total + LIT_AFTER(LABELS_NOTEBOOK_NAME, "\"labels\":"));
   LIT(P, LABELS_NOTEBOOK_NAME);
   put_str(P, v.name);
@@ -43,7 +43,7 @@ NB_HD void plan_labels_notebook_name(Planner& P, const NbView& v, ViewOut vw) {
 }
 
 NB_HD void plan_network_policy(Planner& P, const NbView& v, const EnvLits& env, uint32_t flags,
-                               bool oauth_np, ViewOut vw) {
+                               bool oauth_np, ViewOut& vw) {
   LIT(P, NP_HEAD);
   vw.set(VF_KIND, LIT_AFTER(NP_HEAD, "\"kind\":"), LIT_AFTER(NP_HEAD, "\"kind\":\"NetworkPolicy\""));
   P.in(inner(v.name));
@@ -64,7 +64,7 @@ NB_HD void plan_network_policy(Planner& P, const NbView& v, const EnvLits& env, 
   vw.set(VF_ROOT, 0, P.total);
 }
 
-NB_HD void plan_route(Planner& P, const NbView& v, uint32_t flags, bool oauth_route, ViewOut vw) {
+NB_HD void plan_route(Planner& P, const NbView& v, uint32_t flags, bool oauth_route, ViewOut& vw) {
   LIT(P, ROUTE_HEAD);
   vw.set(VF_KIND, LIT_AFTER(ROUTE_HEAD, "\"kind\":"), LIT_AFTER(ROUTE_HEAD, "\"kind\":\"Route\""));
   put_str(P, v.name);
@@ -85,7 +85,7 @@ NB_HD void plan_route(Planner& P, const NbView& v, uint32_t flags, bool oauth_ro
   vw.set(VF_ROOT, 0, P.total);
 }
 
-NB_HD void plan_service_account(Planner& P, const NbView& v, uint32_t flags, ViewOut vw) {
+NB_HD void plan_service_account(Planner& P, const NbView& v, uint32_t flags, ViewOut& vw) {
   LIT(P, SA_HEAD);
   vw.set(VF_KIND, LIT_AFTER(SA_HEAD, "\"kind\":"), LIT_AFTER(SA_HEAD, "\"kind\":\"ServiceAccount\""));
   put_str(P, v.name);
@@ -97,7 +97,7 @@ NB_HD void plan_service_account(Planner& P, const NbView& v, uint32_t flags, Vie
   vw.set(VF_ROOT, 0, P.total);
 }
 
-NB_HD void plan_oauth_service(Planner& P, const NbView& v, uint32_t flags, ViewOut vw) {
+NB_HD void plan_oauth_service(Planner& P, const NbView& v, uint32_t flags, ViewOut& vw) {
   LIT(P, TLSSVC_HEAD);
   vw.set(VF_KIND, LIT_AFTER(TLSSVC_HEAD, "\"kind\":"), LIT_AFTER(TLSSVC_HEAD, "\"kind\":\"Service\""));
   P.in(inner(v.name));
@@ -145,7 +145,7 @@ NB_HD uint32_t base64(const unsigned char* in, uint32_t n, char* out) {
 // cookie_secret = base64(base64(16 seed bytes)), 32 characters (:192-195).  The
 // seed comes from the caller's CSPRNG; nothing random is drawn on the device.
 NB_HD void plan_oauth_secret(Planner& P, const NbView& v, uint32_t flags, const unsigned char* seed16,
-                             Aux& aux, ViewOut vw) {
+                             Aux& aux, ViewOut& vw) {
   LIT(P, SECRET_HEAD);
   vw.set(VF_KIND, LIT_AFTER(SECRET_HEAD, "\"kind\":"), LIT_AFTER(SECRET_HEAD, "\"kind\":\"Secret\""));
   P.in(inner(v.name));
@@ -169,7 +169,7 @@ NB_HD void plan_oauth_secret(Planner& P, const NbView& v, uint32_t flags, const 
   vw.set(VF_ROOT, 0, P.total);
 }
 
-NB_HD void plan_rolebinding(Planner& P, const NbView& v, uint32_t flags, ViewOut vw) {
+NB_HD void plan_rolebinding(Planner& P, const NbView& v, uint32_t flags, ViewOut& vw) {
   LIT(P, RB_HEAD);
   vw.set(VF_KIND, LIT_AFTER(RB_HEAD, "\"kind\":"), LIT_AFTER(RB_HEAD, "\"kind\":\"RoleBinding\""));
   P.in(inner(v.name));
@@ -192,7 +192,7 @@ NB_HD void plan_rolebinding(Planner& P, const NbView& v, uint32_t flags, ViewOut
 // reference would not build that object for this Notebook.
 NB_HD void plan_odh_object(Planner& P, const Doc& d, const NbView& v, const EnvLits& env,
                            uint32_t flags, uint32_t k, bool oauth, bool mesh,
-                           const unsigned char* seed16, Aux& aux, ViewOut vw) {
+                           const unsigned char* seed16, Aux& aux, ViewOut& vw) {
   vw.clear();
   switch (k) {
     case 0: plan_network_policy(P, v, env, flags, false, vw); break;
@@ -220,10 +220,10 @@ struct GenOdh {
     NB_HD void operator()(Planner& P, uint32_t k) {
       const unsigned char* seed =
           c.extra ? (const unsigned char*)c.extra + (size_t)c.index * 16 : nullptr;
-      ViewRec rec;
-      plan_odh_object(P, c.d[0], v, *c.env, c.flags, k, oauth, mesh, seed, c.aux,
-                      ViewOut{views.p ? &rec : nullptr});
-      if (views.p) views.store(view_j + k, rec);
+      ViewOut vw;
+      vw.t = views;
+      vw.j = view_j + k;
+      plan_odh_object(P, c.d[0], v, *c.env, c.flags, k, oauth, mesh, seed, c.aux, vw);
     }
   };
   NB_HD static uint32_t run(DocCtx& c, ObjSink s) {

@@ -155,46 +155,39 @@ struct ViewRec {
   uint32_t off[VIEW_FIELDS];
   uint32_t len[VIEW_FIELDS];
 };
-// A planner fills a ViewRec of its own (registers) while it plans ...
-struct ViewOut {
-  ViewRec* r;  // null: nobody asked
-  NB_HD void clear() {
-    if (r)
-      for (uint32_t f = 0; f < VIEW_FIELDS; ++f) r->off[f] = r->len[f] = 0;
-  }
-  NB_HD void set(uint32_t f, uint32_t off, uint32_t end) {
-    if (r) {
-      r->off[f] = off;
-      r->len[f] = end - off;
-    }
-  }
-  NB_HD void begin(uint32_t f, uint32_t off) {
-    if (r) r->off[f] = off;
-  }
-  NB_HD void end(uint32_t f, uint32_t e) {
-    if (r) r->len[f] = e - r->off[f];
-  }
-};
-// ... and the views of a batch are kept field-major: (off, len) of field f of object j at
+// The views of a batch are kept field-major: (off, len) of field f of object j at
 // p[f * n + j].  Threads that plan or read neighbouring objects then touch neighbouring
-// words, where an array of records would put every lane in a cache line of its own.
+// words, where an array of records would put every lane in a cache line of its own.  The
+// table is zeroed before the plan kernel runs; a planner stores only the fields it has.
 struct alignas(8) ViewEnt {
   uint32_t off, len;
 };
 struct ViewTable {
   ViewEnt* p;  // VIEW_FIELDS * n entries, or null
   uint32_t n;  // objects in the batch
-  NB_HD void store(uint32_t j, const ViewRec& r) const {
-    for (uint32_t f = 0; f < VIEW_FIELDS; ++f) {
-      ViewEnt e;
-      e.off = r.off[f];
-      e.len = r.len[f];
-      p[(size_t)f * n + j] = e;
-    }
+  NB_HD void store(uint32_t j, uint32_t f, uint32_t off, uint32_t len) const {
+    ViewEnt e;
+    e.off = off;
+    e.len = len;
+    p[(size_t)f * n + j] = e;
   }
   NB_HD Span get(uint32_t j, uint32_t f) const {
     const ViewEnt e = p[(size_t)f * n + j];
     return mk(e.off, e.len);
+  }
+};
+// What a planner writes through: one object's column of the table.
+struct ViewOut {
+  ViewTable t;  // t.p null: nobody asked
+  uint32_t j;
+  uint32_t b[VIEW_FIELDS];  // where a field began (begin ... end); constant indices, so these are registers
+  NB_HD void clear() {}
+  NB_HD void set(uint32_t f, uint32_t off, uint32_t end) {
+    if (t.p) t.store(j, f, off, end - off);
+  }
+  NB_HD void begin(uint32_t f, uint32_t off) { b[f] = off; }
+  NB_HD void end(uint32_t f, uint32_t e) {
+    if (t.p) t.store(j, f, b[f], e - b[f]);
   }
 };
 // The views of one input document, as a planner receives them.

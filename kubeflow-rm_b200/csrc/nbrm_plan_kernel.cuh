@@ -143,7 +143,7 @@ static const uint32_t PLAN_SMEM = 100 * 1024;  // two blocks per SM
 // own tuple only: a batch of mixed shapes costs the sum of its tuples, not 32 times the
 // largest of every 32.
 static const uint32_t PLANW_WARPS = 4;
-static const uint32_t NBRM_WARP_MAX_TUPLES = 32768;
+static const uint32_t NBRM_WARP_MAX_TUPLES = 4096;  // measured: profiles/README.md, "warp or thread"
 
 template <class G>
 __global__ void __launch_bounds__(PLANW_WARPS * 32) plan_kernel_warp(PlanIn in, PlanOut out,

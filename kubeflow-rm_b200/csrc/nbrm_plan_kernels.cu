@@ -32,6 +32,9 @@ void gen_shape_reviewopen(uint32_t*, uint32_t*, bool*);
 void launch_plan_reviewclose(const PlanIn&, const PlanOut&, uint64_t, cudaStream_t);
 void gen_shape_reviewclose(uint32_t*, uint32_t*, bool*);
 
+void launch_plan_convert(const PlanIn&, const PlanOut&, uint64_t, cudaStream_t);
+void gen_shape_convert(uint32_t*, uint32_t*, bool*);
+
 void launch_plan(int gen, const PlanIn& in, const PlanOut& out, uint64_t in_bytes, cudaStream_t st) {
   switch (gen) {
     case GEN_ID_NBC: launch_plan_nbc(in, out, in_bytes, st); break;
@@ -47,6 +50,7 @@ void launch_plan(int gen, const PlanIn& in, const PlanOut& out, uint64_t in_byte
     case GEN_ID_DIFF: launch_plan_diff(in, out, in_bytes, st); break;
     case GEN_ID_REVIEW_OPEN: launch_plan_reviewopen(in, out, in_bytes, st); break;
     case GEN_ID_REVIEW_CLOSE: launch_plan_reviewclose(in, out, in_bytes, st); break;
+    case GEN_ID_CONVERT: launch_plan_convert(in, out, in_bytes, st); break;
   }
 }
 
@@ -65,6 +69,7 @@ static bool shape_of(int gen, uint32_t* nobj, uint32_t* cap, bool* shared1) {
     case GEN_ID_DIFF: gen_shape_diff(nobj, cap, shared1); return true;
     case GEN_ID_REVIEW_OPEN: gen_shape_reviewopen(nobj, cap, shared1); return true;
     case GEN_ID_REVIEW_CLOSE: gen_shape_reviewclose(nobj, cap, shared1); return true;
+    case GEN_ID_CONVERT: gen_shape_convert(nobj, cap, shared1); return true;
   }
   *nobj = 0;
   *cap = 0;

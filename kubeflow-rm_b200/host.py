@@ -44,6 +44,11 @@ def load_host_library():
     lib.nbrm_odh_reconciler_free.argtypes = [C.c_void_p]
     lib.nbrm_odh_reconciler_free.restype = None
     lib.nbrm_odh_reconciler_reconcile.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.c_uint64), C.POINTER(C.c_double)]
+    lib.nbrm_ca_bundle.argtypes = [C.c_char_p, C.c_char_p, C.c_int, C.c_char_p, C.c_int, C.c_void_p,
+                                   C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
+    lib.nbrm_pem_count_certificates.argtypes = [C.c_char_p, C.c_uint64]
+    lib.nbrm_pem_count_certificates.restype = C.c_uint64
+    lib.nbrm_unset_notebook_cert_config.argtypes = [C.c_char_p, C.c_uint64, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
     lib.nbrm_workqueue_new.restype = C.c_void_p
     for fn in ("free", "add", "forget", "done"):
         getattr(lib, "nbrm_workqueue_" + fn).restype = None
@@ -200,3 +205,39 @@ class WorkQueue:
         if self.h:
             self.lib.nbrm_workqueue_free(self.h)
             self.h = None
+
+
+def ca_bundle(odh_cm, kube_cm, x509_ok=None):
+    """CreateNotebookCertConfigMap's bundle (nbrm_ca_bundle): odh_cm / kube_cm are the ConfigMaps'
+    data dicts or None (NotFound).  Returns the bundle text or None."""
+    lib = load_host_library()
+    enc = lambda cm, k: None if cm is None or k not in cm else cm[k].encode("latin-1")
+    ok = None
+    if x509_ok is not None:
+        ok = (C.c_int8 * 3)(*[(-1 if x509_ok.get(k) is None else int(x509_ok[k]))
+                              for k in ("ca-bundle.crt", "odh-ca-bundle.crt", "ca.crt")])
+    out, n = C.c_void_p(), C.c_uint64()
+    rc = lib.nbrm_ca_bundle(enc(odh_cm, "ca-bundle.crt"), enc(odh_cm, "odh-ca-bundle.crt"), 0 if odh_cm is None else 1,
+                            enc(kube_cm, "ca.crt"), 0 if kube_cm is None else 1, ok, C.byref(out), C.byref(n))
+    if rc != 1:
+        return None
+    b = C.string_at(out.value, n.value).decode("latin-1")
+    lib.nbrm_store_free_string(out)
+    return b
+
+
+def pem_count_certificates(bundle):
+    b = bundle.encode("latin-1")
+    return int(load_host_library().nbrm_pem_count_certificates(b, len(b)))
+
+
+def unset_notebook_cert_config(nb_json):
+    """(rc, bytes or None): nbrm_unset_notebook_cert_config."""
+    lib = load_host_library()
+    out, n = C.c_void_p(), C.c_uint64()
+    rc = lib.nbrm_unset_notebook_cert_config(nb_json, len(nb_json), C.byref(out), C.byref(n))
+    if rc != 1:
+        return rc, None
+    b = C.string_at(out.value, n.value)
+    lib.nbrm_store_free_string(out)
+    return rc, b

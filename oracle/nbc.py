@@ -408,3 +408,37 @@ def nb_name_from_involved_object(get_pod, ref):
 def is_sts_or_pod_event(event):
     """isStsOrPodEvent, notebook_controller.go:662-664."""
     return (event.get("involvedObject") or {}).get("kind") in ("Pod", "StatefulSet")
+
+
+# ---------------------------------------------------------------- version conversion
+API_VERSIONS = ("kubeflow.org/v1beta1", "kubeflow.org/v1", "kubeflow.org/v1alpha1")
+
+
+def convert_notebook(src, to_version, keep_metadata=False):
+    """ConvertTo / ConvertFrom, components/notebook-controller/api/v1/notebook_conversion.go:25-69
+    (api/v1alpha1 has the same two functions): the hub is v1beta1, a spoke converts to it with
+    ConvertTo and from it with ConvertFrom, and both copy exactly four things —
+    spec.template.spec, status.readyReplicas, status.containerState, and of every condition its
+    type, lastProbeTime, reason and message.  A condition's `status` and `lastTransitionTime`
+    are NOT copied (:30-38, :56-64): the destination has status "" and a zero time.  ObjectMeta
+    is not touched by these functions; keep_metadata carries the source's through, as a caller
+    that wants a usable object has to."""
+    spec = ((src.get("spec") or {}).get("template") or {}).get("spec")
+    st = src.get("status") or {}
+    conds = []
+    for c in st.get("conditions") or []:
+        n = {"type": c.get("type", ""), "status": ""}
+        if c.get("lastProbeTime"):
+            n["lastProbeTime"] = c["lastProbeTime"]
+        if c.get("reason"):
+            n["reason"] = c["reason"]
+        if c.get("message"):
+            n["message"] = c["message"]
+        conds.append(n)
+    out = {"apiVersion": to_version, "kind": "Notebook", "metadata": {},
+           "spec": {"template": {"spec": deepcopy(spec) if isinstance(spec, dict) else {}}},
+           "status": {"conditions": conds, "readyReplicas": st.get("readyReplicas") or 0,
+                      "containerState": deepcopy(st.get("containerState")) if isinstance(st.get("containerState"), dict) else {}}}
+    if keep_metadata and isinstance(src.get("metadata"), dict):
+        out["metadata"] = deepcopy(src["metadata"])
+    return out

@@ -21,6 +21,7 @@
 #include "../../kubeflow-rm_b200/csrc/nbrm_pd.cuh"
 #include "../../kubeflow-rm_b200/csrc/nbrm_profile.cuh"
 #include "../../kubeflow-rm_b200/csrc/nbrm_patch.cuh"
+#include "../../kubeflow-rm_b200/csrc/nbrm_convert.cuh"
 #include "../../kubeflow-rm_b200/csrc/nbrm_pool.h"
 
 using namespace nbrm;
@@ -107,7 +108,7 @@ int run_host(Out& g_out, const char* const data[3], const uint64_t* const off[3]
     s.nseg = nseg.data();
     s.lens = lens.data();
     s.cap = cap;
-    memset(views.data(), 0, views.size() * sizeof(ViewEnt));
+    memset(views.data(), 0, views.size() * sizeof(ViewEnt));  // as the host zeroes the table before a plan kernel
     s.views.p = views.data();
     s.views.n = G::NOBJ;
     s.view_j = 0;
@@ -316,6 +317,7 @@ HP_API int hostplan_run(int gen, const char* d0, const uint64_t* o0, const char*
     case 10: rc = run_host<GenJsonDiff>(g_out, data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenJsonDiff::NOBJ; break;
     case 11: rc = run_host<GenReviewOpen>(g_out, data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenReviewOpen::NOBJ; break;
     case 12: rc = run_host<GenReviewClose>(g_out, data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenReviewClose::NOBJ; break;
+    case 13: rc = run_host<GenConvert>(g_out, data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenConvert::NOBJ; break;
     case 8: rc = run_host<GenProfile>(g_out, data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenProfile::NOBJ; break;
   }
   *out_data = g_out.data.data();

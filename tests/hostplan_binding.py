@@ -115,3 +115,6 @@ class HostPlan:
         import numpy as np
         return self.run(GEN_REVIEW_CLOSE, [reviews, patches], flags=flags,
                         extra=np.asarray(statuses, dtype=np.uint32).tobytes())
+
+    def convert(self, notebooks, to_version, flags=0):
+        return self.run(13, [notebooks], flags=flags, arg0=to_version)

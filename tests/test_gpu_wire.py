@@ -96,3 +96,19 @@ def test_poddefault_reviews(ctx, pkg, wl):
             wire.check_patch_effect(pod, patch, exp[1])
             seen["patched"] += 1
     assert seen["empty"] > 50 and seen["patched"] > 100 and seen["plain"] > 100 and seen["error"] > 0, seen
+
+
+def test_notebook_version_conversion(ctx, pkg, wl, hostplan):
+    """nbrm_notebook_convert against the oracle's ConvertTo / ConvertFrom and the CPU build."""
+    from oracle import gojson, nbc
+    from test_hostplan_convert import samples, with_status
+    rng = random.Random(4)
+    nbs = [with_status(rng, nb) for nb in list(samples().values()) + wl.corpus("fuzz", 2000, start=9)]
+    docs = [wl.dumps(nb, rng) for nb in nbs]
+    for to_version, flags in ((0, 0), (1, 1), (2, 0)):
+        res = ctx.notebook_convert(pkg.Docs(docs), to_version, flags)
+        outs, st = hostplan.convert(docs, to_version, flags)
+        assert res.docs() == outs and not any(res.status)
+        for nb, o in zip(nbs, outs):
+            want = nbc.convert_notebook(nb, nbc.API_VERSIONS[to_version], keep_metadata=bool(flags))
+            assert gojson.canon(json.loads(o)) == gojson.canon(want)

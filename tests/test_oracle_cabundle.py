@@ -71,3 +71,37 @@ def test_unset_cert_config_and_its_loop_quirk():
         cabundle.unset_notebook_cert_config(notebook_with_certs(dup_last=True))
     out, changed = cabundle.unset_notebook_cert_config({"metadata": {"name": "x"}, "spec": {"template": {"spec": {"containers": [{"name": "y"}]}}}})
     assert not changed
+
+
+def test_host_library_matches_the_oracle(pkg, wl):
+    """kubeflow-rm_b200/host/ca_bundle.cc against the oracle on the same cases."""
+    import importlib
+    import json
+    import random
+    import __graft_entry__ as graft
+    host = importlib.import_module(graft.PKG_NAME + ".host")
+    for odh_cm, kube_cm, want in bundle_cases():
+        got = host.ca_bundle(odh_cm, kube_cm)
+        assert got == cabundle.cert_bundle(odh_cm, kube_cm)
+        if want is not None:
+            assert host.pem_count_certificates(got) == want
+    odh_cm = {"ca-bundle.crt": PEM["a"], "odh-ca-bundle.crt": PEM["b"]}
+    ok = {"ca-bundle.crt": False, "odh-ca-bundle.crt": True}       # the caller's x509 parser rejects the first
+    assert host.ca_bundle(odh_cm, None, ok) == cabundle.cert_bundle(odh_cm, None, ok) == PEM["b"]
+    nb = notebook_with_certs()
+    rc, out = host.unset_notebook_cert_config(wl.dumps(nb))
+    assert rc == 1 and json.loads(out) == cabundle.unset_notebook_cert_config(nb)[0]
+    assert host.unset_notebook_cert_config(wl.dumps(notebook_with_certs(dup_last=True)))[0] == -1
+    assert host.unset_notebook_cert_config(wl.dumps({"metadata": {"name": "x"}, "spec": {"template": {"spec": {"containers": [{"name": "y"}]}}}}))[0] == 0
+    rng = random.Random(3)
+    for _ in range(300):                      # shuffled / duplicated variables: same result or same panic
+        nb = notebook_with_certs()
+        env = nb["spec"]["template"]["spec"]["containers"][1]["env"]
+        env += [dict(rng.choice(env)) for _ in range(rng.randrange(3))]
+        rng.shuffle(env)
+        rc, out = host.unset_notebook_cert_config(wl.dumps(nb))
+        try:
+            want, _ = cabundle.unset_notebook_cert_config(nb)
+            assert rc == 1 and json.loads(out) == want
+        except cabundle.ReferencePanic:
+            assert rc == -1
