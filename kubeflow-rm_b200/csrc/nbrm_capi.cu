@@ -516,7 +516,7 @@ int run_generator(nbrm_ctx* c, int gen, const int (&map)[3], uint32_t flags, con
     }
     in.slot[k].data = s.data.as<char>();
     in.slot[k].off = s.off.as<uint64_t>();
-    if (s.indexed && !shared) {
+    if (s.indexed) {  // per-tuple slots and the shared arena alike
       in.slot[k].tape = s.tape.p;
       in.slot[k].tidx = s.tidx.as<uint2>();
     }
@@ -813,6 +813,11 @@ int nbrm_odh_mutate(nbrm_ctx* c, const nbrm_docs* notebooks, const nbrm_docs* ol
 
 int nbrm_poddefault_mutate_resident(nbrm_ctx* c) {
   if (!c) return -2;
+  // every Pod of the batch consults every PodDefault of its namespace several times: the list is
+  // indexed once (it usually stays resident across batches, like the reference's List would
+  // come from a cache) and the planner hops through the index instead of re-reading its text
+  if (c->slot[1].off.p && !c->slot[1].indexed)
+    if (int r = nbrm_slot_index(c, 1)) return r;
   const void* ranges = nullptr;
   if (c->extra_bytes) {
     if (c->extra_bytes != (uint64_t)c->slot[0].n * 8)

@@ -40,6 +40,10 @@ struct DocCtx {
   const char* shared;
   const uint64_t* shared_off;
   uint32_t shared_n;
+  // ... and its structural index when the arena was indexed (nbrm_slot_index): entries, and per
+  // document (first entry, count | flags << 16)
+  const void* shared_tape = nullptr;
+  const void* shared_tidx = nullptr;
   uint32_t result;      // generator-specific per-tuple result word (0 when unused)
   ViewIn view[3] = {{{nullptr, 0}, 0}, {{nullptr, 0}, 0}, {{nullptr, 0}, 0}};  // the producing generator's view of d[k], when it left one
 };

@@ -35,6 +35,15 @@ NB_HD Doc pd_doc(const DocCtx& c, uint32_t j) {
   const uint64_t o0 = c.shared_off[j], o1 = c.shared_off[j + 1];
   d.p = c.shared + o0;
   d.n = (uint32_t)(o1 - o0);
+#ifdef NBRM_TAPE
+  if (c.shared_tidx) {  // the PodDefault list stays resident and was indexed once: hop, do not scan
+    const uint32_t* ti = reinterpret_cast<const uint32_t*>(c.shared_tidx) + 2 * (size_t)j;
+    d.tape = reinterpret_cast<const TapeEnt*>(c.shared_tape) + ti[0];
+    d.nt = ti[1] & 0xffffu;
+    d.tflags = d.nt ? (ti[1] >> 16) : DOC_WS;
+    d.dlim = TAPE_MAX_DEPTH;
+  }
+#endif
   return d;
 }
 

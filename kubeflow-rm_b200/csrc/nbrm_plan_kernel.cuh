@@ -112,6 +112,8 @@ __global__ void plan_kernel(PlanIn in, PlanOut out, uint32_t smem_cap, uint32_t 
   c.shared = G::SHARED1 ? in.slot[1].data : nullptr;
   c.shared_off = G::SHARED1 ? in.slot[1].off : nullptr;
   c.shared_n = G::SHARED1 ? in.shared_n : 0;
+  c.shared_tape = G::SHARED1 ? in.slot[1].tape : nullptr;
+  c.shared_tidx = G::SHARED1 ? (const void*)in.slot[1].tidx : nullptr;
   ObjSink s;
   s.segs = out.segs + (size_t)i * G::NOBJ * out.cap;
   s.nseg = out.nseg + (size_t)i * G::NOBJ;
@@ -203,6 +205,8 @@ __global__ void __launch_bounds__(PLANW_WARPS * 32) plan_kernel_warp(PlanIn in, 
   c.shared = G::SHARED1 ? in.slot[1].data : nullptr;
   c.shared_off = G::SHARED1 ? in.slot[1].off : nullptr;
   c.shared_n = G::SHARED1 ? in.shared_n : 0;
+  c.shared_tape = G::SHARED1 ? in.slot[1].tape : nullptr;
+  c.shared_tidx = G::SHARED1 ? (const void*)in.slot[1].tidx : nullptr;
   ObjSink s;
   s.segs = out.segs + (size_t)i * G::NOBJ * out.cap;
   s.nseg = out.nseg + (size_t)i * G::NOBJ;

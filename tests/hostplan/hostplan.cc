@@ -62,6 +62,23 @@ int run_host(Out& g_out, const char* const data[3], const uint64_t* const off[3]
   std::vector<ViewEnt> views((size_t)G::NOBJ * VIEW_FIELDS);
   g_out.views.clear();
   const char* bases[SRC_COUNT] = {data[0], data[1], data[2], pool.data(), aux.data()};
+#ifdef NBRM_TAPE
+  // the shared arena (PodDefault list) is indexed once, as nbrm_slot_index does on the device
+  std::vector<TapeEnt> sh_tape;
+  std::vector<uint32_t> sh_tidx;
+  if (G::SHARED1 && data[1]) {
+    for (uint32_t j = 0; j < shared_n; ++j) {
+      const uint32_t len = (uint32_t)(off[1][j + 1] - off[1][j]);
+      const size_t at = sh_tape.size();
+      sh_tape.resize(at + len + 1);
+      uint32_t tf = 0;
+      const uint32_t nt = build_tape_scalar(data[1] + off[1][j], len, sh_tape.data() + at, g_tape_cap, &tf);
+      sh_tape.resize(at + nt);
+      sh_tidx.push_back((uint32_t)at);
+      sh_tidx.push_back(nt | (tf << 16));
+    }
+  }
+#endif
   for (uint64_t i = 0; i < n; ++i) {
     DocCtx c;
     uint32_t aux_abs = (uint32_t)i * AUX_PAD, aux_cap = AUX_PAD;
@@ -103,6 +120,12 @@ int run_host(Out& g_out, const char* const data[3], const uint64_t* const off[3]
     c.shared = G::SHARED1 ? data[1] : nullptr;
     c.shared_off = G::SHARED1 ? off[1] : nullptr;
     c.shared_n = G::SHARED1 ? shared_n : 0;
+#ifdef NBRM_TAPE
+    if (G::SHARED1 && data[1]) {
+      c.shared_tape = sh_tape.data();
+      c.shared_tidx = sh_tidx.data();
+    }
+#endif
     ObjSink s;
     s.segs = segs.data();
     s.nseg = nseg.data();
