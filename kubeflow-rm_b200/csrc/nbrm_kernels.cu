@@ -204,6 +204,13 @@ struct Writer {
       acc = fill ? ((unsigned long long)v >> (8u * (nb - fill))) : 0ull;
     }
   }
+  // append 8 bytes at once (only once the head bytes are out: o is 8-byte aligned then)
+  __device__ __forceinline__ void put8(unsigned long long v) {
+    const uint32_t sh = 8u * fill;
+    *reinterpret_cast<unsigned long long*>(o) = acc | (v << sh);
+    o += 8;
+    acc = fill ? (v >> (64u - sh)) : 0ull;
+  }
   __device__ __forceinline__ void finish() {
     for (uint32_t k = 0; k < fill; ++k) o[k] = (char)(acc >> (8u * k));
   }
@@ -222,6 +229,16 @@ __device__ __forceinline__ void copy_segment(const char* src, uint32_t len, Writ
     if (nb <= last) wn = *reinterpret_cast<const uint4*>(nb);
     const uint32_t k = (uint32_t)a & 15u;
     const uint32_t avail = min(16u - k, len);
+    if (k == 0 && avail == 16 && W.head == 0) {
+      // a whole source block (the inside of a long segment, e.g. a copied PodSpec): two 8-byte
+      // appends instead of four 4-byte ones
+      W.put8((unsigned long long)w.x | ((unsigned long long)w.y << 32));
+      W.put8((unsigned long long)w.z | ((unsigned long long)w.w << 32));
+      a += 16;
+      len -= 16;
+      w = wn;
+      continue;
+    }
     uint32_t done = 0;
     while (done < avail) {
       const uint32_t kk = k + done;
