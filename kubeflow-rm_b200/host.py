@@ -49,6 +49,8 @@ def load_host_library():
     lib.nbrm_pem_count_certificates.argtypes = [C.c_char_p, C.c_uint64]
     lib.nbrm_pem_count_certificates.restype = C.c_uint64
     lib.nbrm_unset_notebook_cert_config.argtypes = [C.c_char_p, C.c_uint64, C.POINTER(C.c_void_p), C.POINTER(C.c_uint64)]
+    lib.nbrm_kfam_binding_name.argtypes = [C.c_char_p] * 4
+    lib.nbrm_kfam_binding_name.restype = C.c_void_p
     lib.nbrm_workqueue_new.restype = C.c_void_p
     for fn in ("free", "add", "forget", "done"):
         getattr(lib, "nbrm_workqueue_" + fn).restype = None
@@ -241,3 +243,11 @@ def unset_notebook_cert_config(nb_json):
     b = C.string_at(out.value, n.value)
     lib.nbrm_store_free_string(out)
     return rc, b
+
+
+def kfam_binding_name(user_kind, user_name, roleref_kind, roleref_name):
+    lib = load_host_library()
+    p = lib.nbrm_kfam_binding_name(user_kind.encode(), user_name.encode(), roleref_kind.encode(), roleref_name.encode())
+    out = C.string_at(p).decode()
+    lib.nbrm_store_free_string(C.c_void_p(p))
+    return out

@@ -99,3 +99,13 @@ def profile_objects(profile, env, default_labels):
             sa("default-viewer"), rb("default-viewer", "kubeflow-view", sa_subject("default-viewer")),
             rb("namespaceAdmin", "kubeflow-admin", [deepcopy(owner)], {"user": owner_name, "role": "admin"}),
             quota]
+
+
+def kfam_binding_name(user_kind, user_name, roleref_kind, roleref_name):
+    """getBindingName, components/access-management/kfam/bindings.go:61-78: every run of
+    characters outside [a-zA-Z0-9] becomes one '-', the four parts are joined by '-' and
+    lower-cased (url.QueryEscape is the identity on what the first replacement leaves)."""
+    import re
+    reg = re.compile(r"[^a-zA-Z0-9]+")
+    raw = "-".join([user_kind, reg.sub("-", user_name), roleref_kind, roleref_name]).lower()
+    return reg.sub("-", raw)

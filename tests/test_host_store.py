@@ -101,3 +101,27 @@ def test_workqueue_semantics(pkg):
         last = q.add_rate_limited("ns", "e", 0.0)
     assert last == 1000.0
     q.close()
+
+
+def test_kfam_binding_names(pkg):
+    """getBindingName against the reference's table (access-management/kfam/bindings_test.go:25-41;
+    the Binding there is User / ClusterRole "edit"), oracle and C++ alike."""
+    import importlib
+    import random
+    import __graft_entry__ as graft
+    from oracle import profile as oprofile
+    host = importlib.import_module(graft.PKG_NAME + ".host")
+    table = [("lalith.vaka@zq.msds.kp.org", "user-lalith-vaka-zq-msds-kp-org-clusterrole-edit"),
+             ("397401@zq.msds.kp.org", "user-397401-zq-msds-kp-org-clusterrole-edit"),
+             ("lalith.397401@zq.msds.kp.org", "user-lalith-397401-zq-msds-kp-org-clusterrole-edit"),
+             ("397401.vaka@zq.msds.kp.org", "user-397401-vaka-zq-msds-kp-org-clusterrole-edit"),
+             ("i397401@zq.msds.kp.org", "user-i397401-zq-msds-kp-org-clusterrole-edit")]
+    for name, want in table:
+        assert oprofile.kfam_binding_name("User", name, "ClusterRole", "edit") == want
+        assert host.kfam_binding_name("User", name, "ClusterRole", "edit") == want
+    rng = random.Random(1)
+    for _ in range(500):
+        name = "".join(rng.choice("aZ09.@_-+ é/~") for _ in range(rng.randrange(0, 20)))
+        kind = rng.choice(["User", "Group", "ServiceAccount"])
+        assert host.kfam_binding_name(kind, name, "ClusterRole", "kubeflow-edit") == \
+            oprofile.kfam_binding_name(kind, name, "ClusterRole", "kubeflow-edit")
