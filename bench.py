@@ -399,7 +399,7 @@ def traffic_from_profiles(kernel, batch):
     """DRAM bytes per launch of `kernel` from the newest `ncu --set full` summary under profiles/
     that has it (written by profiles/summarize_ncu.py; its header names the batch it was taken at),
     scaled to this run's batch.  (bytes, file) or (None, None)."""
-    short = kernel.replace("plan_kernel<", "").replace("emit_objects[", "").rstrip(">]")
+    short = kernel.replace("plan_kernel<", "").replace("emit_warp[", "").rstrip(">]")
     for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_ncu_full*.txt")), reverse=True):
         text = open(path).read()
         m = re.search(r"batch[ _]notebooks[ :=]+(\d+)", text) or re.search(r"--batch (\d+)", text)
@@ -574,7 +574,7 @@ def main():
         for g, nm in enumerate(names):
             if prof.runs_gen[g]:
                 kern["plan_kernel<%s>" % nm] = (prof.plan_ms_gen[g] / args.steps, prof.plan_bytes_gen[g] / args.steps)
-                kern["emit_objects[%s]" % nm] = (prof.emit_ms_gen[g] / args.steps, prof.emit_bytes_gen[g] / args.steps)
+                kern["emit_warp[%s]" % nm] = (prof.emit_ms_gen[g] / args.steps, prof.emit_bytes_gen[g] / args.steps)
         # parity inside the bench: the write sets have the size the oracle expects, and the first
         # Notebooks' results equal the oracle's, object by object
         out = rp.run(d_req, seeds, copy=True, overlap=False)

@@ -587,7 +587,7 @@ int run_generator(nbrm_ctx* c, int gen, const int (&map)[3], uint32_t flags, con
   b.p[SRC_POOL] = c->pool.as<char>();
   b.p[SRC_AUX] = c->aux.as<char>();
   {
-    KScope k(c, K_EMIT, n_out ? 2 : 0, gen);
+    KScope k(c, K_EMIT, n_out ? 1 : 0, gen);
     launch_emit(po.segs, po.nseg, po.lens, c->out_off.as<uint64_t>(), n_out, cap, nobj, b,
                 c->out.as<char>(), c->sm_count, c->stream);
   }

@@ -5,6 +5,7 @@
 #include <mutex>
 
 #include "nbrm_dev.h"
+#include "nbrm_emit.cuh"
 
 namespace nbrm {
 
@@ -156,156 +157,117 @@ size_t scan_tmp_bytes(uint32_t n) {
 }
 
 // ---------------------------------------------------------------- emit
-// Gather-copy of every planned object into the packed output.
+// Gather-copy of every planned object into the packed output: one warp per object, one lane
+// per 16-byte block of the output (nbrm_emit.cuh has the per-block work and the reasons).
 //
-// Objects here are a few hundred bytes assembled from segments of a few dozen
-// bytes (template text alternating with names), so a warp spread over one
-// object idles most of its lanes on per-segment bookkeeping.  emit_objects
-// therefore gives each object to ONE thread, and makes the 32 lanes of a warp
-// work on the same object kind of 32 consecutive input documents (objects are
-// stored document-major, nobj per document), so that the lanes run the same
-// segment structure in lockstep.  A thread reads each source through aligned
-// 16-byte blocks and writes its object through aligned 8-byte words; only the
-// bytes before the first and after the last aligned word are stored singly,
-// because those words are shared with the neighbouring objects.
-//
-// Objects longer than BIG_OBJECT bytes (a Notebook with a huge annotation) are
-// left to emit_big_objects, which spreads a warp over each of them.
+// The segment list of an object is taken in windows of EMITW_WIN segments: the warp loads a
+// window with coalesced 8-byte loads, scans the lengths with shuffles and leaves segments and
+// prefix sums in shared memory.  The output is walked in rounds of 32 aligned 16-byte blocks;
+// nbrm_emit.cuh says how a round is cut into pieces and dealt to the lanes.  Objects of any
+// length and any number of segments take this path.
 
-static const uint32_t BIG_OBJECT = 16384;
+static const uint32_t EMITW_WARPS = EMIT_THREADS / 32;
+static const uint32_t EMITW_WIN = 128;
 
-struct Writer {
-  char* o;
-  unsigned long long acc;
-  uint32_t fill;  // bytes in acc
-  uint32_t head;  // single bytes still to store before o is 8-byte aligned
-  __device__ __forceinline__ void init(char* p) {
-    o = p;
-    acc = 0;
-    fill = 0;
-    head = (uint32_t)((8u - ((uint32_t)(unsigned long long)p & 7u)) & 7u);
+__global__ void __launch_bounds__(EMIT_THREADS) emit_warp(const Seg* __restrict__ segs,
+                                                         const uint32_t* __restrict__ nseg,
+                                                         const uint64_t* __restrict__ off,
+                                                         uint32_t n_out, uint32_t cap, uint32_t opw,
+                                                         SrcBases bases, char* __restrict__ out) {
+  __shared__ uint32_t sP[EMITW_WARPS][EMITW_WIN + 1];
+  __shared__ Seg sS[EMITW_WARPS][EMITW_WIN];
+  __shared__ const char* sB[SRC_COUNT];
+  __shared__ __align__(16) uint32_t sscr[EMITW_WARPS][32 * 12];  // per lane: the source words of its piece (nbrm_emit.cuh)
+  __shared__ uint4 sT[17];                         // sT[x]: all bytes below position x set
+  if (threadIdx.x < 17u)
+    sT[threadIdx.x] = make_uint4(emitw::below_word(threadIdx.x, 0), emitw::below_word(threadIdx.x, 1),
+                                 emitw::below_word(threadIdx.x, 2), emitw::below_word(threadIdx.x, 3));
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (uint32_t k = 0; k < SRC_COUNT; ++k) sB[k] = bases.p[k];
   }
-  // append the nb (1..4) low bytes of v
-  __device__ __forceinline__ void put(uint32_t v, uint32_t nb) {
-    while (head && nb) {
-      *o++ = (char)v;
-      v >>= 8;
-      --nb;
-      --head;
-    }
-    if (!nb) return;
-    if (nb < 4) v &= (1u << (8u * nb)) - 1u;
-    acc |= (unsigned long long)v << (8u * fill);
-    fill += nb;
-    if (fill >= 8) {
-      *reinterpret_cast<unsigned long long*>(o) = acc;
-      o += 8;
-      fill -= 8;
-      acc = fill ? ((unsigned long long)v >> (8u * (nb - fill))) : 0ull;
-    }
+  __syncthreads();
+  const uint32_t FULL = 0xffffffffu;
+  const uint32_t lane = threadIdx.x & 31u, wib = threadIdx.x >> 5;
+  // a warp takes `opw` consecutive objects: their segment counts and offsets come with one
+  // coalesced load each, and objects that have nothing to write (a compare that found no
+  // difference) cost nothing more than that
+  const uint32_t base = (blockIdx.x * EMITW_WARPS + wib) * opw;
+  if (base >= n_out) return;
+  uint32_t my_ns = 0;
+  unsigned long long my_off = 0;
+  if (lane < opw && base + lane < n_out) {
+    my_ns = nseg[base + lane];
+    my_off = off[base + lane];
   }
-  // append 8 bytes at once (only once the head bytes are out: o is 8-byte aligned then)
-  __device__ __forceinline__ void put8(unsigned long long v) {
-    const uint32_t sh = 8u * fill;
-    *reinterpret_cast<unsigned long long*>(o) = acc | (v << sh);
-    o += 8;
-    acc = fill ? (v >> (64u - sh)) : 0ull;
-  }
-  __device__ __forceinline__ void finish() {
-    for (uint32_t k = 0; k < fill; ++k) o[k] = (char)(acc >> (8u * k));
-  }
-};
-
-__device__ __forceinline__ void copy_segment(const char* src, uint32_t len, Writer& W) {
-  if (!len) return;
-  unsigned long long a = (unsigned long long)src;
-  const unsigned long long last = (a + len - 1) & ~15ull;  // the aligned block that holds the last byte
-  uint4 w = *reinterpret_cast<const uint4*>(a & ~15ull);
-  while (len) {
-    // the next block is on its way while this one is written out (a thread's loads are
-    // otherwise a chain: descriptor -> source block -> source block ...)
-    const unsigned long long nb = (a & ~15ull) + 16;
-    uint4 wn = w;
-    if (nb <= last) wn = *reinterpret_cast<const uint4*>(nb);
-    const uint32_t k = (uint32_t)a & 15u;
-    const uint32_t avail = min(16u - k, len);
-    if (k == 0 && avail == 16 && W.head == 0) {
-      // a whole source block (the inside of a long segment, e.g. a copied PodSpec): two 8-byte
-      // appends instead of four 4-byte ones
-      W.put8((unsigned long long)w.x | ((unsigned long long)w.y << 32));
-      W.put8((unsigned long long)w.z | ((unsigned long long)w.w << 32));
-      a += 16;
-      len -= 16;
-      w = wn;
-      continue;
-    }
-    uint32_t done = 0;
-    while (done < avail) {
-      const uint32_t kk = k + done;
-      const uint32_t word = (kk & 8u) ? ((kk & 4u) ? w.w : w.z) : ((kk & 4u) ? w.y : w.x);
-      const uint32_t sh = kk & 3u;
-      const uint32_t nb4 = min(4u - sh, avail - done);
-      W.put(word >> (8u * sh), nb4);
-      done += nb4;
-    }
-    a += avail;
-    len -= avail;
-    w = wn;
-  }
-}
-
-__global__ void __launch_bounds__(EMIT_THREADS) emit_objects(const Seg* __restrict__ segs,
-                                                            const uint32_t* __restrict__ nseg,
-                                                            const uint32_t* __restrict__ lens,
-                                                            const uint64_t* __restrict__ off,
-                                                            uint32_t n_out, uint32_t cap,
-                                                            uint32_t nobj, SrcBases bases,
-                                                            char* __restrict__ out) {
-  // thread -> object: lanes of a warp take the same kind k of 32 consecutive documents
-  const uint32_t t = blockIdx.x * EMIT_THREADS + threadIdx.x;
-  const uint32_t per_group = 32u * nobj;
-  const uint32_t group = t / per_group, r = t - group * per_group;
-  const uint32_t k = r >> 5, lane = r & 31u;
-  const uint32_t obj = (group * 32u + lane) * nobj + k;
-  if (obj >= n_out) return;
-  const uint32_t ns = nseg[obj];
-  if (!ns || lens[obj] > BIG_OBJECT) return;
-  const Seg* s = segs + (size_t)obj * cap;
-  Writer W;
-  W.init(out + off[obj]);
-  Seg next = s[0];
-  for (uint32_t j = 0; j < ns; ++j) {
-    const Seg sg = next;
-    if (j + 1 < ns) next = s[j + 1];  // the next descriptor loads while this segment is copied
-    copy_segment(bases.p[sg.len_src >> 28] + sg.off, sg.len_src & SEG_LEN_MASK, W);
-  }
-  W.finish();
-}
-
-// One warp per object, lanes stride over each segment's bytes; only for the
-// rare objects emit_objects skips.
-__global__ void __launch_bounds__(EMIT_THREADS) emit_big_objects(const Seg* __restrict__ segs,
-                                                                const uint32_t* __restrict__ nseg,
-                                                                const uint32_t* __restrict__ lens,
-                                                                const uint64_t* __restrict__ off,
-                                                                uint32_t n_out, uint32_t cap,
-                                                                SrcBases bases,
-                                                                char* __restrict__ out) {
-  const int lane = threadIdx.x & 31;
-  const uint32_t warps_per_block = EMIT_THREADS / 32;
-  uint32_t w = blockIdx.x * warps_per_block + (threadIdx.x >> 5);
-  const uint32_t stride = gridDim.x * warps_per_block;
-  for (; w < n_out; w += stride) {
-    if (lens[w] <= BIG_OBJECT) continue;
-    const uint32_t ns = nseg[w];
-    const Seg* s = segs + (size_t)w * cap;
-    char* o = out + off[w];
-    for (uint32_t k = 0; k < ns; ++k) {
-      const Seg sg = s[k];
-      const uint32_t len = sg.len_src & SEG_LEN_MASK;
-      const char* src = bases.p[sg.len_src >> 28] + sg.off;
-      for (uint32_t j = lane; j < len; j += 32) o[j] = src[j];
-      o += len;
+  uint32_t* P = sP[wib];
+  Seg* S = sS[wib];
+  uint32_t* scr = sscr[wib];
+  uint32_t live = __ballot_sync(FULL, my_ns != 0u);
+  while (live) {
+    const uint32_t oi = (uint32_t)__ffs((int)live) - 1u;
+    live &= live - 1u;
+    const uint32_t ns = __shfl_sync(FULL, my_ns, oi);
+    const Seg* os = segs + (size_t)(base + oi) * cap;
+    char* dst = out + __shfl_sync(FULL, my_off, oi);
+    for (uint32_t w0 = 0; w0 < ns; w0 += EMITW_WIN) {
+      const uint32_t m = min(EMITW_WIN, ns - w0);
+      uint32_t run = 0;
+      for (uint32_t j0 = 0; j0 < m; j0 += 32u) {
+        const uint32_t j = j0 + lane;
+        Seg s;
+        s.off = 0;
+        s.len_src = 0;
+        if (j < m) s = os[w0 + j];
+        uint32_t v = s.len_src & SEG_LEN_MASK;
+#pragma unroll
+        for (uint32_t d = 1; d < 32u; d <<= 1) {
+          const uint32_t t = __shfl_up_sync(FULL, v, d);
+          if (lane >= d) v += t;
+        }
+        if (j < m) {
+          S[j] = s;
+          P[j + 1] = run + v;
+        }
+        run += __shfl_sync(FULL, v, 31);
+      }
+      if (lane == 0) P[0] = 0;
+      __syncwarp();
+      const uint32_t L = run;  // bytes of this window
+      const uint32_t head = (uint32_t)((unsigned long long)dst & 15ull);
+      char* blk0 = dst - head;
+      const uint32_t nblocks = (head + L + 15u) >> 4;
+      uint32_t first = 0;  // the segment the round's first byte lies in
+      for (uint32_t c = 0; c < nblocks; c += 32u) {
+        const uint32_t nbr = min(32u, nblocks - c);
+        const uint32_t qs = c ? 16u * c - head : 0u;
+        const uint32_t qe = min(L, 16u * (c + nbr) - head);
+        // segments that start inside the round (the prefix sums are ascending)
+        uint32_t cnt = 0;
+        for (;;) {
+          const uint32_t t = first + 1u + cnt + lane;
+          const uint32_t bal = __ballot_sync(FULL, t < m && P[t] < qe);
+          cnt += __popc(bal);
+          if (bal != FULL) break;
+        }
+        const bool ragged = (c == 0u && head) || 16u * (c + nbr) - head > L;  // a block shared with a neighbour
+        char* rdst = blk0 + 16ull * c;
+        if (cnt == 0u && !ragged) {
+          // the round lies inside segment `first`: source to output, one shift for the whole warp
+          const Seg sg = S[first];
+          if (lane < nbr) emitw::copy_pure_block(sB[sg.len_src >> 28] + sg.off + (qs - P[first]), rdst, lane);
+        } else if (lane < nbr) {
+          const uint32_t b = c + lane;
+          const uint32_t q = b ? 16u * b - head : 0u;
+          const uint32_t g = cnt ? emitw::find_seg(P, first, first + cnt, q) : first;
+          emitw::emit_block(P, S, g, sB, q, min(L, 16u * (b + 1u) - head), b ? 0u : head, rdst + 16ull * lane,
+                            scr + 12u * lane, reinterpret_cast<const uint32_t*>(sT));
+        }
+        first += cnt;
+        if (first + 1u < m && P[first + 1u] == qe) ++first;
+      }
+      dst += L;
+      __syncwarp();
     }
   }
 }
@@ -313,17 +275,17 @@ __global__ void __launch_bounds__(EMIT_THREADS) emit_big_objects(const Seg* __re
 void launch_emit(const Seg* segs, const uint32_t* nseg, const uint32_t* lens, const uint64_t* off,
                  uint32_t n_out, uint32_t cap, uint32_t nobj, const SrcBases& bases, char* out,
                  int sm_count, cudaStream_t st) {
+  (void)lens;
+  (void)nobj;
+  (void)sm_count;
   if (!n_out) return;
-  // round the thread count up to whole (32 * nobj) groups
-  const uint32_t per_group = 32u * nobj;
-  const uint64_t threads = (uint64_t)((n_out / nobj + 31u) / 32u) * per_group;
-  const uint32_t blocks = (uint32_t)((threads + EMIT_THREADS - 1) / EMIT_THREADS);
-  emit_objects<<<blocks, EMIT_THREADS, 0, st>>>(segs, nseg, lens, off, n_out, cap, nobj, bases, out);
-  uint32_t wpb = EMIT_THREADS / 32;
-  uint32_t big_blocks = (n_out + wpb - 1) / wpb;
-  uint32_t max_blocks = (uint32_t)sm_count * 8;
-  if (big_blocks > max_blocks) big_blocks = max_blocks;
-  emit_big_objects<<<big_blocks, EMIT_THREADS, 0, st>>>(segs, nseg, lens, off, n_out, cap, bases, out);
+  // objects per warp: one while the batch is small (latency), up to eight once there are more
+  // warps than the GPU holds at a time
+  uint32_t opw = n_out / 8192u;
+  opw = opw < 1u ? 1u : opw > 8u ? 8u : opw;
+  const uint32_t warps = (n_out + opw - 1) / opw;
+  const uint32_t blocks = (warps + EMITW_WARPS - 1) / EMITW_WARPS;
+  emit_warp<<<blocks, EMIT_THREADS, 0, st>>>(segs, nseg, off, n_out, cap, opw, bases, out);
 }
 
 }  // namespace nbrm

@@ -6,6 +6,7 @@
 #include <stdint.h>
 #include <string.h>
 
+#include <algorithm>
 #include <string>
 #include <thread>
 #include <vector>
@@ -23,6 +24,7 @@
 #include "../../kubeflow-rm_b200/csrc/nbrm_patch.cuh"
 #include "../../kubeflow-rm_b200/csrc/nbrm_convert.cuh"
 #include "../../kubeflow-rm_b200/csrc/nbrm_pool.h"
+#include "../../kubeflow-rm_b200/csrc/nbrm_emit.cuh"
 
 using namespace nbrm;
 
@@ -163,6 +165,80 @@ int run_host(Out& g_out, const char* const data[3], const uint64_t* const off[3]
 #define HP_API __attribute__((visibility("default")))
 
 extern "C" {
+
+// The emit kernel's per-block routine (nbrm_emit.cuh), run block by block the way emit_warp's
+// rounds hand blocks to lanes.  srcs[k] / src_len[k]: the source buffers; seg_*: the segment
+// list of one object; head: where in a 16-byte block of the output the object starts; win:
+// segments per window.  out must hold head + total + 16 bytes and comes back with every
+// byte outside [head, head + total) untouched.
+HP_API int hostplan_emit_blocks(const char* const* srcs, const uint64_t* src_len, uint32_t n_src,
+                                const uint32_t* seg_off, const uint32_t* seg_len, const uint32_t* seg_src,
+                                uint32_t ns, uint32_t head, uint32_t win, char* out) {
+  if (n_src > SRC_COUNT || head > 15 || !win) return -1;
+  // sources in 16-byte aligned, padded copies: the routine reads whole aligned blocks
+  std::vector<std::vector<char>> copies(n_src);
+  const char* bases[SRC_COUNT] = {};
+  for (uint32_t k = 0; k < n_src; ++k) {
+    copies[k].assign(src_len[k] + 48, 0x55);
+    char* a = copies[k].data();
+    a += (16 - ((uintptr_t)a & 15)) & 15;
+    memcpy(a, srcs[k], src_len[k]);
+    bases[k] = a;
+  }
+  std::vector<char> obuf(head + 64, 0);
+  uint64_t total = 0;
+  for (uint32_t j = 0; j < ns; ++j) total += seg_len[j];
+  obuf.assign(head + total + 64, 0);
+  char* o = obuf.data();
+  o += (16 - ((uintptr_t)o & 15)) & 15;
+  memcpy(o, out, head + total + 16);
+  char* dst = o + head;
+  for (uint32_t w0 = 0; w0 < ns; w0 += win) {
+    const uint32_t m = ns - w0 < win ? ns - w0 : win;
+    std::vector<uint32_t> P(m + 1, 0);
+    std::vector<Seg> S(m);
+    for (uint32_t j = 0; j < m; ++j) {
+      S[j].off = seg_off[w0 + j];
+      S[j].len_src = (seg_src[w0 + j] << 28) | seg_len[w0 + j];
+      P[j + 1] = P[j] + seg_len[w0 + j];
+    }
+    const uint32_t L = P[m];
+    const uint32_t hd = (uint32_t)((uintptr_t)dst & 15);
+    char* blk0 = dst - hd;
+    const uint32_t nblocks = (hd + L + 15) >> 4;
+    uint32_t first = 0;
+    uint32_t T[17 * 4];
+    for (uint32_t x = 0; x < 17; ++x)
+      for (uint32_t w = 0; w < 4; ++w) T[4 * x + w] = emitw::below_word(x, w);
+    for (uint32_t c = 0; c < nblocks; c += 32) {  // the rounds of emit_warp, lanes one after the other
+      const uint32_t nbr = std::min<uint32_t>(32, nblocks - c);
+      const uint32_t qs = c ? 16 * c - hd : 0;
+      const uint32_t qe = std::min<uint32_t>(L, 16 * (c + nbr) - hd);
+      uint32_t cnt = 0;
+      while (first + 1 + cnt < m && P[first + 1 + cnt] < qe) ++cnt;
+      const bool ragged = (c == 0 && hd) || 16 * (c + nbr) - hd > L;
+      char* rdst = blk0 + 16 * (size_t)c;
+      for (uint32_t lane = 0; lane < nbr; ++lane) {
+        if (cnt == 0 && !ragged) {
+          emitw::copy_pure_block(bases[S[first].len_src >> 28] + S[first].off + (qs - P[first]), rdst, lane);
+          continue;
+        }
+        const uint32_t b = c + lane;
+        const uint32_t q = b ? 16 * b - hd : 0;
+        const uint32_t g = cnt ? emitw::find_seg(P.data(), first, first + cnt, q) : first;
+        uint32_t X[12];
+        memset(X, 0xcc, sizeof X);
+        emitw::emit_block(P.data(), S.data(), g, bases, q, std::min<uint32_t>(L, 16 * (b + 1) - hd), b ? 0 : hd,
+                          rdst + 16 * (size_t)lane, X, T);
+      }
+      first += cnt;
+      if (first + 1 < m && P[first + 1] == qe) ++first;
+    }
+    dst += L;
+  }
+  memcpy(out, o, head + total + 16);
+  return 0;
+}
 
 HP_API int hostplan_tape_mode(void) {
 #ifdef NBRM_TAPE
