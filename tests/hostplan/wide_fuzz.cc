@@ -44,6 +44,34 @@ static uint32_t scalar_skip(const char* p, uint32_t i, uint32_t n) {
   return n;
 }
 
+// skip_string and skip_key, restated from the byte loops of nbrm_json.cuh
+static uint32_t scalar_string(const char* p, uint32_t i, uint32_t n) {
+  uint32_t j = i + 1;
+  while (j < n) {
+    char c = p[j];
+    if (c == '\\') j += 2;
+    else if (c == '"') return j + 1;
+    else ++j;
+  }
+  return n;
+}
+static uint32_t scalar_key(const char* p, uint32_t i, uint32_t n, uint32_t& h) {
+  uint32_t j = i + 1;
+  h = 2166136261u;
+  while (j < n) {
+    char c = p[j];
+    if (c == '"') return j + 1;
+    h = (h ^ (uint32_t)(unsigned char)c) * 16777619u;
+    if (c == '\\' && j + 1 < n) {
+      h = (h ^ (uint32_t)(unsigned char)p[j + 1]) * 16777619u;
+      j += 2;
+    } else {
+      ++j;
+    }
+  }
+  return n;
+}
+
 static uint64_t rng_state = 0x9e3779b97f4a7c15ull;
 static uint32_t rnd() {
   rng_state ^= rng_state << 13;
@@ -155,6 +183,23 @@ int main() {
           printf("inner skip differs at %u: want %u got %u align %u doc %s\n", i, want, got, align,
                  doc.c_str());
           return 1;
+        }
+      }
+      // the string scanners from every quote of the text (whatever it opens), whole and truncated
+      for (uint32_t i = 0; i < text.size(); ++i) {
+        if (p[i] != '"') continue;
+        const uint32_t ns[3] = {(uint32_t)text.size(), i + 1 + rnd() % 12, i + 1};
+        for (uint32_t n : ns) {
+          if (n > text.size() || n <= i) continue;
+          const uint32_t want = scalar_string(p, i, n), got = wide::skip_string(p, i, n);
+          uint32_t hw = 0, hg = 0;
+          const uint32_t wantk = scalar_key(p, i, n, hw), gotk = wide::skip_key(p, i, n, hg);
+          cases += 2;
+          if (want != got || wantk != gotk || (wantk < n && hw != hg) || (wantk == n && gotk == n && hw != hg)) {
+            printf("string scan differs at %u n %u align %u: string %u/%u key %u/%u hash %08x/%08x text %.*s\n", i, n,
+                   align, want, got, wantk, gotk, hw, hg, (int)n, p);
+            return 1;
+          }
         }
       }
       // bytes_equal against the obvious loop, both operands at every alignment
