@@ -261,7 +261,11 @@ static void launch_thread(const PlanIn& in, const PlanOut& out, uint64_t in_byte
   // 100 KB.  Larger tuples would leave one warp per block and two blocks per SM,
   // far too few threads to hide the walk's latency; those run unstaged, 128
   // threads per block with no shared memory, on the L1/L2 caches.
+#ifdef NBRM_NO_STAGING
+  const uint64_t avg = PLAN_SMEM;  // this unit's kernel always walks global memory
+#else
   const uint64_t avg = in_bytes / in.n + 48;
+#endif
   if (in.period > 1 && in.period <= 8) {  // threads that run together take one kind (see plan_kernel)
     if ((uint64_t)32 * in.period * avg <= PLAN_SMEM) {
       const uint32_t threads = 32 * in.period;
