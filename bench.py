@@ -464,6 +464,14 @@ def other_configs(pkg, wl, ctx):
     r = timed(lambda: ctx.profile_generate(profs, copy=False), 40)
     r["profiles_per_s"] = 500 / (r["p50_ms"] / 1e3)
     out["configs[3] profile-controller: 500 Profiles per call"] = r
+    # the tensorboard-controller's three objects for 10 000 Tensorboards
+    ctx.set_env({"TENSORBOARD_IMAGE": "tensorflow/tensorflow:2.5.1", "ISTIO_GATEWAY": "kubeflow/kubeflow-gateway",
+                 "ISTIO_HOST": "*"})
+    tbs = pkg.Docs([wl.dumps(wl.tensorboard_cr(rng, i)) for i in range(10000)], pinned=True)
+    r = timed(lambda: ctx.tensorboard_generate(tbs, None, 8, copy=False), 20)
+    r["tensorboards_per_s"] = 10000 / (r["p50_ms"] / 1e3)
+    out["tensorboard-controller (SURVEY 8 f4): 10 000 Tensorboards per call"] = r
+    ctx.set_env({})
     # configs[4] (restated): one culling pass over 100 000 Notebooks with their Jupyter answers
     rng = random.Random(19)
     cases = [wl.culling_case(rng, i, NOW) for i in range(20000)]

@@ -48,7 +48,10 @@ enum {
   NBRM_E_DENIED = 6,        /* admission.Denied, odh-notebook-controller/controllers/notebook_webhook.go:274 */
   NBRM_E_CONFLICT = 7,      /* PodDefault merge conflict, admission-webhook/main.go:671-679 */
   NBRM_E_LIMIT = 8,         /* a documented fixed limit of this library was exceeded */
-  NBRM_E_SELECTOR = 9       /* label selector conversion failed, admission-webhook/main.go:77-79 */
+  NBRM_E_SELECTOR = 9,      /* label selector conversion failed, admission-webhook/main.go:77-79 */
+  NBRM_E_ENV = 10           /* a required environment variable is not set (getEnvVariable,
+                             * tensorboard-controller/controllers/tensorboard_controller.go:535-541) or
+                             * RWO_PVC_SCHEDULING has a value rwoPVCScheduling :471-482 rejects */
 };
 
 /* The process environment and flags the reference reads while generating
@@ -74,6 +77,11 @@ typedef struct nbrm_env {
   const char* istio_ingress_gateway_principal;
   const char* kfp_ui_principal;
   const char* namespace_labels_json;
+  /* tensorboard-controller: TENSORBOARD_IMAGE (controllers/tensorboard_controller.go:172),
+   * RWO_PVC_SCHEDULING (:471-482).  It reads ISTIO_GATEWAY / ISTIO_HOST (:325,:330) too, and
+   * takes them as set, with no default: for nbrm_tensorboard_generate NULL means "not set". */
+  const char* tensorboard_image;
+  const char* rwo_pvc_scheduling;
 } nbrm_env;
 
 typedef struct nbrm_docs {
@@ -315,6 +323,19 @@ int nbrm_poddefault_mutate_resident(nbrm_ctx* ctx);
  * AuthorizationPolicy is recalled, not pinned by a reference test. */
 int nbrm_profile_generate(nbrm_ctx* ctx, const nbrm_docs* profiles, nbrm_out* out);
 int nbrm_profile_generate_resident(nbrm_ctx* ctx);
+
+/* ---- tensorboard-controller desired objects -----------------------------------
+ * Replaces, for a batch of Tensorboard CRs, generateDeployment / generateService /
+ * generateVirtualService and the three ctrl.SetControllerReference calls of
+ * TensorboardReconciler.Reconcile (tensorboard-controller/controllers/
+ * tensorboard_controller.go:67-160, :167-378).  node_names (may be NULL): per Tensorboard the
+ * node a running Pod mounts its ReadWriteOnce PVC on, as a JSON string ("" or an empty
+ * document: none) — what the PVC Get and the Pod List of the RWO_PVC_SCHEDULING path
+ * (:207-232, :427-468) lead to; used only when that variable is "true".  flags:
+ * NBRM_GEN_OWNER_REF.  Output: Deployment, Service, VirtualService per Tensorboard.
+ * status: NBRM_E_ENV when TENSORBOARD_IMAGE, ISTIO_GATEWAY or ISTIO_HOST is not set. */
+int nbrm_tensorboard_generate(nbrm_ctx* ctx, const nbrm_docs* tensorboards, const nbrm_docs* node_names,
+                              uint32_t flags, nbrm_out* out);
 
 /* ---- composing generators --------------------------------------------------
  * Run one generator on arbitrary slots: tuple i = document i of slot_a (and of

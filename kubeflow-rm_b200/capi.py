@@ -14,7 +14,7 @@ MUT_CREATE, MUT_CA_BUNDLE = 1, 2
 G_ODH_DECIDE = 9
 
 STATUS_NAMES = {0: "OK", 1: "E_PARSE", 2: "E_NO_CONTAINERS", 3: "E_SEGS", 4: "E_PORTS_EMPTY",
-                5: "E_NIL_REPLICAS", 6: "E_DENIED", 7: "E_CONFLICT", 8: "E_LIMIT", 9: "E_SELECTOR"}
+                5: "E_NIL_REPLICAS", 6: "E_DENIED", 7: "E_CONFLICT", 8: "E_LIMIT", 9: "E_SELECTOR", 10: "E_ENV"}
 
 
 class NbrmError(RuntimeError):
@@ -26,7 +26,7 @@ class _Env(C.Structure):
         "use_istio", "istio_gateway", "istio_host", "cluster_domain", "add_fsgroup",
         "controller_namespace", "oauth_proxy_image", "userid_header", "userid_prefix",
         "notebook_controller_principal", "istio_ingress_gateway_principal", "kfp_ui_principal",
-        "namespace_labels_json")]
+        "namespace_labels_json", "tensorboard_image", "rwo_pvc_scheduling")]
 
 
 class _Docs(C.Structure):
@@ -55,7 +55,8 @@ ENV_FIELDS = {"USE_ISTIO": "use_istio", "ISTIO_GATEWAY": "istio_gateway", "ISTIO
               "USERID_HEADER": "userid_header", "USERID_PREFIX": "userid_prefix",
               "NOTEBOOK_CONTROLLER_PRINCIPAL": "notebook_controller_principal",
               "ISTIO_INGRESS_GATEWAY_PRINCIPAL": "istio_ingress_gateway_principal",
-              "KFP_UI_PRINCIPAL": "kfp_ui_principal", "NAMESPACE_LABELS_JSON": "namespace_labels_json"}
+              "KFP_UI_PRINCIPAL": "kfp_ui_principal", "NAMESPACE_LABELS_JSON": "namespace_labels_json",
+              "TENSORBOARD_IMAGE": "tensorboard_image", "RWO_PVC_SCHEDULING": "rwo_pvc_scheduling"}
 
 
 def lib_path():
@@ -131,6 +132,7 @@ def load_library():
     lib.nbrm_download_wait.argtypes = [C.c_void_p, C.c_int, C.POINTER(_Out)]
     lib.nbrm_profile_generate.argtypes = [C.c_void_p, C.POINTER(_Docs), C.POINTER(_Out)]
     lib.nbrm_profile_generate_resident.argtypes = [C.c_void_p]
+    lib.nbrm_tensorboard_generate.argtypes = [C.c_void_p, C.POINTER(_Docs), C.POINTER(_Docs), C.c_uint32, C.POINTER(_Out)]
     lib.nbrm_scan_lengths_noalloc.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p,
                                               C.c_char_p, C.c_size_t]
     _lib = lib
@@ -431,6 +433,15 @@ class Context:
     def download_wait(self, lane, copy=True):
         o = _Out()
         self._check(self.lib.nbrm_download_wait(self.h, lane, C.byref(o)))
+        return Result(o, copy)
+
+    # --- tensorboard-controller objects
+    def tensorboard_generate(self, tensorboards, node_names=None, flags=0, copy=True):
+        """Deployment, Service, VirtualService per Tensorboard CR (include/nbrm.h)."""
+        d, o = tensorboards.c_struct(), _Out()
+        nn = node_names.c_struct() if node_names is not None else None
+        self._check(self.lib.nbrm_tensorboard_generate(self.h, C.byref(d), C.byref(nn) if nn is not None else None,
+                                                       flags, C.byref(o)))
         return Result(o, copy)
 
     # --- profile-controller objects

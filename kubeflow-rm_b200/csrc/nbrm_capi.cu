@@ -1115,6 +1115,18 @@ int nbrm_tape_dump(nbrm_ctx* c, int slot, uint32_t cap, uint64_t* entries, uint3
   return 0;
 }
 
+int nbrm_tensorboard_generate(nbrm_ctx* c, const nbrm_docs* tensorboards, const nbrm_docs* node_names,
+                              uint32_t flags, nbrm_out* out) {
+  if (!c || !out) return -2;
+  if (int r = nbrm_upload(c, 0, tensorboards)) return r;
+  if (node_names) {
+    if (node_names->n != tensorboards->n) return fail_msg(c, "node_names must hold one document per Tensorboard");
+    if (int r = nbrm_upload(c, 1, node_names)) return r;
+  }
+  if (int r = run_generator(c, GEN_ID_TENSORBOARD, {0, node_names ? 1 : -1, -1}, flags, nullptr, 0)) return r;
+  return nbrm_download(c, out);
+}
+
 int nbrm_profile_generate_resident(nbrm_ctx* c) {
   if (!c) return -2;
   return run_generator(c, GEN_ID_PROFILE, {0, -1, -1}, 0, nullptr, 0);

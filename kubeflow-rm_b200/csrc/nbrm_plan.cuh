@@ -31,6 +31,7 @@ enum Err : uint32_t {
   E_CONFLICT = 7,       // PodDefault merge conflict (admission-webhook/main.go:671-679)
   E_LIMIT = 8,          // a documented fixed limit of this implementation was exceeded
   E_SELECTOR = 9,       // a PodDefault's label selector does not convert (admission-webhook/main.go:77-79)
+  E_ENV = 10,           // an environment variable the reference requires is not set, or has a value it rejects
 };
 
 struct Seg {
@@ -217,8 +218,11 @@ struct EnvLits {
   PoolSpan prof_prefix;     // userid prefix (unquoted, escaped)
   PoolSpan prof_igw, prof_kfp, prof_nbc;  // principals (quoted)
   PoolSpan prof_ns_labels;  // members of the Namespace's labels map, rendered by the host
+  // tensorboard-controller (tensorboard_controller.go:172,:325,:330): as set, no defaults (quoted)
+  PoolSpan tb_image, tb_gateway, tb_host;
   uint32_t add_fsgroup; // ADD_FSGROUP unset or "true"  (notebook_controller.go:475)
   uint32_t use_istio;   // USE_ISTIO == "true"          (:213)
+  uint32_t tb_env;      // TbEnvBits (nbrm_tb.cuh): which of those are set; RWO_PVC_SCHEDULING on / invalid (:471-482)
 };
 
 // Separator-aware writer for the members of one JSON object or array.

@@ -107,6 +107,21 @@ inline void build_pool_host(const nbrm_env* env, std::string& pool, EnvLits& L) 
   L.prof_nbc = add("\"" + json_escape(get(env ? env->notebook_controller_principal : nullptr,
                        "cluster.local/ns/kubeflow/sa/notebook-controller-service-account")) + "\"");
   L.prof_ns_labels = add(render_namespace_labels(env ? env->namespace_labels_json : nullptr));
+  // tensorboard-controller: os.LookupEnv, a variable that is set but empty is used as it is
+  // (tensorboard_controller.go:535-541); RWO_PVC_SCHEDULING :471-482
+  auto quoted = [&](const char* v) { return add("\"" + json_escape(v ? v : "") + "\""); };
+  L.tb_image = quoted(env ? env->tensorboard_image : nullptr);
+  L.tb_gateway = quoted(env ? env->istio_gateway : nullptr);
+  L.tb_host = quoted(env ? env->istio_host : nullptr);
+  L.tb_env = 0;
+  if (env && env->tensorboard_image) L.tb_env |= 1u;
+  if (env && env->istio_gateway) L.tb_env |= 2u;
+  if (env && env->istio_host) L.tb_env |= 4u;
+  if (env && env->rwo_pvc_scheduling) {
+    const char* r = env->rwo_pvc_scheduling;
+    if (!strcmp(r, "true") || !strcmp(r, "True") || !strcmp(r, "TRUE")) L.tb_env |= 8u;
+    else if (strcmp(r, "false") && strcmp(r, "False") && strcmp(r, "FALSE")) L.tb_env |= 16u;
+  }
   // ADD_FSGROUP: add the fsGroup when unset or exactly "true" (:475)
   L.add_fsgroup = (!env || !env->add_fsgroup || strcmp(env->add_fsgroup, "true") == 0) ? 1u : 0u;
   L.use_istio = (env && env->use_istio && strcmp(env->use_istio, "true") == 0) ? 1u : 0u;

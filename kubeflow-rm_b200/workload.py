@@ -657,3 +657,43 @@ def profile_cr(rng, i):
     elif r < 0.26:
         del p["metadata"]["uid"]
     return p
+
+
+# ---- tensorboard-controller: Tensorboard CRs (tensorboard-controller/api/v1alpha1/tensorboard_types.go)
+TENSORBOARD_PATHS = ["pvc://logs-pvc/run1", "pvc://logs-pvc/", "pvc://logs-pvc", "pvc://", "pvc:///x", "pvc://a/b/c/d",
+                     "gs://bucket/logs", "s3://bucket/logs", "/cns/cell/home/logs", "/some/legacy/path", "", "relative",
+                     "pvc://na\"me/sub\\dir", "gs://b/\u00e9t\u00e9", "pvc://p/\ttab", "pvc:/notpvc", "PVC://upper/x"]
+
+
+def tensorboard_cr(rng, i):
+    """One Tensorboard CR: every kind of log path the controller tells apart, labels with and
+    without an "app" key, sometimes no namespace / null labels / no spec."""
+    labels = {}
+    if rng.random() < 0.7:
+        for k in rng.sample(["app", "team", "access-ml-pipeline", "a/b", "x\"y"], rng.randint(0, 4)):
+            labels[k] = rng.choice(["true", "v", "", "tb-%d" % i])
+    meta = {"name": "tb-%d" % i, "namespace": rng.choice(["user-ns", "kubeflow-user-example-com", "n%d" % (i % 7)]),
+            "uid": "3c1f-%04d" % i}
+    if labels or rng.random() < 0.2:
+        meta["labels"] = labels
+    if rng.random() < 0.1:
+        del meta["namespace"]
+    if rng.random() < 0.05:
+        meta["labels"] = None
+    tb = {"apiVersion": "tensorboard.kubeflow.org/v1alpha1", "kind": "Tensorboard", "metadata": meta,
+          "spec": {"logspath": rng.choice(TENSORBOARD_PATHS)}}
+    if rng.random() < 0.3:
+        tb["status"] = {"conditions": [{"deploymentState": "Available"}], "readyReplicas": 1}
+    if rng.random() < 0.03:
+        tb["spec"] = {}
+    return tb
+
+
+def tensorboard_node(rng):
+    """The node-name side input of one Tensorboard: absent, empty, or a JSON string."""
+    r = rng.random()
+    if r < 0.4:
+        return b""
+    if r < 0.5:
+        return b'""'
+    return json.dumps(rng.choice(["node-1", "ip-10-0-0-1.ec2.internal", "n\"q"])).encode()

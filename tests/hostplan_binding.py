@@ -7,6 +7,7 @@ import numpy as np
 GEN_NBC, GEN_ODH, GEN_COPY, GEN_STATUS, GEN_CULL, GEN_MUTATE, GEN_GUARD, GEN_PD, GEN_PROFILE = 0, 1, 2, 3, 4, 5, 6, 7, 8
 GEN_ODH_DECIDE = 9
 GEN_DIFF, GEN_REVIEW_OPEN, GEN_REVIEW_CLOSE = 10, 11, 12
+GEN_TENSORBOARD = 14
 
 
 def _pack(docs_list):
@@ -101,6 +102,9 @@ class HostPlan:
         if not desired_list:
             return [], np.zeros(0, dtype=np.uint32), np.zeros(0, dtype=np.uint32)
         return self.run(GEN_ODH_DECIDE, [desired_list, found_list], want_result=True)
+
+    def tensorboard(self, tensorboards, node_names=None, env=None, flags=0):
+        return self.run(GEN_TENSORBOARD, [tensorboards, node_names], env, flags=flags)
 
     def profile(self, profiles, env=None):
         return self.run(GEN_PROFILE, [profiles], env)
