@@ -383,7 +383,7 @@ def run_reference(args):
     v = n * args.steps / dt
     sample = ("%d Notebooks/step of the same workload (found objects as an API server returns them), JSON in -> "
               "oracle full pass -> JSON out, %d processes forked after the items were built" % (n, cores))
-    print(json.dumps({
+    emit_line(json.dumps({
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
@@ -502,7 +502,27 @@ def other_configs(pkg, wl, ctx):
     return out
 
 
+_REAL_STDOUT = None
+
+
+def quiet_stdout():
+    """stdout carries ONE JSON line: whatever libraries print there while the bench runs (NCCL's
+    version banner, for one) goes to stderr instead."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
+
+
+def emit_line(text):
+    out = _REAL_STDOUT or sys.stdout
+    out.write(text + "\n")
+    out.flush()
+
+
 def main():
+    quiet_stdout()
     args = parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -697,7 +717,7 @@ def main():
     except Exception as e:          # the headline must not die with a side measurement
         others = {"error": repr(e)}
 
-    print(json.dumps({
+    emit_line(json.dumps({
         "metric": METRIC, "value": results[variants[0]]["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": head["ms"] / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
