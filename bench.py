@@ -472,6 +472,17 @@ def other_configs(pkg, wl, ctx):
     r["tensorboards_per_s"] = 10000 / (r["p50_ms"] / 1e3)
     out["tensorboard-controller (SURVEY 8 f4): 10 000 Tensorboards per call"] = r
     ctx.set_env({})
+    # what 10 000 PVCViewer reconciles write, a third of the objects found and updated
+    from oracle import pvcviewer as opv
+    vs_ = [wl.pvcviewer_cr(rng, i) for i in range(10000)]
+    fo_ = []
+    for v in vs_:
+        fo_ += [wl.pvcviewer_found(rng, o, v) for o in opv.viewer_objects(v, {})]
+    vd = pkg.Docs([wl.dumps(v) for v in vs_], pinned=True)
+    fd = pkg.Docs([b"" if f is None else wl.dumps(f) for f in fo_], pinned=True)
+    r = timed(lambda: ctx.pvcviewer_reconcile(vd, fd, None, copy=False), 20)
+    r["viewers_per_s"] = 10000 / (r["p50_ms"] / 1e3)
+    out["pvcviewer-controller (SURVEY 8 f4): 10 000 PVCViewers per call"] = r
     # configs[4] (restated): one culling pass over 100 000 Notebooks with their Jupyter answers
     rng = random.Random(19)
     cases = [wl.culling_case(rng, i, NOW) for i in range(20000)]

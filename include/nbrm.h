@@ -82,6 +82,9 @@ typedef struct nbrm_env {
    * takes them as set, with no default: for nbrm_tensorboard_generate NULL means "not set". */
   const char* tensorboard_image;
   const char* rwo_pvc_scheduling;
+  /* pvcviewer-controller webhook: the PodSpec of the defaults file DEFAULT_POD_SPEC_PATH names
+   * (api/v1alpha1/pvcviewer_webhook.go:78-91), as JSON; NULL or "" = the variable is not set. */
+  const char* pvcviewer_default_podspec_json;
 } nbrm_env;
 
 typedef struct nbrm_docs {
@@ -336,6 +339,27 @@ int nbrm_profile_generate_resident(nbrm_ctx* ctx);
  * status: NBRM_E_ENV when TENSORBOARD_IMAGE, ISTIO_GATEWAY or ISTIO_HOST is not set. */
 int nbrm_tensorboard_generate(nbrm_ctx* ctx, const nbrm_docs* tensorboards, const nbrm_docs* node_names,
                               uint32_t flags, nbrm_out* out);
+
+/* ---- pvcviewer-controller: what a reconcile writes ------------------------------
+ * Replaces, for a batch of PVCViewer CRs, the bodies reconcileDeployment / reconcileService /
+ * reconcileVirtualService build between their Get and their Create or Update
+ * (pvcviewer-controller/controllers/pvcviewer_controller.go:149-336), ownerReference included
+ * (SetControllerReference :198,:240,:326).  found (may be NULL: every Get was NotFound): 3 n
+ * documents, 3 i + k = the Deployment / Service / VirtualService the Get returned for viewer i,
+ * empty = NotFound; a found object keeps everything the reconciler does not overwrite.
+ * node_names (may be NULL): per viewer the node its ReadWriteOnce PVC is mounted on, as a JSON
+ * string — the outcome of generateAffinity's PVC Get and Pod List (:372-443); used for
+ * rwoScheduling viewers whose Deployment is being created (:170).  Output: 3 objects per
+ * viewer; Service and VirtualService have length 0 when spec.networking is the zero value
+ * (:212,:253).  status: NBRM_E_CONFLICT when a found object has another controller. */
+int nbrm_pvcviewer_reconcile(nbrm_ctx* ctx, const nbrm_docs* viewers, const nbrm_docs* found,
+                             const nbrm_docs* node_names, nbrm_out* out);
+
+/* The viewer's defaulting and validating webhook: (*PVCViewer).Default and validate
+ * (pvcviewer-controller/api/v1alpha1/pvcviewer_webhook.go:70-146, :153-178).  Output: one object
+ * per viewer, the viewer as Default leaves it.  result: 0 = valid, 1 = "PVC name must be
+ * specified", 2 = "PodSpec must be specified", 3 = "PVC <pvc> must be used in the podSpec". */
+int nbrm_pvcviewer_webhook(nbrm_ctx* ctx, const nbrm_docs* viewers, nbrm_out* out);
 
 /* ---- composing generators --------------------------------------------------
  * Run one generator on arbitrary slots: tuple i = document i of slot_a (and of

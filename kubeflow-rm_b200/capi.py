@@ -26,7 +26,7 @@ class _Env(C.Structure):
         "use_istio", "istio_gateway", "istio_host", "cluster_domain", "add_fsgroup",
         "controller_namespace", "oauth_proxy_image", "userid_header", "userid_prefix",
         "notebook_controller_principal", "istio_ingress_gateway_principal", "kfp_ui_principal",
-        "namespace_labels_json", "tensorboard_image", "rwo_pvc_scheduling")]
+        "namespace_labels_json", "tensorboard_image", "rwo_pvc_scheduling", "pvcviewer_default_podspec_json")]
 
 
 class _Docs(C.Structure):
@@ -56,7 +56,8 @@ ENV_FIELDS = {"USE_ISTIO": "use_istio", "ISTIO_GATEWAY": "istio_gateway", "ISTIO
               "NOTEBOOK_CONTROLLER_PRINCIPAL": "notebook_controller_principal",
               "ISTIO_INGRESS_GATEWAY_PRINCIPAL": "istio_ingress_gateway_principal",
               "KFP_UI_PRINCIPAL": "kfp_ui_principal", "NAMESPACE_LABELS_JSON": "namespace_labels_json",
-              "TENSORBOARD_IMAGE": "tensorboard_image", "RWO_PVC_SCHEDULING": "rwo_pvc_scheduling"}
+              "TENSORBOARD_IMAGE": "tensorboard_image", "RWO_PVC_SCHEDULING": "rwo_pvc_scheduling",
+              "PVCVIEWER_DEFAULT_PODSPEC_JSON": "pvcviewer_default_podspec_json"}
 
 
 def lib_path():
@@ -132,6 +133,8 @@ def load_library():
     lib.nbrm_download_wait.argtypes = [C.c_void_p, C.c_int, C.POINTER(_Out)]
     lib.nbrm_profile_generate.argtypes = [C.c_void_p, C.POINTER(_Docs), C.POINTER(_Out)]
     lib.nbrm_profile_generate_resident.argtypes = [C.c_void_p]
+    lib.nbrm_pvcviewer_webhook.argtypes = [C.c_void_p, C.POINTER(_Docs), C.POINTER(_Out)]
+    lib.nbrm_pvcviewer_reconcile.argtypes = [C.c_void_p, C.POINTER(_Docs), C.POINTER(_Docs), C.POINTER(_Docs), C.POINTER(_Out)]
     lib.nbrm_tensorboard_generate.argtypes = [C.c_void_p, C.POINTER(_Docs), C.POINTER(_Docs), C.c_uint32, C.POINTER(_Out)]
     lib.nbrm_scan_lengths_noalloc.argtypes = [C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p,
                                               C.c_char_p, C.c_size_t]
@@ -433,6 +436,22 @@ class Context:
     def download_wait(self, lane, copy=True):
         o = _Out()
         self._check(self.lib.nbrm_download_wait(self.h, lane, C.byref(o)))
+        return Result(o, copy)
+
+    # --- pvcviewer-controller: the bodies a reconcile writes
+    def pvcviewer_reconcile(self, viewers, found=None, node_names=None, copy=True):
+        """Deployment, Service, VirtualService per PVCViewer (include/nbrm.h); found: 3 per viewer."""
+        d, o = viewers.c_struct(), _Out()
+        f = found.c_struct() if found is not None else None
+        nn = node_names.c_struct() if node_names is not None else None
+        self._check(self.lib.nbrm_pvcviewer_reconcile(self.h, C.byref(d), C.byref(f) if f is not None else None,
+                                                      C.byref(nn) if nn is not None else None, C.byref(o)))
+        return Result(o, copy)
+
+    def pvcviewer_webhook(self, viewers, copy=True):
+        """Default + validate of the viewer's webhook: defaulted viewers, result = validation code."""
+        d, o = viewers.c_struct(), _Out()
+        self._check(self.lib.nbrm_pvcviewer_webhook(self.h, C.byref(d), C.byref(o)))
         return Result(o, copy)
 
     # --- tensorboard-controller objects

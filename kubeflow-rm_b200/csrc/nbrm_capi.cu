@@ -1127,6 +1127,31 @@ int nbrm_tensorboard_generate(nbrm_ctx* c, const nbrm_docs* tensorboards, const 
   return nbrm_download(c, out);
 }
 
+int nbrm_pvcviewer_reconcile(nbrm_ctx* c, const nbrm_docs* viewers, const nbrm_docs* found, const nbrm_docs* node_names,
+                             nbrm_out* out) {
+  if (!c || !out || !viewers) return -2;
+  if (found && found->n != 3 * viewers->n) return fail_msg(c, "found must hold three documents per PVCViewer");
+  if (node_names && node_names->n != viewers->n) return fail_msg(c, "node_names must hold one document per PVCViewer");
+  if (int r = nbrm_upload(c, 0, viewers)) return r;
+  nbrm_docs none;
+  const uint64_t zero = 0;
+  none.data = "";
+  none.off = &zero;
+  none.n = 0;
+  if (int r = nbrm_upload(c, 1, found ? found : &none)) return r;  // the shared arena: empty = every Get NotFound
+  if (node_names)
+    if (int r = nbrm_upload(c, 2, node_names)) return r;
+  if (int r = run_generator(c, GEN_ID_PVCVIEWER, {0, 1, node_names ? 2 : -1}, 0, nullptr, 0)) return r;
+  return nbrm_download(c, out);
+}
+
+int nbrm_pvcviewer_webhook(nbrm_ctx* c, const nbrm_docs* viewers, nbrm_out* out) {
+  if (!c || !out) return -2;
+  if (int r = nbrm_upload(c, 0, viewers)) return r;
+  if (int r = run_generator(c, GEN_ID_PVCVIEWER_DEFAULT, {0, -1, -1}, 0, nullptr, 0)) return r;
+  return nbrm_download(c, out);
+}
+
 int nbrm_profile_generate_resident(nbrm_ctx* c) {
   if (!c) return -2;
   return run_generator(c, GEN_ID_PROFILE, {0, -1, -1}, 0, nullptr, 0);

@@ -220,8 +220,11 @@ struct EnvLits {
   PoolSpan prof_ns_labels;  // members of the Namespace's labels map, rendered by the host
   // tensorboard-controller (tensorboard_controller.go:172,:325,:330): as set, no defaults (quoted)
   PoolSpan tb_image, tb_gateway, tb_host;
+  // pvcviewer webhook: the defaults file's PodSpec (pvcviewer_webhook.go:78-91), split by the host
+  PoolSpan pv_default_rest, pv_default_volumes;
   uint32_t add_fsgroup; // ADD_FSGROUP unset or "true"  (notebook_controller.go:475)
   uint32_t use_istio;   // USE_ISTIO == "true"          (:213)
+  uint32_t pv_default_set;  // a defaults file with a non-zero PodSpec was given
   uint32_t tb_env;      // TbEnvBits (nbrm_tb.cuh): which of those are set; RWO_PVC_SCHEDULING on / invalid (:471-482)
 };
 

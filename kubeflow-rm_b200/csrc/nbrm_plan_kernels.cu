@@ -36,6 +36,10 @@ void launch_plan_convert(const PlanIn&, const PlanOut&, uint64_t, cudaStream_t);
 void gen_shape_convert(uint32_t*, uint32_t*, bool*);
 void launch_plan_tensorboard(const PlanIn&, const PlanOut&, uint64_t, cudaStream_t);
 void gen_shape_tensorboard(uint32_t*, uint32_t*, bool*);
+void launch_plan_pvcviewer(const PlanIn&, const PlanOut&, uint64_t, cudaStream_t);
+void gen_shape_pvcviewer(uint32_t*, uint32_t*, bool*);
+void launch_plan_pvcviewerdefault(const PlanIn&, const PlanOut&, uint64_t, cudaStream_t);
+void gen_shape_pvcviewerdefault(uint32_t*, uint32_t*, bool*);
 
 void launch_plan(int gen, const PlanIn& in, const PlanOut& out, uint64_t in_bytes, cudaStream_t st) {
   switch (gen) {
@@ -54,6 +58,8 @@ void launch_plan(int gen, const PlanIn& in, const PlanOut& out, uint64_t in_byte
     case GEN_ID_REVIEW_CLOSE: launch_plan_reviewclose(in, out, in_bytes, st); break;
     case GEN_ID_CONVERT: launch_plan_convert(in, out, in_bytes, st); break;
     case GEN_ID_TENSORBOARD: launch_plan_tensorboard(in, out, in_bytes, st); break;
+    case GEN_ID_PVCVIEWER: launch_plan_pvcviewer(in, out, in_bytes, st); break;
+    case GEN_ID_PVCVIEWER_DEFAULT: launch_plan_pvcviewerdefault(in, out, in_bytes, st); break;
   }
 }
 
@@ -74,6 +80,8 @@ static bool shape_of(int gen, uint32_t* nobj, uint32_t* cap, bool* shared1) {
     case GEN_ID_REVIEW_CLOSE: gen_shape_reviewclose(nobj, cap, shared1); return true;
     case GEN_ID_CONVERT: gen_shape_convert(nobj, cap, shared1); return true;
     case GEN_ID_TENSORBOARD: gen_shape_tensorboard(nobj, cap, shared1); return true;
+    case GEN_ID_PVCVIEWER: gen_shape_pvcviewer(nobj, cap, shared1); return true;
+    case GEN_ID_PVCVIEWER_DEFAULT: gen_shape_pvcviewerdefault(nobj, cap, shared1); return true;
   }
   *nobj = 0;
   *cap = 0;

@@ -122,6 +122,36 @@ inline void build_pool_host(const nbrm_env* env, std::string& pool, EnvLits& L) 
     if (!strcmp(r, "true") || !strcmp(r, "True") || !strcmp(r, "TRUE")) L.tb_env |= 8u;
     else if (strcmp(r, "false") && strcmp(r, "False") && strcmp(r, "FALSE")) L.tb_env |= 16u;
   }
+  // pvcviewer webhook: DEFAULT_POD_SPEC_PATH's PodSpec as JSON; the members other than `volumes`
+  // and the items of `volumes` go to the pool separately because Default appends a volume
+  // (pvcviewer_webhook.go:135-143)
+  {
+    std::string rest, vols;
+    bool set = false;
+    const char* js = env ? env->pvcviewer_default_podspec_json : nullptr;
+    if (js && *js) {
+      Doc d;
+      d.p = js;
+      d.n = (uint32_t)strlen(js);
+      ObjIter it(d, root(d));
+      Member mem;
+      while (it.next(d, mem)) {
+        if (!is_null(d, mem.val)) set = true;
+        if (str_eq(d, mem.key, "volumes")) {
+          if (is_array(d, mem.val) && mem.val.len > 2) vols.assign(d.p + mem.val.off + 1, mem.val.len - 2);
+        } else {
+          rest += (rest.empty() ? "" : ",") + std::string(d.p + mem.all.off, mem.all.len);
+        }
+      }
+      if (!set) {  // DeepEqual(defaultPodSpec, PodSpec{}): the built-in default is used
+        rest.clear();
+        vols.clear();
+      }
+    }
+    L.pv_default_rest = add(rest);
+    L.pv_default_volumes = add(vols);
+    L.pv_default_set = set ? 1u : 0u;
+  }
   // ADD_FSGROUP: add the fsGroup when unset or exactly "true" (:475)
   L.add_fsgroup = (!env || !env->add_fsgroup || strcmp(env->add_fsgroup, "true") == 0) ? 1u : 0u;
   L.use_istio = (env && env->use_istio && strcmp(env->use_istio, "true") == 0) ? 1u : 0u;

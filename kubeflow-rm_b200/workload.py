@@ -697,3 +697,74 @@ def tensorboard_node(rng):
     if r < 0.5:
         return b'""'
     return json.dumps(rng.choice(["node-1", "ip-10-0-0-1.ec2.internal", "n\"q"])).encode()
+
+
+# ---- pvcviewer-controller: PVCViewer CRs (pvcviewer-controller/api/v1alpha1/pvcviewer_types.go)
+def pvcviewer_cr(rng, i):
+    """One PVCViewer: with and without networking (zero value: no Service / VirtualService),
+    a pod spec of its own or the webhook's default shape, rwoScheduling on and off."""
+    name = "viewer-%d" % i
+    meta = {"name": name, "namespace": rng.choice(["user-ns", "kubeflow-user-example-com", "n%d" % (i % 5)]),
+            "uid": "7a2e-%04d" % i}
+    if rng.random() < 0.05:
+        del meta["namespace"]
+    pod = {"containers": [{"name": "pvcviewer", "image": rng.choice(["filebrowser/filebrowser:latest", "img\"q:1"]),
+                           "ports": [{"containerPort": 8080, "protocol": "TCP"}],
+                           "env": [{"name": "FB_PORT", "value": "8080"}], "workingDir": "/data",
+                           "volumeMounts": [{"name": "viewer-volume", "mountPath": "/data"}]}],
+           "volumes": [{"name": "viewer-volume", "persistentVolumeClaim": {"claimName": "pvc-%d" % i}}]}
+    if rng.random() < 0.3:
+        pod["affinity"] = {"podAffinity": {}}
+    if rng.random() < 0.3:
+        pod["securityContext"] = {"runAsUser": 1234}
+    spec = {"pvc": "pvc-%d" % i, "podSpec": pod, "rwoScheduling": rng.random() < 0.5}
+    r = rng.random()
+    if r < 0.6:
+        spec["networking"] = {"targetPort": rng.choice([8080, "http", 0]), "basePrefix": rng.choice(["/pvcviewer", "", "/x\"y"]),
+                              "rewrite": rng.choice(["/", ""]), "timeout": rng.choice(["30s", ""])}
+        if rng.random() < 0.3:
+            del spec["networking"]["rewrite"]
+            del spec["networking"]["timeout"]
+    elif r < 0.75:
+        spec["networking"] = {"targetPort": 0, "basePrefix": "", "rewrite": ""}     # the zero value, spelled out
+    elif r < 0.8:
+        spec["networking"] = None
+    if rng.random() < 0.05:
+        del spec["podSpec"]
+    return {"apiVersion": "kubeflow.org/v1alpha1", "kind": "PVCViewer", "metadata": meta, "spec": spec}
+
+
+def pvcviewer_found(rng, obj, viewer):
+    """What a Get returns for an object the controller wrote earlier: sometimes NotFound (None),
+    else the object with what an API server and other actors add, sometimes drifted, sometimes
+    owned by someone else."""
+    if obj is None or rng.random() < 0.35:
+        return None
+    f = json.loads(json.dumps(obj))
+    f["metadata"].update({"resourceVersion": str(rng.randint(1, 99999)), "generation": 2,
+                          "creationTimestamp": "2026-11-07T00:00:00Z"})
+    if rng.random() < 0.5:
+        f["metadata"]["labels"] = dict(f["metadata"].get("labels") or {}, extra="x")
+    f["status"] = {"observedGeneration": 2}
+    spec = f.setdefault("spec", {})
+    if f.get("kind") == "Deployment":
+        spec.update({"replicas": rng.choice([0, 1, 2]), "revisionHistoryLimit": 10, "strategy": {"type": "RollingUpdate"}})
+        if rng.random() < 0.5:
+            spec["template"]["spec"]["affinity"] = {"nodeAffinity": {"requiredDuringSchedulingIgnoredDuringExecution": {"nodeSelectorTerms": []}}}
+        elif rng.random() < 0.3:
+            spec["template"]["spec"].pop("affinity", None)
+    elif f.get("kind") == "Service":
+        spec.update({"clusterIP": "10.0.0.%d" % rng.randint(1, 250), "sessionAffinity": "None", "type": "NodePort"})
+    r = rng.random()
+    refs = f["metadata"].get("ownerReferences") or []
+    if r < 0.15:
+        f["metadata"].pop("ownerReferences", None)
+    elif r < 0.3:
+        f["metadata"]["ownerReferences"] = [{"apiVersion": "v1", "kind": "ConfigMap", "name": "other", "uid": "u-other"}] + refs
+    elif r < 0.36:
+        f["metadata"]["ownerReferences"] = [{"apiVersion": "apps/v1", "kind": "ReplicaSet", "name": "rs", "uid": "u-rs",
+                                             "controller": True}]
+    elif r < 0.45 and refs:
+        refs[0]["blockOwnerDeletion"] = False      # the same owner, to be replaced in place
+        f["metadata"]["ownerReferences"] = refs + [{"apiVersion": "v1", "kind": "Secret", "name": "s", "uid": "u-s"}]
+    return f

@@ -202,6 +202,19 @@ int main() {
           }
         }
       }
+      // load8: up to eight bytes from any alignment
+      for (uint32_t o = 0; o + 8 <= text.size() && o < 24; ++o)
+        for (uint32_t nb = 1; nb <= 8; ++nb) {
+          uint64_t want = 0;
+          memcpy(&want, p + o, nb);
+          uint64_t got = wide::load8(p + o, nb);
+          if (nb < 8) got &= (1ull << (8 * nb)) - 1;
+          ++cases;
+          if (want != got) {
+            printf("load8 differs at %u nb %u align %u\n", o, nb, align);
+            return 1;
+          }
+        }
       // bytes_equal against the obvious loop, both operands at every alignment
       for (uint32_t balign = 0; balign < 8; ++balign) {
         char* q = base + 32768 + balign;

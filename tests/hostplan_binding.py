@@ -8,6 +8,8 @@ GEN_NBC, GEN_ODH, GEN_COPY, GEN_STATUS, GEN_CULL, GEN_MUTATE, GEN_GUARD, GEN_PD,
 GEN_ODH_DECIDE = 9
 GEN_DIFF, GEN_REVIEW_OPEN, GEN_REVIEW_CLOSE = 10, 11, 12
 GEN_TENSORBOARD = 14
+GEN_PVCVIEWER = 15
+GEN_PVCVIEWER_DEFAULT = 16
 
 
 def _pack(docs_list):
@@ -102,6 +104,12 @@ class HostPlan:
         if not desired_list:
             return [], np.zeros(0, dtype=np.uint32), np.zeros(0, dtype=np.uint32)
         return self.run(GEN_ODH_DECIDE, [desired_list, found_list], want_result=True)
+
+    def pvcviewer(self, viewers, found=None, node_names=None, env=None):
+        return self.run(GEN_PVCVIEWER, [viewers, found if found is not None else [], node_names], env, shared1=True)
+
+    def pvcviewer_webhook(self, viewers, env=None):
+        return self.run(GEN_PVCVIEWER_DEFAULT, [viewers], env, want_result=True)
 
     def tensorboard(self, tensorboards, node_names=None, env=None, flags=0):
         return self.run(GEN_TENSORBOARD, [tensorboards, node_names], env, flags=flags)
