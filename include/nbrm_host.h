@@ -50,6 +50,25 @@ nbrm_odh_reconciler* nbrm_odh_reconciler_new(nbrm_store* s, nbrm_ctx* ctx, int r
 void nbrm_odh_reconciler_free(nbrm_odh_reconciler* r);
 int nbrm_odh_reconciler_reconcile(nbrm_odh_reconciler* r, const char* keys, uint64_t* stats, double* slept_seconds);
 
+/* ProfileReconciler (profile-controller/controllers/profile_controller.go:105-334): the eight
+ * desired objects of every Profile from one GPU pass, then per Profile what the reference does
+ * object by object against the store: the Namespace (create, or label update when the `owner`
+ * annotation is the Profile's owner, else a `Failed` condition on the Profile and nothing more),
+ * AuthorizationPolicy, ServiceAccounts, RoleBindings, ResourceQuota (created, brought back in
+ * line, or deleted when the Profile no longer asks for one), PatchDefaultPluginSpec (which
+ * writes the Profile every time), the finalizer.  names: Profile names, one per line.
+ * workload_identity: the --workload-identity flag ("" = off); default_labels_json: the
+ * namespace-labels file as JSON (the context's nbrm_env.namespace_labels_json must hold the
+ * same text).  stats[13] = keys, reconciled, not_found, creates, updates, deletes, rejected,
+ * profile_writes, finalizers_added, finalizers_removed, plugins_applied, plugins_revoked,
+ * errors.  Plugins are C++ callbacks (host/profile_reconciler.h); through this C entry they
+ * are counted and do nothing.  Returns the number of Profiles that ended in an error. */
+typedef struct nbrm_profile_reconciler nbrm_profile_reconciler;
+nbrm_profile_reconciler* nbrm_profile_reconciler_new(nbrm_store* s, nbrm_ctx* ctx, const char* workload_identity,
+                                                     const char* default_labels_json);
+void nbrm_profile_reconciler_free(nbrm_profile_reconciler* r);
+int nbrm_profile_reconciler_reconcile(nbrm_profile_reconciler* r, const char* names, uint64_t* stats);
+
 /* The work queue between watch events and the reconcilers (controller-runtime's workqueue
  * semantics; kubeflow-rm_b200/host/workqueue.h): a key waits at most once, is never handed
  * out while it is being reconciled, comes back after `seconds` (ctrl.Result{RequeueAfter},

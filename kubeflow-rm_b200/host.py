@@ -1,6 +1,7 @@
 """ctypes binding of include/nbrm_host.h (libnbrm_host.so): the C++ object store
 and NotebookReconciler."""
 import ctypes as C
+import json
 import os
 
 from . import capi
@@ -163,6 +164,34 @@ class OpenshiftNotebookReconciler:
     def close(self):
         if self.h:
             self.lib.nbrm_odh_reconciler_free(self.h)
+            self.h = None
+
+
+PROFILE_STAT_NAMES = ("keys", "reconciled", "not_found", "creates", "updates", "deletes", "rejected", "profile_writes",
+                      "finalizers_added", "finalizers_removed", "plugins_applied", "plugins_revoked", "errors")
+
+
+class ProfileReconciler:
+    """ProfileReconciler (profile-controller/controllers/profile_controller.go:105-334)."""
+
+    def __init__(self, store, ctx, workload_identity="", default_labels=None):
+        self.lib = load_host_library()
+        self.store, self.ctx = store, ctx
+        self.lib.nbrm_profile_reconciler_new.restype = C.c_void_p
+        self.lib.nbrm_profile_reconciler_new.argtypes = [C.c_void_p, C.c_void_p, C.c_char_p, C.c_char_p]
+        self.lib.nbrm_profile_reconciler_reconcile.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p]
+        self.lib.nbrm_profile_reconciler_free.argtypes = [C.c_void_p]
+        labels = None if default_labels is None else json.dumps(default_labels).encode()
+        self.h = self.lib.nbrm_profile_reconciler_new(store.h, ctx.h, workload_identity.encode(), labels)
+
+    def reconcile(self, names):
+        st = (C.c_uint64 * 13)()
+        rc = self.lib.nbrm_profile_reconciler_reconcile(self.h, "\n".join(names).encode(), st)
+        return rc, dict(zip(PROFILE_STAT_NAMES, list(st)))
+
+    def close(self):
+        if self.h:
+            self.lib.nbrm_profile_reconciler_free(self.h)
             self.h = None
 
 

@@ -5,6 +5,7 @@
 #include "../../include/nbrm_host.h"
 #include "notebook_reconciler.h"
 #include "odh_reconciler.h"
+#include "profile_reconciler.h"
 #include "workqueue.h"
 
 using namespace nbrm_host;
@@ -92,6 +93,37 @@ int nbrm_odh_reconciler_reconcile(nbrm_odh_reconciler* r, const char* keys, uint
     stats[7] = st.pull_secret_waits; stats[8] = st.errors;
   }
   if (slept_seconds) *slept_seconds = r->slept;
+  return (int)st.errors;
+}
+
+struct nbrm_profile_reconciler {
+  ProfileReconciler r;
+};
+nbrm_profile_reconciler* nbrm_profile_reconciler_new(nbrm_store* s, nbrm_ctx* ctx, const char* workload_identity,
+                                                     const char* default_labels_json) {
+  return new nbrm_profile_reconciler{ProfileReconciler(&s->s, ctx, workload_identity ? workload_identity : "",
+                                                       default_labels_json ? default_labels_json : "")};
+}
+void nbrm_profile_reconciler_free(nbrm_profile_reconciler* r) { delete r; }
+int nbrm_profile_reconciler_reconcile(nbrm_profile_reconciler* r, const char* names, uint64_t* stats) {
+  std::vector<std::string> keys;
+  const char* p = names;
+  while (p && *p) {
+    const char* e = strchr(p, '\n');
+    std::string line = e ? std::string(p, e - p) : std::string(p);
+    if (!line.empty()) keys.push_back(line);
+    if (!e) break;
+    p = e + 1;
+  }
+  ProfileStats st;
+  std::vector<std::string> errs;
+  r->r.ReconcileBatch(keys, &st, &errs);
+  if (stats) {
+    stats[0] = st.keys; stats[1] = st.reconciled; stats[2] = st.not_found; stats[3] = st.creates;
+    stats[4] = st.updates; stats[5] = st.deletes; stats[6] = st.rejected; stats[7] = st.profile_writes;
+    stats[8] = st.finalizers_added; stats[9] = st.finalizers_removed; stats[10] = st.plugins_applied;
+    stats[11] = st.plugins_revoked; stats[12] = st.errors;
+  }
   return (int)st.errors;
 }
 
