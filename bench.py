@@ -67,7 +67,8 @@ VARIANT_NOTES = {
     "server": "found objects API-server-shaped (Go field order, defaulted fields, managedFields, status): every "
               "StatefulSet is an Update, as with the reference on a live cluster",
     "steady": "found objects textually equal to the library's own output: nothing to write (round 1's workload, best case)",
-    "hetero": "512 Notebook shapes (reference fixtures + fuzzed), server-shaped found objects, 5 % of the shapes drifted",
+    "hetero": "512 Notebook shapes (reference fixtures + fuzzed), server-shaped found objects, 5 % of the shapes drifted; "
+              "NBRM_OPT_GROUP_BY_LENGTH on (threads take the tuples in the order of their length)",
 }
 T0 = 900000   # template Notebooks are built at these indices and re-keyed by text substitution
 
@@ -81,6 +82,7 @@ def parse_args():
     ap.add_argument("--batch", type=int, default=131072, help="Notebooks per GPU per step")
     ap.add_argument("--ref-sample", type=int, default=8000,
                     help="Notebooks per step of the CPU reference arm")
+    ap.add_argument("--no-group", action="store_true", help="hetero variant without NBRM_OPT_GROUP_BY_LENGTH")
     ap.add_argument("--variants", default="server,steady,hetero",
                     help="workloads to time; the first is the headline")
     return ap.parse_args()
@@ -585,6 +587,8 @@ def main():
         cb_n = 24000 if (vi == 0 and rank == 0) else 0
         w = build_workload(wl, variant, idx, want_items=cb_n)
         n_v = len(idx)
+        # a batch that mixes shapes: the library hands the tuples to its threads by length (include/nbrm.h)
+        ctx.set_option(pkg.capi.OPT_GROUP_BY_LENGTH, 1 if variant == "hetero" and not args.no_group else 0)
         d_req = pkg.Docs(w["reqs"], pinned=True)
         seeds = bytes(16 * n_v)
         rp.set_cluster_state(pkg.Docs(w["found"]), pkg.Docs(w["stss"]), pkg.Docs(w["pods"]),
@@ -700,6 +704,7 @@ def main():
         return
 
     # literal configs[1]: 100 Notebooks, latency of one full pass through the C ABI
+    ctx.set_option(pkg.capi.OPT_GROUP_BY_LENGTH, 0)
     w100 = build_workload(wl, variants[0], list(range(100)))
     small = pkg.Docs(w100["reqs"], pinned=True)
     rp.set_cluster_state(pkg.Docs(w100["found"]), pkg.Docs(w100["stss"]), pkg.Docs(w100["pods"]),

@@ -121,6 +121,13 @@ int nbrm_ctx_create(int device, nbrm_ctx** ctx);
 void nbrm_ctx_destroy(nbrm_ctx* ctx);
 const char* nbrm_last_error(const nbrm_ctx* ctx);
 int nbrm_ctx_set_env(nbrm_ctx* ctx, const nbrm_env* env);
+/* Options.  NBRM_OPT_GROUP_BY_LENGTH (default 0): for batches of more than 4096 tuples, hand the
+ * tuples to the threads of a plan kernel in the order of their first document's length, so that
+ * documents of one shape share warps; results do not move.  Worth it on batches that mix many
+ * shapes (the objects of a real cluster), costs a sort of n lengths per generator on uniform
+ * ones. */
+enum { NBRM_OPT_GROUP_BY_LENGTH = 1 };
+int nbrm_ctx_set_option(nbrm_ctx* ctx, int option, int value);
 int nbrm_sync(nbrm_ctx* ctx);
 
 /* Pinned host memory for inputs (optional). */

@@ -49,6 +49,8 @@ class Profile(C.Structure):
 
 
 # reference process environment (nbrm_env) key -> struct field
+OPT_GROUP_BY_LENGTH = 1
+
 ENV_FIELDS = {"USE_ISTIO": "use_istio", "ISTIO_GATEWAY": "istio_gateway", "ISTIO_HOST": "istio_host",
               "CLUSTER_DOMAIN": "cluster_domain", "ADD_FSGROUP": "add_fsgroup",
               "CONTROLLER_NAMESPACE": "controller_namespace", "OAUTH_PROXY_IMAGE": "oauth_proxy_image",
@@ -83,6 +85,7 @@ def load_library():
     lib.nbrm_last_error.argtypes = [C.c_void_p]
     lib.nbrm_last_error.restype = C.c_char_p
     lib.nbrm_ctx_set_env.argtypes = [C.c_void_p, C.POINTER(_Env)]
+    lib.nbrm_ctx_set_option.argtypes = [C.c_void_p, C.c_int, C.c_int]
     lib.nbrm_sync.argtypes = [C.c_void_p]
     lib.nbrm_host_alloc.argtypes = [C.c_size_t]
     lib.nbrm_host_alloc.restype = C.c_void_p
@@ -254,6 +257,10 @@ class Context:
         for k, v in env.items():
             setattr(e, ENV_FIELDS[k], None if v is None else v.encode())
         self._check(self.lib.nbrm_ctx_set_env(self.h, C.byref(e)))
+
+    def set_option(self, option, value):
+        """nbrm_ctx_set_option; option: OPT_GROUP_BY_LENGTH."""
+        self._check(self.lib.nbrm_ctx_set_option(self.h, int(option), int(value)))
 
     def sync(self):
         self._check(self.lib.nbrm_sync(self.h))

@@ -119,6 +119,8 @@ struct nbrm_ctx {
   DevBuf views;       // views of the last result's objects (generators that write them)
   bool res_views = false;
   size_t views_max = 0;  // view buffers rotate between the context and the slots: all grow to the largest asked for
+  bool group_by_length = false;  // NBRM_OPT_GROUP_BY_LENGTH
+  DevBuf group_buf, group_tmp;
   DevBuf gen_status;  // nbrm_nbc_reconcile: the generator stage's status words, kept across the compare
   uint64_t extra_bytes = 0;
   PinBuf h_out, h_off, h_status, h_result, h_total;
@@ -366,6 +368,15 @@ void nbrm_ctx_destroy(nbrm_ctx* c) {
 
 const char* nbrm_last_error(const nbrm_ctx* c) { return c ? c->err.c_str() : "null context"; }
 
+int nbrm_ctx_set_option(nbrm_ctx* c, int option, int value) {
+  if (!c) return -2;
+  if (option == NBRM_OPT_GROUP_BY_LENGTH) {
+    c->group_by_length = value != 0;
+    return 0;
+  }
+  return fail_msg(c, "unknown option");
+}
+
 int nbrm_ctx_set_env(nbrm_ctx* c, const nbrm_env* env) {
   if (!c) return -2;
   CK(cudaSetDevice(c->device));
@@ -533,6 +544,17 @@ int run_generator(nbrm_ctx* c, int gen, const int (&map)[3], uint32_t flags, con
   in.arg0 = arg0;
   in.arg1 = arg1;
   in.period = map[0] >= 0 ? c->slot[map[0]].period : 1;
+  in.perm = nullptr;
+  if (c->group_by_length && map[0] >= 0 && in.period == 1 && n > 4096) {
+    // threads take the tuples in the order of their first document's length (nbrm_group.cu)
+    const size_t tb = group_tmp_bytes(n);
+    CK(c->group_buf.reserve((size_t)n * 16 + 16));
+    CK(c->group_tmp.reserve(tb));
+    in.perm = launch_group_by_length(c->slot[map[0]].off.as<uint64_t>(), n, c->group_buf.as<uint32_t>(),
+                                     c->group_tmp.p, tb, c->stream);
+    c->launches += 1;  // the key kernel; the sort's kernels are the library's
+    CK(cudaGetLastError());
+  }
   const uint32_t n_out = n * nobj;
   CK(c->segs.reserve((size_t)n_out * cap * sizeof(Seg) + 16));
   CK(c->nseg.reserve((size_t)n_out * 4 + 16));

@@ -39,6 +39,7 @@ struct PlanIn {
   uint32_t arg0, arg1;
   uint32_t shared_n;  // documents in slot 1 when the generator reads it as a shared arena
   uint32_t period;    // kinds of document repeat with this period in slot 0 (1 = all alike)
+  const uint32_t* perm;  // thread t plans tuple perm[t] (nbrm_group.cu), or null: tuple t
 };
 
 // Where a plan kernel writes.
@@ -63,6 +64,11 @@ void launch_merge_status(const uint32_t* gen, uint32_t* pair, uint32_t n_pairs, 
 void launch_emit(const Seg* segs, const uint32_t* nseg, const uint32_t* lens, const uint64_t* off,
                  uint32_t n_out, uint32_t cap, uint32_t nobj, const SrcBases& bases, char* out,
                  int sm_count, cudaStream_t st);
+
+// nbrm_group.cu
+size_t group_tmp_bytes(uint32_t n);
+const uint32_t* launch_group_by_length(const uint64_t* off, uint32_t n, uint32_t* buf, void* tmp, size_t tmp_bytes,
+                                       cudaStream_t st);
 
 // nbrm_tape_index.cu
 void launch_index_slot(const DevDocs& docs, uint32_t n, void* arena, uint32_t arena_cap, uint32_t* cursor,

@@ -70,6 +70,7 @@ __global__ void plan_kernel(PlanIn in, PlanOut out, uint32_t smem_cap, uint32_t 
   }
   __syncthreads();
   if (i >= in.n) return;
+  if (in.perm) i = in.perm[i];  // unstaged, period 1 (launch_thread): tuples in the order of their length
 
   DocCtx c;
   uint32_t aux_abs = i * AUX_PAD, aux_cap = AUX_PAD;
@@ -264,7 +265,7 @@ static void launch_thread(const PlanIn& in, const PlanOut& out, uint64_t in_byte
 #ifdef NBRM_NO_STAGING
   const uint64_t avg = PLAN_SMEM;  // this unit's kernel always walks global memory
 #else
-  const uint64_t avg = in_bytes / in.n + 48;
+  const uint64_t avg = in.perm ? PLAN_SMEM : in_bytes / in.n + 48;  // a permuted batch is not contiguous per block
 #endif
   if (in.period > 1 && in.period <= 8) {  // threads that run together take one kind (see plan_kernel)
     if ((uint64_t)32 * in.period * avg <= PLAN_SMEM) {
