@@ -347,6 +347,16 @@ int nbrm_profile_generate_resident(nbrm_ctx* ctx);
 int nbrm_tensorboard_generate(nbrm_ctx* ctx, const nbrm_docs* tensorboards, const nbrm_docs* node_names,
                               uint32_t flags, nbrm_out* out);
 
+/* After the Get of the Deployment (tensorboard_controller.go:484-510, :119-152): per Tensorboard
+ * the desired Deployment (output 3 i of nbrm_tensorboard_generate) and the found one (empty =
+ * NotFound: the caller Creates the desired object and nothing is returned).  Output 2 i: the
+ * body of the Update — the found object with the labels, replicas and affinity of the desired
+ * one (CopyDeploymentSetFields :512-533) — or length 0 when nothing differs; output 2 i + 1: the
+ * Tensorboard's status as r.Status().Update sends it (the Deployment's first condition appended
+ * when its type is not the last deploymentState, readyReplicas).  result: 1 = Update needed. */
+int nbrm_tensorboard_update(nbrm_ctx* ctx, const nbrm_docs* tensorboards, const nbrm_docs* desired,
+                            const nbrm_docs* found, nbrm_out* out);
+
 /* ---- pvcviewer-controller: what a reconcile writes ------------------------------
  * Replaces, for a batch of PVCViewer CRs, the bodies reconcileDeployment / reconcileService /
  * reconcileVirtualService build between their Get and their Create or Update
@@ -367,6 +377,12 @@ int nbrm_pvcviewer_reconcile(nbrm_ctx* ctx, const nbrm_docs* viewers, const nbrm
  * per viewer, the viewer as Default leaves it.  result: 0 = valid, 1 = "PVC name must be
  * specified", 2 = "PodSpec must be specified", 3 = "PVC <pvc> must be used in the podSpec". */
 int nbrm_pvcviewer_webhook(nbrm_ctx* ctx, const nbrm_docs* viewers, nbrm_out* out);
+
+/* reconcileStatus (pvcviewer_controller.go:339-369): per viewer its Deployment (empty = the Get
+ * failed: ready false).  Output: the status the reconciler sends — url from the networking,
+ * ready = replicas == readyReplicas, the Deployment's first condition appended when the last
+ * one differs.  NBRM_E_NIL_REPLICAS where the reference dereferences a nil Spec.Replicas. */
+int nbrm_pvcviewer_status(nbrm_ctx* ctx, const nbrm_docs* viewers, const nbrm_docs* deployments, nbrm_out* out);
 
 /* ---- composing generators --------------------------------------------------
  * Run one generator on arbitrary slots: tuple i = document i of slot_a (and of

@@ -136,6 +136,8 @@ def load_library():
     lib.nbrm_download_wait.argtypes = [C.c_void_p, C.c_int, C.POINTER(_Out)]
     lib.nbrm_profile_generate.argtypes = [C.c_void_p, C.POINTER(_Docs), C.POINTER(_Out)]
     lib.nbrm_profile_generate_resident.argtypes = [C.c_void_p]
+    lib.nbrm_tensorboard_update.argtypes = [C.c_void_p, C.POINTER(_Docs), C.POINTER(_Docs), C.POINTER(_Docs), C.POINTER(_Out)]
+    lib.nbrm_pvcviewer_status.argtypes = [C.c_void_p, C.POINTER(_Docs), C.POINTER(_Docs), C.POINTER(_Out)]
     lib.nbrm_pvcviewer_webhook.argtypes = [C.c_void_p, C.POINTER(_Docs), C.POINTER(_Out)]
     lib.nbrm_pvcviewer_reconcile.argtypes = [C.c_void_p, C.POINTER(_Docs), C.POINTER(_Docs), C.POINTER(_Docs), C.POINTER(_Out)]
     lib.nbrm_tensorboard_generate.argtypes = [C.c_void_p, C.POINTER(_Docs), C.POINTER(_Docs), C.c_uint32, C.POINTER(_Out)]
@@ -453,6 +455,17 @@ class Context:
         nn = node_names.c_struct() if node_names is not None else None
         self._check(self.lib.nbrm_pvcviewer_reconcile(self.h, C.byref(d), C.byref(f) if f is not None else None,
                                                       C.byref(nn) if nn is not None else None, C.byref(o)))
+        return Result(o, copy)
+
+    def tensorboard_update(self, tensorboards, desired, found, copy=True):
+        """Per Tensorboard: the Deployment Update body (or b"") and the status (include/nbrm.h)."""
+        a, b, d, o = tensorboards.c_struct(), desired.c_struct(), found.c_struct(), _Out()
+        self._check(self.lib.nbrm_tensorboard_update(self.h, C.byref(a), C.byref(b), C.byref(d), C.byref(o)))
+        return Result(o, copy)
+
+    def pvcviewer_status(self, viewers, deployments, copy=True):
+        a, b, o = viewers.c_struct(), deployments.c_struct(), _Out()
+        self._check(self.lib.nbrm_pvcviewer_status(self.h, C.byref(a), C.byref(b), C.byref(o)))
         return Result(o, copy)
 
     def pvcviewer_webhook(self, viewers, copy=True):

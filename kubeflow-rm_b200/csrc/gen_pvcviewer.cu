@@ -7,4 +7,5 @@
 namespace nbrm {
 NBRM_DEFINE_GENERATOR(pvcviewer, GenPvcViewer)
 NBRM_DEFINE_GENERATOR(pvcviewerdefault, GenPvcViewerDefault)
+NBRM_DEFINE_GENERATOR(pvstatus, GenPvStatus)
 }  // namespace nbrm

@@ -6,4 +6,5 @@
 
 namespace nbrm {
 NBRM_DEFINE_GENERATOR(tensorboard, GenTensorboard)
+NBRM_DEFINE_GENERATOR(tbupdate, GenTbUpdate)
 }  // namespace nbrm

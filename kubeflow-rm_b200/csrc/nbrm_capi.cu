@@ -1167,6 +1167,24 @@ int nbrm_pvcviewer_reconcile(nbrm_ctx* c, const nbrm_docs* viewers, const nbrm_d
   return nbrm_download(c, out);
 }
 
+int nbrm_tensorboard_update(nbrm_ctx* c, const nbrm_docs* tensorboards, const nbrm_docs* desired,
+                            const nbrm_docs* found, nbrm_out* out) {
+  if (!c || !out) return -2;
+  if (int r = nbrm_upload(c, 0, tensorboards)) return r;
+  if (int r = nbrm_upload(c, 1, desired)) return r;
+  if (int r = nbrm_upload(c, 2, found)) return r;
+  if (int r = run_generator(c, GEN_ID_TB_UPDATE, {0, 1, 2}, 0, nullptr, 0)) return r;
+  return nbrm_download(c, out);
+}
+
+int nbrm_pvcviewer_status(nbrm_ctx* c, const nbrm_docs* viewers, const nbrm_docs* deployments, nbrm_out* out) {
+  if (!c || !out) return -2;
+  if (int r = nbrm_upload(c, 0, viewers)) return r;
+  if (int r = nbrm_upload(c, 1, deployments)) return r;
+  if (int r = run_generator(c, GEN_ID_PVCVIEWER_STATUS, {0, 1, -1}, 0, nullptr, 0)) return r;
+  return nbrm_download(c, out);
+}
+
 int nbrm_pvcviewer_webhook(nbrm_ctx* c, const nbrm_docs* viewers, nbrm_out* out) {
   if (!c || !out) return -2;
   if (int r = nbrm_upload(c, 0, viewers)) return r;

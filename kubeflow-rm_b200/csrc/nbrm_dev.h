@@ -79,7 +79,7 @@ void launch_tape_dump(const DevDocs& docs, uint32_t n, uint32_t cap, void* out, 
 // nbrm_plan_kernels.cu
 enum GenId { GEN_ID_NBC = 0, GEN_ID_ODH = 1, GEN_ID_COPY = 2, GEN_ID_STATUS = 3, GEN_ID_CULL = 4,
              GEN_ID_MUTATE = 5, GEN_ID_GUARD = 6, GEN_ID_PODDEFAULT = 7, GEN_ID_PROFILE = 8, GEN_ID_ODHDECIDE = 9, GEN_ID_DIFF = 10,
-             GEN_ID_REVIEW_OPEN = 11, GEN_ID_REVIEW_CLOSE = 12, GEN_ID_CONVERT = 13, GEN_ID_TENSORBOARD = 14, GEN_ID_PVCVIEWER = 15, GEN_ID_PVCVIEWER_DEFAULT = 16 };
+             GEN_ID_REVIEW_OPEN = 11, GEN_ID_REVIEW_CLOSE = 12, GEN_ID_CONVERT = 13, GEN_ID_TENSORBOARD = 14, GEN_ID_PVCVIEWER = 15, GEN_ID_PVCVIEWER_DEFAULT = 16, GEN_ID_TB_UPDATE = 17, GEN_ID_PVCVIEWER_STATUS = 18 };
 void launch_plan(int gen, const PlanIn& in, const PlanOut& out, uint64_t in_bytes, cudaStream_t st);
 void gen_shape(int gen, uint32_t* nobj, uint32_t* cap);
 bool gen_shared1(int gen);

@@ -40,6 +40,10 @@ void launch_plan_pvcviewer(const PlanIn&, const PlanOut&, uint64_t, cudaStream_t
 void gen_shape_pvcviewer(uint32_t*, uint32_t*, bool*);
 void launch_plan_pvcviewerdefault(const PlanIn&, const PlanOut&, uint64_t, cudaStream_t);
 void gen_shape_pvcviewerdefault(uint32_t*, uint32_t*, bool*);
+void launch_plan_tbupdate(const PlanIn&, const PlanOut&, uint64_t, cudaStream_t);
+void gen_shape_tbupdate(uint32_t*, uint32_t*, bool*);
+void launch_plan_pvstatus(const PlanIn&, const PlanOut&, uint64_t, cudaStream_t);
+void gen_shape_pvstatus(uint32_t*, uint32_t*, bool*);
 
 void launch_plan(int gen, const PlanIn& in, const PlanOut& out, uint64_t in_bytes, cudaStream_t st) {
   switch (gen) {
@@ -60,6 +64,8 @@ void launch_plan(int gen, const PlanIn& in, const PlanOut& out, uint64_t in_byte
     case GEN_ID_TENSORBOARD: launch_plan_tensorboard(in, out, in_bytes, st); break;
     case GEN_ID_PVCVIEWER: launch_plan_pvcviewer(in, out, in_bytes, st); break;
     case GEN_ID_PVCVIEWER_DEFAULT: launch_plan_pvcviewerdefault(in, out, in_bytes, st); break;
+    case GEN_ID_TB_UPDATE: launch_plan_tbupdate(in, out, in_bytes, st); break;
+    case GEN_ID_PVCVIEWER_STATUS: launch_plan_pvstatus(in, out, in_bytes, st); break;
   }
 }
 
@@ -82,6 +88,8 @@ static bool shape_of(int gen, uint32_t* nobj, uint32_t* cap, bool* shared1) {
     case GEN_ID_TENSORBOARD: gen_shape_tensorboard(nobj, cap, shared1); return true;
     case GEN_ID_PVCVIEWER: gen_shape_pvcviewer(nobj, cap, shared1); return true;
     case GEN_ID_PVCVIEWER_DEFAULT: gen_shape_pvcviewerdefault(nobj, cap, shared1); return true;
+    case GEN_ID_TB_UPDATE: gen_shape_tbupdate(nobj, cap, shared1); return true;
+    case GEN_ID_PVCVIEWER_STATUS: gen_shape_pvstatus(nobj, cap, shared1); return true;
   }
   *nobj = 0;
   *cap = 0;

@@ -321,6 +321,91 @@ struct GenPvcViewer {
   }
 };
 
+// ---- reconcileStatus :339-369 -------------------------------------------------------------
+// Slot 0: the viewer, slot 1: its Deployment (empty: the Get failed).  Output: the status
+// r.Client.Status().Update sends: url from the networking, ready = replicas == readyReplicas,
+// the Deployment's first condition appended when the last one differs.
+NB_HD void plan_pv_status(Planner& P, DocCtx& c) {
+  const Doc& d = c.d[0];
+  const Doc& dep = c.d[1];
+  const PvView v = view_pvcviewer(d);
+  const Span conds = FIND(d, FIND(d, root(d), "status"), "conditions");
+  Span last = mk(0, 0);
+  uint32_t n_old = 0;
+  {
+    ArrIter it(d, conds);
+    Span e;
+    while (it.next(d, e)) {
+      last = e;
+      ++n_old;
+    }
+  }
+  Span d0 = mk(0, 0);
+  bool ready = false;
+  if (dep.n) {
+    const Span dr = root(dep);
+    const Span rep = FIND(dep, FIND(dep, dr, "spec"), "replicas");
+    if (is_nil(dep, rep)) {  // *deployment.Spec.Replicas :357
+      P.err = E_NIL_REPLICAS;
+      return;
+    }
+    const Span dst = FIND(dep, dr, "status");
+    const Span rr = FIND(dep, dst, "readyReplicas");
+    ready = is_nil(dep, rr) ? (rep.len == 1 && dep.at(rep.off) == '0') : spans_eq(dep, rep, dep, rr);
+    ArrIter it(dep, FIND(dep, dst, "conditions"));
+    Span e;
+    if (it.next(dep, e)) d0 = e;
+  }
+  bool deep = false;
+  const bool append = d0.ok() && (n_old == 0 || !json_equal(d, last, dep, d0, &deep));  // :360-363
+  if (deep) {
+    P.err = E_LIMIT;
+    return;
+  }
+  LIT(P, LBRACE);
+  if (n_old || append) {
+    LIT(P, PVS_CONDS);
+    Sep s;
+    ArrIter it(d, conds);
+    Span e;
+    while (it.next(d, e)) s.in(P, d, e);
+    if (append) {
+      s.next(P);
+      P.in(d0, 1);
+    }
+    LIT(P, PVS_CONDS_CLOSE);
+  }
+  if (ready) LIT(P, PVS_READY_TRUE);
+  else LIT(P, PVS_READY_FALSE);
+  if (!v.net_zero) {
+    LIT(P, PVS_URL);
+    if (is_string(d, v.base)) P.in(inner(v.base));
+    LIT(P, SLASH);
+    P.in(inner(v.ns));
+    LIT(P, SLASH);
+    P.in(inner(v.name));
+    LIT(P, SLASH_QUOTE);
+  }
+  LIT(P, RBRACE);
+}
+
+struct GenPvStatus {
+  static const uint32_t NOBJ = 1;
+  static const bool SHARED1 = false;
+  static const uint32_t CAP = 48;
+  struct K {
+    DocCtx& c;
+    NB_HD void operator()(Planner& P, uint32_t) { plan_pv_status(P, c); }
+  };
+  NB_HD static uint32_t run(DocCtx& c, ObjSink s) {
+    const Doc& d = c.d[0];
+    const uint32_t i0 = skip_ws(d, 0);
+    const uint32_t st = (i0 < d.n && d.at(i0) == '{') ? E_OK : E_PARSE;
+    K k{c};
+    return plan_objects(c, s, NOBJ, st, k);
+  }
+};
+
 // ---- the viewer's webhook ------------------------------------------------------------------
 // Reference: pvcviewer-controller/api/v1alpha1/pvcviewer_webhook.go — Default :70-146 (the
 // defaults file of DEFAULT_POD_SPEC_PATH :78-91 arrives through the environment, split by the

@@ -13,6 +13,7 @@
 // the error (having written the Deployment and the Service first when it is the VirtualService's
 // variables that are missing; the batch form fails the whole tuple).
 #pragma once
+#include "nbrm_cmp.cuh"
 #include "nbrm_nbc.cuh"
 
 namespace nbrm {
@@ -258,6 +259,232 @@ struct GenTensorboard {
     if (!st && (c.env->tb_env & need) != need) st = E_ENV;
     TbView v = view_tensorboard(d);
     K k{c, v};
+    return plan_objects(c, s, NOBJ, st, k);
+  }
+};
+
+// ---- after the Get of the Deployment -----------------------------------------------------
+// Reference: Deployment :484-510 with CopyDeploymentSetFields :512-533 (labels of the found
+// object that the desired one does not carry with the same value, replicas, affinity), and
+// the status update of Reconcile :119-152.  Slot 0: Tensorboard CR, slot 1: the desired
+// Deployment (GenTensorboard's), slot 2: the found one (empty: NotFound — the caller Creates
+// the desired object and writes no status, :491-498,:124-129).  Output 0: the body of the
+// Update (the found object with labels, replicas and affinity of the desired one), length 0
+// when CopyDeploymentSetFields says nothing changed.  Output 1: the Tensorboard's status as
+// r.Status().Update sends it (:148).  result: 1 = the Deployment is updated.
+NB_HD void plan_tb_deployment_update(Planner& P, DocCtx& c) {
+  const Doc& from = c.d[1];
+  const Doc& to = c.d[2];
+  if (!to.n) return;
+  const Span fr = root(from), tr = root(to);
+  if (!is_object(from, fr) || !is_object(to, tr)) {
+    P.err = E_PARSE;
+    return;
+  }
+  const Span flabels = FIND(from, FIND(from, fr, "metadata"), "labels");
+  const Span tmeta = FIND(to, tr, "metadata");
+  const Span fspec = FIND(from, fr, "spec"), tspec = FIND(to, tr, "spec");
+  const Span frep = FIND(from, fspec, "replicas"), trep = FIND(to, tspec, "replicas");
+  const Span faff = FIND(from, FIND(from, FIND(from, fspec, "template"), "spec"), "affinity");
+  const Span ttmpl = FIND(to, tspec, "template");
+  const Span tpod = FIND(to, ttmpl, "spec");
+  const Span taff = FIND(to, tpod, "affinity");
+  if (is_nil(from, frep) || is_nil(to, trep)) {  // *from.Spec.Replicas != *to.Spec.Replicas :521
+    P.err = E_NIL_REPLICAS;
+    return;
+  }
+  bool deep = false;
+  bool update = map_field_differs(from, flabels, to, FIND(to, tmeta, "labels"));  // :514-518
+  if (!spans_eq(from, frep, to, trep)) update = true;
+  const bool fnil = is_nil(from, faff), tnil = is_nil(to, taff);
+  if (fnil != tnil || (!fnil && !json_equal(from, faff, to, taff, &deep))) update = true;  // :526-529
+  if (deep) {
+    P.err = E_LIMIT;
+    return;
+  }
+  if (!update) return;
+  c.result |= 1u;
+  // the found object, with the three fields of the desired one
+  LIT(P, LBRACE);
+  Sep s;
+  ObjIter it(to, tr);
+  Member m;
+  bool had_meta = false, had_spec = false;
+  while (it.next(to, m)) {
+    if (str_eq(to, m.key, "metadata") && is_object(to, m.val)) {
+      had_meta = true;
+      s.next(P);
+      LIT(P, TBU_META);
+      Sep ms;
+      ObjIter mi(to, m.val);
+      Member mm;
+      while (mi.next(to, mm)) {
+        if (str_eq(to, mm.key, "labels")) continue;
+        ms.in(P, to, mm.all, 2);
+      }
+      if (!is_nil(from, flabels)) {  // to.Labels = from.Labels :519
+        ms.next(P);
+        LIT(P, TBU_LABELS);
+        P.in(flabels, 1);
+      }
+      LIT(P, RBRACE);
+    } else if (str_eq(to, m.key, "spec") && is_object(to, m.val)) {
+      had_spec = true;
+      s.next(P);
+      LIT(P, PV_WH_SPEC);
+      Sep ss;
+      ObjIter si(to, m.val);
+      Member sm;
+      bool had_tmpl = false;
+      while (si.next(to, sm)) {
+        if (str_eq(to, sm.key, "replicas")) continue;
+        if (str_eq(to, sm.key, "template") && is_object(to, sm.val)) {
+          had_tmpl = true;
+          ss.next(P);
+          LIT(P, TBU_TEMPLATE);
+          Sep ts;
+          ObjIter ti(to, sm.val);
+          Member tm;
+          bool had_pod = false;
+          while (ti.next(to, tm)) {
+            if (str_eq(to, tm.key, "spec") && is_object(to, tm.val)) {
+              had_pod = true;
+              ts.next(P);
+              LIT(P, PV_WH_SPEC);
+              Sep ps;
+              ObjIter pi(to, tm.val);
+              Member pm;
+              while (pi.next(to, pm)) {
+                if (str_eq(to, pm.key, "affinity")) continue;
+                ps.in(P, to, pm.all, 2);
+              }
+              if (!fnil) {
+                ps.next(P);
+                LIT(P, PV_AFFINITY_KEY);
+                P.in(faff, 1);
+              }
+              LIT(P, RBRACE);
+            } else {
+              ts.in(P, to, tm.all, 2);
+            }
+          }
+          if (!had_pod && !fnil) {
+            ts.next(P);
+            LIT(P, PV_WH_SPEC);
+            LIT(P, PV_AFFINITY_KEY);
+            P.in(faff, 1);
+            LIT(P, RBRACE);
+          }
+          LIT(P, RBRACE);
+        } else {
+          ss.in(P, to, sm.all, 2);
+        }
+      }
+      if (!had_tmpl && !fnil) {
+        ss.next(P);
+        LIT(P, TBU_TEMPLATE);
+        LIT(P, PV_WH_SPEC);
+        LIT(P, PV_AFFINITY_KEY);
+        P.in(faff, 1);
+        LIT(P, RBRACE2);
+      }
+      ss.next(P);
+      LIT(P, TBU_REPLICAS);
+      P.in(frep, 1);
+      LIT(P, RBRACE);
+    } else {
+      s.in(P, to, m.all, 2);
+    }
+  }
+  if (!had_meta && !is_nil(from, flabels)) {
+    s.next(P);
+    LIT(P, TBU_META);
+    LIT(P, TBU_LABELS);
+    P.in(flabels, 1);
+    LIT(P, RBRACE);
+  }
+  (void)had_spec;  // the found spec exists: its replicas were read above
+  LIT(P, RBRACE);
+}
+
+NB_HD void plan_tb_status(Planner& P, DocCtx& c) {
+  const Doc& tb = c.d[0];
+  const Doc& dep = c.d[2];
+  if (!dep.n) return;
+  const Span st = FIND(tb, root(tb), "status");
+  const Span conds = FIND(tb, st, "conditions");
+  const Span dst = FIND(dep, root(dep), "status");
+  Span d0 = mk(0, 0);
+  {
+    ArrIter it(dep, FIND(dep, dst, "conditions"));
+    Span e;
+    if (it.next(dep, e)) d0 = e;
+  }
+  // the last condition's state against the Deployment's first condition (:131-141)
+  Span last = mk(0, 0);
+  uint32_t n_old = 0;
+  {
+    ArrIter it(tb, conds);
+    Span e;
+    while (it.next(tb, e)) {
+      last = e;
+      ++n_old;
+    }
+  }
+  bool append = false;
+  Span dtype = mk(0, 0);
+  if (d0.ok()) {
+    dtype = FIND(dep, d0, "type");
+    const Span ls = FIND(tb, last, "deploymentState");
+    const bool le = !is_string(tb, ls) || ls.len == 2, de = !is_string(dep, dtype) || dtype.len == 2;
+    append = n_old == 0 || (le != de) || (!le && !str_equal(tb, ls, dep, dtype));
+  }
+  LIT(P, TBU_STATUS_HEAD);
+  if (n_old == 0 && !append) {
+    LIT(P, NULL_LIT);
+  } else {
+    LIT(P, LBRACKET);
+    Sep s;
+    ArrIter it(tb, conds);
+    Span e;
+    while (it.next(tb, e)) s.in(P, tb, e);
+    if (append) {
+      s.next(P);
+      LIT(P, TBU_COND);
+      if (is_string(dep, dtype)) P.in(dtype, 2);
+      else LIT(P, EMPTY_STR);
+      LIT(P, TBU_PROBE);
+      const Span lut = FIND(dep, d0, "lastUpdateTime");
+      if (is_string(dep, lut)) P.in(lut, 2);
+      else LIT(P, NULL_LIT);
+      LIT(P, RBRACE);
+    }
+    LIT(P, RBRACKET);
+  }
+  LIT(P, TBU_READY);
+  const Span rr = FIND(dep, dst, "readyReplicas");
+  if (is_nil(dep, rr)) LIT(P, ZERO);
+  else P.in(rr, 2);
+  LIT(P, RBRACE);
+}
+
+struct GenTbUpdate {
+  static const uint32_t NOBJ = 2;
+  static const bool SHARED1 = false;
+  static const uint32_t CAP = 96;
+  struct K {
+    DocCtx& c;
+    NB_HD void operator()(Planner& P, uint32_t k) {
+      if (k == 0) plan_tb_deployment_update(P, c);
+      else plan_tb_status(P, c);
+    }
+  };
+  NB_HD static uint32_t run(DocCtx& c, ObjSink s) {
+    const Doc& d = c.d[0];
+    const uint32_t i0 = skip_ws(d, 0);
+    const uint32_t st = (i0 < d.n && d.at(i0) == '{') ? E_OK : E_PARSE;
+    c.result = 0;
+    K k{c};
     return plan_objects(c, s, NOBJ, st, k);
   }
 };

@@ -156,6 +156,8 @@ def reconcile_status(viewer, deployment):
         status.pop("url", None)
     if deployment is None:
         status["ready"] = False
+        if not status.get("conditions"):
+            status.pop("conditions", None)
         return status
     replicas = (deployment.get("spec") or {}).get("replicas")
     if replicas is None:
@@ -167,6 +169,8 @@ def reconcile_status(viewer, deployment):
         if not conds or conds[-1] != dconds[0]:
             conds.append(deepcopy(dconds[0]))
         status["conditions"] = conds
+    if not status.get("conditions"):
+        status.pop("conditions", None)                                                  # omitempty
     return status
 
 

@@ -202,11 +202,10 @@ def update_status(tb, found_deployment):
     conds = list(status.get("conditions") or [])
     dconds = (found_deployment.get("status") or {}).get("conditions") or []
     if dconds:                                                                          # :131-141
-        c = {"deploymentState": dconds[0].get("type", "")}
-        if dconds[0].get("lastUpdateTime"):
-            c["lastProbeTime"] = dconds[0]["lastUpdateTime"]
+        # metav1.Time has no omitempty that works on a struct: the zero time is written as null
+        c = {"deploymentState": dconds[0].get("type", ""), "lastProbeTime": dconds[0].get("lastUpdateTime")}
         if not conds or conds[-1].get("deploymentState", "") != c["deploymentState"]:
             conds.append(c)
-    status["conditions"] = conds
+    status["conditions"] = conds if conds else None      # `json:"conditions"`: a nil slice is null
     status["readyReplicas"] = (found_deployment.get("status") or {}).get("readyReplicas", 0)   # :143-146
     return status

@@ -419,6 +419,8 @@ HP_API int hostplan_run(int gen, const char* d0, const uint64_t* o0, const char*
     case 11: rc = run_host<GenReviewOpen>(g_out, data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenReviewOpen::NOBJ; break;
     case 12: rc = run_host<GenReviewClose>(g_out, data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenReviewClose::NOBJ; break;
     case 13: rc = run_host<GenConvert>(g_out, data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenConvert::NOBJ; break;
+    case 17: rc = run_host<GenTbUpdate>(g_out, data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenTbUpdate::NOBJ; break;
+    case 18: rc = run_host<GenPvStatus>(g_out, data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenPvStatus::NOBJ; break;
     case 16: rc = run_host<GenPvcViewerDefault>(g_out, data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenPvcViewerDefault::NOBJ; break;
     case 15: rc = run_host<GenPvcViewer>(g_out, data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenPvcViewer::NOBJ; break;
     case 14: rc = run_host<GenTensorboard>(g_out, data, off, n, env, flags, extra, now, arg0, arg1, shared_n); *nobj = GenTensorboard::NOBJ; break;

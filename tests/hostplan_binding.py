@@ -10,6 +10,7 @@ GEN_DIFF, GEN_REVIEW_OPEN, GEN_REVIEW_CLOSE = 10, 11, 12
 GEN_TENSORBOARD = 14
 GEN_PVCVIEWER = 15
 GEN_PVCVIEWER_DEFAULT = 16
+GEN_TB_UPDATE, GEN_PV_STATUS = 17, 18
 
 
 def _pack(docs_list):
@@ -107,6 +108,12 @@ class HostPlan:
 
     def pvcviewer(self, viewers, found=None, node_names=None, env=None):
         return self.run(GEN_PVCVIEWER, [viewers, found if found is not None else [], node_names], env, shared1=True)
+
+    def tensorboard_update(self, tensorboards, desired, found):
+        return self.run(GEN_TB_UPDATE, [tensorboards, desired, found], want_result=True)
+
+    def pvcviewer_status(self, viewers, deployments):
+        return self.run(GEN_PV_STATUS, [viewers, deployments])
 
     def pvcviewer_webhook(self, viewers, env=None):
         return self.run(GEN_PVCVIEWER_DEFAULT, [viewers], env, want_result=True)

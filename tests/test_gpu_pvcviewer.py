@@ -51,3 +51,15 @@ def test_webhook(ctx, pkg, wl, hostplan):
             assert outs == res.docs() and list(r) == list(res.result)
     finally:
         ctx.set_env({})
+
+
+def test_reconcile_status(ctx, pkg, wl, hostplan):
+    from test_hostplan_pvcviewer import check_status, status_cases
+    viewers, deps = status_cases(wl, 6000, 93)
+    rng = random.Random(94)
+    a = [wl.dumps(v, rng) for v in viewers]
+    b = [b"" if d is None else wl.dumps(d, rng) for d in deps]
+    res = ctx.pvcviewer_status(pkg.Docs(a), pkg.Docs(b))
+    check_status(viewers, deps, res.docs(), res.status)
+    outs, st = hostplan.pvcviewer_status(a, b)
+    assert outs == res.docs()

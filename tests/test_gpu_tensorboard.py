@@ -36,3 +36,18 @@ def test_tensorboards(ctx, pkg, wl, hostplan):
         assert (np.asarray(res.status) == 10).all() and all(o == b"" for o in res.docs())
     finally:
         ctx.set_env({})
+
+
+def test_deployment_update_and_status(ctx, pkg, wl, hostplan):
+    from test_hostplan_tensorboard import check_update, deployments_for, with_status
+    rng = random.Random(91)
+    tbs = [with_status(rng, wl.tensorboard_cr(rng, i)) for i in range(6000)]
+    desired, found = deployments_for(wl, tbs, 92)
+    a = [wl.dumps(t, rng) for t in tbs]
+    b = [wl.dumps(d, rng) for d in desired]
+    c = [b"" if f is None else wl.dumps(f, rng) for f in found]
+    res = ctx.tensorboard_update(pkg.Docs(a), pkg.Docs(b), pkg.Docs(c))
+    n_upd, n_same = check_update(tbs, desired, found, res.docs(), res.status, res.result)
+    assert n_upd > 2000 and n_same > 600
+    outs, st, r = hostplan.tensorboard_update(a, b, c)
+    assert outs == res.docs() and list(r) == list(res.result)

@@ -170,3 +170,47 @@ def test_webhook_default_and_validate(hostplan, wl):
     for f in (DEFAULT_FILE, {"containers": None}, {"containers": [{"name": "only"}]}):
         outs, st, res = hostplan.pvcviewer_webhook(docs, {"PVCVIEWER_DEFAULT_PODSPEC_JSON": json.dumps(f)})
         check_webhook(viewers, outs, st, res, f)
+
+
+def status_cases(wl, n, seed):
+    rng = random.Random(seed)
+    viewers, deps = [], []
+    cond_a = {"type": "Available", "status": "True", "lastUpdateTime": "2026-11-07T10:00:00Z"}
+    cond_b = {"type": "Progressing", "status": "True", "reason": "NewReplicaSetAvailable"}
+    for i in range(n):
+        v = wl.pvcviewer_cr(rng, i)
+        v["status"] = rng.choice([None, {}, {"ready": False}, {"ready": True, "conditions": [cond_a], "url": "/old/"},
+                                  {"conditions": [cond_b, cond_a]}])
+        if v["status"] is None:
+            del v["status"]
+        r = rng.random()
+        if r < 0.2:
+            deps.append(None)
+        else:
+            d = {"apiVersion": "apps/v1", "kind": "Deployment", "metadata": {"name": "pvcviewer-" + v["metadata"]["name"]},
+                 "spec": {"replicas": rng.choice([0, 1, 2])},
+                 "status": {"readyReplicas": rng.choice([0, 1, 2]), "conditions": rng.choice([[], [cond_a], [cond_b, cond_a], [dict(cond_a, status="False")]])}}
+            if rng.random() < 0.2:
+                del d["status"]["readyReplicas"]
+            if rng.random() < 0.1:
+                d["status"] = {}
+            deps.append(d)
+        viewers.append(v)
+    return viewers, deps
+
+
+def check_status(viewers, deps, outs, st):
+    for v, d, o, s in zip(viewers, deps, outs, st):
+        assert s == 0
+        assert gojson.canon(json.loads(o)) == gojson.canon(opv.reconcile_status(v, d)), (o, v, d)
+
+
+def test_reconcile_status(hostplan, wl):
+    viewers, deps = status_cases(wl, 1500, 81)
+    rng = random.Random(82)
+    outs, st = hostplan.pvcviewer_status([wl.dumps(v, rng) for v in viewers],
+                                         [b"" if d is None else wl.dumps(d, rng) for d in deps])
+    check_status(viewers, deps, outs, st)
+    # a Deployment without spec.replicas: the reference dereferences nil
+    outs, st = hostplan.pvcviewer_status([wl.dumps(viewers[0])], [b'{"kind":"Deployment","spec":{}}'])
+    assert list(st) == [5] and outs == [b""]

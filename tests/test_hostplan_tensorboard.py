@@ -93,3 +93,80 @@ def test_copy_deployment_fields_and_status(wl):
     assert s == {"conditions": [{"deploymentState": "Progressing"},
                                 {"deploymentState": "Available", "lastProbeTime": "2026-11-07T00:00:00Z"}], "readyReplicas": 1}
     assert otb.update_status({"status": s}, dep) == s and otb.update_status({}, None) is None
+    assert otb.update_status({}, {"status": {}}) == {"conditions": None, "readyReplicas": 0}
+
+
+def deployments_for(wl, tbs, seed):
+    """(desired, found) Deployments per Tensorboard: found None (NotFound), equal, or drifted in the
+    three things CopyDeploymentSetFields looks at, with what an API server adds."""
+    rng = random.Random(seed)
+    desired, found = [], []
+    for tb in tbs:
+        d = otb.generate_deployment(tb, ENV, nodename=rng.choice(["", "node-1"]) if rng.random() < 0.3 else "")
+        desired.append(d)
+        r = rng.random()
+        if r < 0.25:
+            found.append(None)
+            continue
+        f = json.loads(json.dumps(d))
+        f["metadata"].update({"resourceVersion": "7", "generation": 3})
+        f["status"] = {"readyReplicas": rng.choice([0, 1]), "conditions": rng.choice(
+            [[], [{"type": "Available", "status": "True", "lastUpdateTime": "2026-11-07T10:00:00Z"}],
+             [{"type": "Progressing", "status": "True"}, {"type": "Available", "status": "True"}]])}
+        if rng.random() < 0.2:
+            del f["status"]["readyReplicas"]
+        if rng.random() < 0.2:
+            f["status"] = {}
+        f["spec"]["strategy"] = {"type": "RollingUpdate"}
+        if r < 0.4:
+            f["spec"]["replicas"] = 3
+        elif r < 0.55:
+            f["metadata"]["labels"] = {"stale": "x"}
+        elif r < 0.65:
+            f["metadata"]["labels"] = {"empty": ""}          # from.Labels[k] == "" == v: no update
+        elif r < 0.8:
+            f["spec"]["template"]["spec"]["affinity"] = otb.node_affinity("node-9")
+        elif r < 0.87:
+            del f["spec"]["template"]["spec"]["affinity"]
+        found.append(f)
+    return desired, found
+
+
+def with_status(rng, tb):
+    tb = json.loads(json.dumps(tb))
+    tb["status"] = rng.choice([None, {}, {"conditions": [], "readyReplicas": 0},
+                               {"conditions": [{"deploymentState": "Available", "lastProbeTime": "2026-11-07T09:00:00Z"}],
+                                "readyReplicas": 1},
+                               {"conditions": [{"deploymentState": "Progressing"}, {"deploymentState": "ReplicaFailure"}]}])
+    if tb["status"] is None:
+        del tb["status"]
+    return tb
+
+
+def check_update(tbs, desired, found, outs, st, res):
+    n_upd = n_same = 0
+    for i, tb in enumerate(tbs):
+        assert st[i] == 0
+        if found[i] is None:
+            assert outs[2 * i] == b"" and outs[2 * i + 1] == b"" and res[i] == 0
+            continue
+        to, upd = otb.copy_deployment_fields(desired[i], found[i])
+        assert bool(res[i] & 1) == upd, (desired[i], found[i])
+        if upd:
+            assert gojson.canon(json.loads(outs[2 * i])) == gojson.canon(to), (outs[2 * i], to)
+            n_upd += 1
+        else:
+            assert outs[2 * i] == b""
+            n_same += 1
+        assert gojson.canon(json.loads(outs[2 * i + 1])) == gojson.canon(otb.update_status(tb, found[i]))
+    return n_upd, n_same
+
+
+def test_deployment_update_and_status(hostplan, wl):
+    rng = random.Random(71)
+    tbs = [with_status(rng, wl.tensorboard_cr(rng, i)) for i in range(1500)]
+    desired, found = deployments_for(wl, tbs, 72)
+    outs, st, res = hostplan.tensorboard_update([wl.dumps(t, rng) for t in tbs], [wl.dumps(d, rng) for d in desired],
+                                                [b"" if f is None else wl.dumps(f, rng) for f in found])
+    n_upd, n_same = check_update(tbs, desired, found, outs, st, res)
+    assert n_upd > 500 and n_same > 150
