@@ -141,7 +141,7 @@ NB_HD void plan_vol_tls(Planner& P, const NbView& v) {
 
 // PodSpec with the injections applied.
 NB_HD void plan_mutated_podspec(Planner& P, const Doc& d, const NbView& v, const EnvLits& env,
-                                bool cert, bool oauth) {
+                                bool cert, bool oauth, ViewOut& vw) {
   LIT(P, LBRACE);
   Sep ps;
   bool had_containers = false, had_volumes = false, had_sa = false;
@@ -152,7 +152,10 @@ NB_HD void plan_mutated_podspec(Planner& P, const Doc& d, const NbView& v, const
       had_containers = true;
       ps.next(P);
       LIT(P, KEY_CONTAINERS_ARR);
-      LIT(P, LBRACKET);
+      const uint32_t arr0 = P.total;  // the readers of this Notebook get the extents of the array and of its
+      LIT(P, LBRACKET);               // first element (VF_PORTS / VF_SUBJECTS, nbrm_nbc.cuh view_notebook)
+      const uint32_t el0 = P.total;
+      bool first_el = true;
       Sep cs;
       bool cert_done = !cert, proxy_done = !oauth;
       ArrIter ci(d, m.val);
@@ -171,12 +174,16 @@ NB_HD void plan_mutated_podspec(Planner& P, const Doc& d, const NbView& v, const
         } else {
           cs.in(P, d, e);
         }
+        if (first_el) vw.set(VF_SUBJECTS, el0, P.total);
+        first_el = false;
       }
       if (!proxy_done) {  // :177-179
         cs.next(P);
         plan_sidecar(P, v, env);
+        if (first_el) vw.set(VF_SUBJECTS, el0, P.total);
       }
       LIT(P, RBRACKET);
+      vw.set(VF_PORTS, arr0, P.total);
       continue;
     }
     if (KEY_IS(d, m, "volumes") && (cert || oauth)) {
@@ -223,9 +230,13 @@ NB_HD void plan_mutated_podspec(Planner& P, const Doc& d, const NbView& v, const
   if (!had_containers && oauth) {
     ps.next(P);
     LIT(P, KEY_CONTAINERS_ARR);
+    const uint32_t arr0 = P.total;
     LIT(P, LBRACKET);
+    const uint32_t el0 = P.total;
     plan_sidecar(P, v, env);
+    vw.set(VF_SUBJECTS, el0, P.total);
     LIT(P, RBRACKET);
+    vw.set(VF_PORTS, arr0, P.total);
   }
   if (!had_volumes && (cert || oauth)) {
     ps.next(P);
@@ -251,7 +262,7 @@ NB_HD void plan_mutated_podspec(Planner& P, const Doc& d, const NbView& v, const
 
 // metadata with the annotation edits: add_lock sets the reconciliation lock
 // (:63-72); pending = 0 leaves update-pending alone, 1 removes it (:292), 2 sets it (:290).
-NB_HD void plan_mutated_metadata(Planner& P, const Doc& d, Span meta, bool add_lock, int pending) {
+NB_HD void plan_mutated_metadata(Planner& P, const Doc& d, Span meta, bool add_lock, int pending, ViewOut& vw) {
   LIT(P, LBRACE);
   Sep ms;
   bool had_ann = false;
@@ -260,15 +271,18 @@ NB_HD void plan_mutated_metadata(Planner& P, const Doc& d, Span meta, bool add_l
   while (it.next(d, m)) {
     if (!KEY_IS(d, m, "annotations")) {
       ms.in(P, d, m.all);
+      if (KEY_IS(d, m, "labels")) vw.set(VF_LABELS, P.total - m.val.len, P.total);
       continue;
     }
     had_ann = true;
     if (!is_object(d, m.val) && !add_lock && pending != 2) {
       ms.in(P, d, m.all);
+      vw.set(VF_ANNOTATIONS, P.total - m.val.len, P.total);
       continue;
     }
     ms.next(P);
     LIT(P, KEY_ANNOTATIONS);
+    const uint32_t ann0 = P.total;
     LIT(P, LBRACE);
     Sep as;
     ObjIter ai(d, m.val);
@@ -281,15 +295,18 @@ NB_HD void plan_mutated_metadata(Planner& P, const Doc& d, Span meta, bool add_l
     if (add_lock) { as.next(P); LIT(P, ANN_LOCK); }
     if (pending == 2) { as.next(P); LIT(P, ANN_UPDATE_PENDING); }
     LIT(P, RBRACE);
+    vw.set(VF_ANNOTATIONS, ann0, P.total);
   }
   if (!had_ann && (add_lock || pending == 2)) {
     ms.next(P);
     LIT(P, KEY_ANNOTATIONS);
+    const uint32_t ann0 = P.total;
     LIT(P, LBRACE);
     Sep as;
     if (add_lock) { as.next(P); LIT(P, ANN_LOCK); }
     if (pending == 2) { as.next(P); LIT(P, ANN_UPDATE_PENDING); }
     LIT(P, RBRACE);
+    vw.set(VF_ANNOTATIONS, ann0, P.total);
   }
   LIT(P, RBRACE);
 }
@@ -306,7 +323,7 @@ struct MutatePlan {
 };
 
 NB_HD void plan_notebook_with(Planner& P, const Doc& d, const NbView& v, const EnvLits& env,
-                              const MutatePlan& mp) {
+                              const MutatePlan& mp, ViewOut& vw) {
   const bool touch_spec = mp.podspec_k >= 0 || mp.cert || mp.oauth;
   LIT(P, LBRACE);
   Sep s;
@@ -318,7 +335,9 @@ NB_HD void plan_notebook_with(Planner& P, const Doc& d, const NbView& v, const E
       had_meta = true;
       s.next(P);
       LIT(P, KEY_METADATA);
-      plan_mutated_metadata(P, d, m.val, mp.add_lock, mp.pending);
+      const uint32_t m0 = P.total;
+      plan_mutated_metadata(P, d, m.val, mp.add_lock, mp.pending, vw);
+      vw.set(VF_META, m0, P.total);
     } else if (KEY_IS(d, m, "spec") && is_object(d, m.val) && touch_spec) {
       s.next(P);
       LIT(P, KEY_SPEC);
@@ -344,8 +363,10 @@ NB_HD void plan_notebook_with(Planner& P, const Doc& d, const NbView& v, const E
           }
           ts.next(P);
           LIT(P, KEY_SPEC);
+          const uint32_t p0 = P.total;
           if (mp.podspec_k >= 0) P.in(mp.podspec_src, (uint32_t)mp.podspec_k);
-          else plan_mutated_podspec(P, d, v, env, mp.cert, mp.oauth);
+          else plan_mutated_podspec(P, d, v, env, mp.cert, mp.oauth, vw);
+          vw.set(VF_TPOD, p0, P.total);
         }
         LIT(P, RBRACE);
       }
@@ -357,9 +378,12 @@ NB_HD void plan_notebook_with(Planner& P, const Doc& d, const NbView& v, const E
   if (!had_meta && (mp.add_lock || mp.pending == 2)) {
     s.next(P);
     LIT(P, KEY_METADATA);
-    plan_mutated_metadata(P, d, mk(0, 0), mp.add_lock, mp.pending);
+    const uint32_t m0 = P.total;
+    plan_mutated_metadata(P, d, mk(0, 0), mp.add_lock, mp.pending, vw);
+    vw.set(VF_META, m0, P.total);
   }
   LIT(P, RBRACE);
+  vw.set(VF_ROOT, 0, P.total);
 }
 
 struct GenMutate {
@@ -369,8 +393,13 @@ struct GenMutate {
   struct K {
     DocCtx& c;
     const NbView& v;
+    ViewTable views;
+    uint32_t view_j;
     NB_HD void operator()(Planner& P, uint32_t) {
       const Doc& d = c.d[0];
+      ViewOut vw;  // what the generators that read the mutated Notebook next will not have to look for
+      vw.t = views;
+      vw.j = view_j;
       MutatePlan mp;
       mp.add_lock = (c.flags & MUT_CREATE) != 0;
       mp.pending = (c.flags & MUT_CREATE) ? 1 : 0;  // Create: NoPendingUpdates -> delete (:319-322,:292)
@@ -386,12 +415,12 @@ struct GenMutate {
         P.err = E_PARSE;
         return;
       }
-      plan_notebook_with(P, d, v, *c.env, mp);
+      plan_notebook_with(P, d, v, *c.env, mp, vw);
     }
   };
   NB_HD static uint32_t run(DocCtx& c, ObjSink s) {
     NbView v = view_notebook(c.d[0]);
-    K k{c, v};
+    K k{c, v, s.views, s.view_j};
     return plan_objects(c, s, NOBJ, v.err, k);
   }
 };
@@ -442,7 +471,11 @@ struct GenRestartGuard {
           }
         }
       }
-      plan_notebook_with(P, mut, mv, *c.env, mp);
+      ViewOut vw;  // the guard's output is not one of the resident Notebooks the generators read
+      vw.t.p = nullptr;
+      vw.t.n = 0;
+      vw.j = 0;
+      plan_notebook_with(P, mut, mv, *c.env, mp, vw);
     }
   };
   NB_HD static uint32_t run(DocCtx& c, ObjSink s) {

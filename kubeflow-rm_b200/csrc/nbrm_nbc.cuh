@@ -156,6 +156,66 @@ NB_HD NbView view_notebook(const Doc& d) {
   return v;
 }
 
+// The same view of a Notebook another generator of this pass wrote (the webhook's mutated
+// Notebook): it left the extents of metadata, labels, annotations, the pod spec, its containers
+// and the first of them (VF_PORTS / VF_SUBJECTS stand for those two here), so only metadata's own
+// members and the two small maps are walked.  Any of the large parts missing: the full walk.
+NB_HD NbView view_notebook(const Doc& d, const ViewIn& vin) {
+  if (!vin.ok()) return view_notebook(d);
+  NbView v;
+  v.root = vin.get(VF_ROOT);
+  v.meta = vin.get(VF_META);
+  v.podspec = vin.get(VF_TPOD);
+  v.containers = vin.get(VF_PORTS);
+  v.c0 = vin.get(VF_SUBJECTS);
+  if (!v.root.ok() || !v.meta.ok() || !v.podspec.ok() || !v.containers.ok() || !v.c0.ok() || v.root.end() > d.n)
+    return view_notebook(d);
+  v.err = E_OK;
+  v.labels = vin.get(VF_LABELS);
+  v.annotations = vin.get(VF_ANNOTATIONS);
+  v.name = v.ns = v.uid = mk(0, 0);
+  v.a_stopped = v.a_rewrite = v.a_headers = v.a_oauth = v.a_mesh = v.a_logout = v.a_restart = mk(0, 0);
+  v.l_statefulset = v.l_notebook_name = v.l_workbench = false;
+  {
+    ObjIter it(d, v.meta);
+    Member m;
+    while (it.next(d, m, v.labels, v.annotations)) {
+      if (KEY_IS(d, m, "name")) v.name = m.val;
+      else if (KEY_IS(d, m, "namespace")) v.ns = m.val;
+      else if (KEY_IS(d, m, "uid")) v.uid = m.val;
+    }
+  }
+  if (!is_object(d, v.labels)) v.labels = mk(0, 0);
+  if (!is_object(d, v.annotations)) v.annotations = mk(0, 0);
+  {
+    ObjIter it(d, v.labels);
+    Member m;
+    while (it.next(d, m)) {
+      if (KEY_IS(d, m, "statefulset")) v.l_statefulset = true;
+      else if (KEY_IS(d, m, "notebook-name")) v.l_notebook_name = true;
+      else if (KEY_IS(d, m, "opendatahub.io/workbenches")) v.l_workbench = true;
+    }
+  }
+  {
+    ObjIter it(d, v.annotations);
+    Member m;
+    while (it.next(d, m)) {
+      if (KEY_IS(d, m, "kubeflow-resource-stopped")) v.a_stopped = m.val;
+      else if (KEY_IS(d, m, "notebooks.kubeflow.org/http-rewrite-uri")) v.a_rewrite = m.val;
+      else if (KEY_IS(d, m, "notebooks.kubeflow.org/http-headers-request-set")) v.a_headers = m.val;
+      else if (KEY_IS(d, m, "notebooks.opendatahub.io/inject-oauth")) v.a_oauth = m.val;
+      else if (KEY_IS(d, m, "opendatahub.io/service-mesh")) v.a_mesh = m.val;
+      else if (KEY_IS(d, m, "notebooks.opendatahub.io/oauth-logout-url")) v.a_logout = m.val;
+      else if (KEY_IS(d, m, "notebooks.opendatahub.io/notebook-restart")) v.a_restart = m.val;
+    }
+  }
+  if (!is_object(d, v.c0)) v.c0 = mk(0, 0);
+  if (!is_string(d, v.name)) v.name = mk(0, 0);
+  if (!is_string(d, v.ns) || v.ns.len == 2) v.ns = mk(0, 0);
+  if (!is_string(d, v.uid)) v.uid = mk(0, 0);
+  return v;
+}
+
 NB_HD void put_str(Planner& P, Span s) {
   if (s.ok()) P.in(s);
   else LIT(P, EMPTY_STR);
@@ -268,7 +328,7 @@ NB_HD void plan_statefulset(Planner& P, const Doc& d, const NbView& v, const Env
     bool has_sc = false;
     ObjIter it(d, v.podspec);
     Member m;
-    while (it.next(d, m)) {
+    while (it.next(d, m, v.containers)) {  // the containers' extent is known: not skipped through again
       if (KEY_IS(d, m, "containers")) {
         ps.next(P);
         LIT(P, KEY_CONTAINERS);
@@ -607,7 +667,7 @@ struct GenNbc {
     }
   };
   NB_HD static uint32_t run(DocCtx& c, ObjSink s) {
-    NbView v = view_notebook(c.d[0]);
+    NbView v = view_notebook(c.d[0], c.view[0]);
     uint32_t st = v.err;
     if (!st && (!is_object(c.d[0], v.podspec) || !v.c0.ok())) st = E_NO_CONTAINERS;
     K k{c, v, s.views, s.view_j};

@@ -227,7 +227,7 @@ struct GenOdh {
     }
   };
   NB_HD static uint32_t run(DocCtx& c, ObjSink s) {
-    NbView v = view_notebook(c.d[0]);
+    NbView v = view_notebook(c.d[0], c.view[0]);
     K k{c, v, false, false, s.views, s.view_j};
     if (!v.err) {
       k.oauth = oauth_enabled(c.d[0], v);

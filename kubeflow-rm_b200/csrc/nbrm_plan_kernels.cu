@@ -102,7 +102,7 @@ void gen_shape(int gen, uint32_t* nobj, uint32_t* cap) {
   shape_of(gen, nobj, cap, &s);
 }
 
-bool gen_views(int gen) { return gen == GEN_ID_NBC || gen == GEN_ID_ODH; }
+bool gen_views(int gen) { return gen == GEN_ID_NBC || gen == GEN_ID_ODH || gen == GEN_ID_MUTATE; }
 
 bool gen_shared1(int gen) {
   uint32_t a, b;

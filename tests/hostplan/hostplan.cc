@@ -264,6 +264,46 @@ HP_API const uint32_t* hostplan_views(uint32_t* fields) {
   *fields = VIEW_FIELDS;
   return reinterpret_cast<const uint32_t*>(g_out.views.data());
 }
+// A Notebook's view built from a recorded ViewRec (as the generators that read a mutated
+// Notebook get it) against the view the full walk finds: 0 when every span and flag agrees.
+HP_API int hostplan_check_notebook_view(const char* p, uint32_t n, const uint32_t* rec) {
+  Doc d;
+  d.p = p;
+  d.n = n;
+  ViewEnt tab[VIEW_FIELDS];
+  for (uint32_t f = 0; f < VIEW_FIELDS; ++f) {
+    tab[f].off = rec[f];
+    tab[f].len = rec[VIEW_FIELDS + f];
+  }
+  ViewIn vin;
+  vin.t.p = tab;
+  vin.t.n = 1;
+  vin.j = 0;
+  const NbView a = view_notebook(d, vin), b = view_notebook(d);
+  auto same = [](Span x, Span y) { return x.len == y.len && (x.len == 0 || x.off == y.off); };
+  if (a.err != b.err) return 1;
+  if (a.err) return 0;
+  if (!same(a.root, b.root)) return 2;
+  if (!same(a.meta, b.meta)) return 3;
+  if (!same(a.name, b.name) || !same(a.ns, b.ns) || !same(a.uid, b.uid)) return 4;
+  if (!same(a.labels, b.labels)) return 5;
+  if (!same(a.annotations, b.annotations)) return 6;
+  if (!same(a.podspec, b.podspec)) return 7;
+  if (!same(a.containers, b.containers)) return 8;
+  if (!same(a.c0, b.c0)) return 9;
+  if (!same(a.a_stopped, b.a_stopped) || !same(a.a_rewrite, b.a_rewrite) || !same(a.a_headers, b.a_headers) ||
+      !same(a.a_oauth, b.a_oauth) || !same(a.a_mesh, b.a_mesh) || !same(a.a_logout, b.a_logout) ||
+      !same(a.a_restart, b.a_restart))
+    return 10;
+  if (a.l_statefulset != b.l_statefulset || a.l_notebook_name != b.l_notebook_name || a.l_workbench != b.l_workbench)
+    return 11;
+  // 100: the recorded extents were complete enough for the short walk to be the one that ran
+  return (rec[VIEW_FIELDS + VF_ROOT] && rec[VIEW_FIELDS + VF_META] && rec[VIEW_FIELDS + VF_TPOD] &&
+          rec[VIEW_FIELDS + VF_PORTS] && rec[VIEW_FIELDS + VF_SUBJECTS])
+             ? 100
+             : 0;
+}
+
 HP_API void hostplan_view_object(const char* p, uint32_t n, uint32_t* out) {
   Doc d;
   d.p = p;

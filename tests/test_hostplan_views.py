@@ -73,3 +73,30 @@ def test_recorded_odh_views_match_a_walk(hostplan, wl):
                     assert got == want, (i, kind, f, got, want, o)
             n_checked += 1
     assert n_checked > 10000
+
+
+def test_mutated_notebook_views(hostplan, wl):
+    """The webhook records where metadata, labels, annotations, the pod spec, its containers and the
+    first of them are in the Notebook it writes; the generators that read that Notebook build
+    their view from those extents.  That view equals the one the full walk finds."""
+    lib = hostplan.lib
+    lib.hostplan_views.restype = C.c_void_p
+    rng = random.Random(9)
+    nbs = wl.corpus("fuzz", 2500, start=77) + wl.corpus("c2", 200) + wl.corpus("c1", 100) + wl.corpus("loadtest", 50)
+    docs = [wl.dumps(nb, rng) for nb in nbs]
+    n_short = n_full = 0
+    for flags in (1, 1 | 2, 0, 2):      # MUT_CREATE, + MUT_CA_BUNDLE, update, update + CA bundle
+        outs, st = hostplan.mutate(docs, {"USE_ISTIO": "true"}, flags)
+        nf = C.c_uint32()
+        ptr = lib.hostplan_views(C.byref(nf))
+        F = nf.value
+        rec = np.frombuffer((C.c_uint32 * (len(outs) * 2 * F)).from_address(ptr), dtype=np.uint32).reshape(len(outs), 2 * F).copy()
+        for i, o in enumerate(outs):
+            if not o:
+                continue
+            r = np.ascontiguousarray(rec[i])
+            rc = lib.hostplan_check_notebook_view(C.c_char_p(o), C.c_uint32(len(o)), C.c_void_p(r.ctypes.data))
+            assert rc in (0, 100), (rc, flags, o, list(r))
+            n_short += rc == 100
+            n_full += rc == 0
+    assert n_short > 2000, (n_short, n_full)
