@@ -341,6 +341,7 @@ NB_HD void plan_notebook_with(Planner& P, const Doc& d, const NbView& v, const E
     } else if (KEY_IS(d, m, "spec") && is_object(d, m.val) && touch_spec) {
       s.next(P);
       LIT(P, KEY_SPEC);
+      const uint32_t s0 = P.total;
       LIT(P, LBRACE);
       Sep ss;
       ObjIter si(d, m.val);
@@ -371,8 +372,10 @@ NB_HD void plan_notebook_with(Planner& P, const Doc& d, const NbView& v, const E
         LIT(P, RBRACE);
       }
       LIT(P, RBRACE);
+      vw.set(VF_SPEC, s0, P.total);
     } else {
       s.in(P, d, m.all);
+      if (KEY_IS(d, m, "spec")) vw.set(VF_SPEC, P.total - m.val.len, P.total);
     }
   }
   if (!had_meta && (mp.add_lock || mp.pending == 2)) {

@@ -58,7 +58,29 @@ NB_HD void plan_status(Planner& P, DocCtx& c) {
         if (KEY_IS(pod, m, "status")) pst = val;
       }
   }
-  {
+  const ViewIn& nv = c.view[0];
+  const Span vroot = nv.ok() ? nv.get(VF_ROOT) : mk(0, 0);
+  const Span vmeta = nv.ok() ? nv.get(VF_META) : mk(0, 0), vspec = nv.ok() ? nv.get(VF_SPEC) : mk(0, 0);
+  if (vroot.ok() && vmeta.ok() && vspec.ok() && vroot.end() <= nb.n) {
+    // the generator that wrote this Notebook left the extents of its metadata and spec: neither is
+    // skipped through, and inside metadata neither are the labels and annotations
+    const Span vl = nv.get(VF_LABELS), va = nv.get(VF_ANNOTATIONS);
+    ObjIter it(nb, vroot);
+    Member m;
+    while (it.next(nb, m, vmeta, vspec)) {
+      if (KEY_IS(nb, m, "metadata")) {
+        ObjIter mi(nb, m.val);
+        Member mm;
+        while (mi.next(nb, mm, vl, va))
+          if (KEY_IS(nb, mm, "name")) nbname = mm.val;
+      } else if (KEY_IS(nb, m, "status")) {
+        ObjIter si(nb, m.val);
+        Member mm;
+        while (si.next(nb, mm))
+          if (KEY_IS(nb, mm, "containerState")) cur = mm.val;
+      }
+    }
+  } else {
     Cursor nc;
     nc.i = 0;
     Member m;
