@@ -104,7 +104,7 @@ typedef struct nbrm_out {
 
 /* Accumulated device time per kernel class since nbrm_profile_enable(ctx, 1),
  * measured with CUDA events on the context's stream. */
-#define NBRM_GENERATORS 16 /* size of the per-generator arrays below; ids 0..13 are in use */
+#define NBRM_GENERATORS 32 /* size of the per-generator arrays below (a power of two); ids 0..18 are in use */
 typedef struct nbrm_profile {
   double plan_ms, scan_ms, emit_ms;
   uint64_t plan_launches, scan_launches, emit_launches;
@@ -394,7 +394,10 @@ int nbrm_pvcviewer_status(nbrm_ctx* ctx, const nbrm_docs* viewers, const nbrm_do
  * 7 PodDefault admission (Pods, shared PodDefault arena), 8 Profile objects (8),
  * 9 ODH write decision (slot_a desired ODH objects, slot_b found; result word 0 nothing,
  * 1 create, 2 update: reconcileRoute / reconcileNetworkPolicy / reconcileRoleBinding and the
- * create-once ServiceAccount, Service, Secret).  use_side_input: pass
+ * create-once ServiceAccount, Service, Secret), 10 JSON diff (RFC 6902), 11 / 12 AdmissionReview open /
+ * close, 13 Notebook version conversion, 14 tensorboard objects (3), 15 what a PVCViewer reconcile
+ * writes (3; slot_b = the shared arena of found objects), 16 the viewer's webhook, 17 tensorboard
+ * Deployment update + status (2), 18 the viewer's status.  use_side_input: pass
  * the bytes of nbrm_upload_bytes (seeds / pod_exists / ranges).  The result is
  * read with nbrm_download or moved on with nbrm_result_to_slot. */
 int nbrm_run(nbrm_ctx* ctx, int generator, int slot_a, int slot_b, int slot_c, uint32_t flags,

@@ -43,9 +43,9 @@ class Profile(C.Structure):
                 ("plan_launches", C.c_uint64), ("scan_launches", C.c_uint64),
                 ("emit_launches", C.c_uint64), ("emit_bytes_read", C.c_uint64),
                 ("emit_bytes_written", C.c_uint64), ("plan_bytes_read", C.c_uint64),
-                ("plan_ms_gen", C.c_double * 16), ("emit_ms_gen", C.c_double * 16),
-                ("plan_bytes_gen", C.c_uint64 * 16), ("emit_bytes_gen", C.c_uint64 * 16),
-                ("runs_gen", C.c_uint64 * 16)]
+                ("plan_ms_gen", C.c_double * 32), ("emit_ms_gen", C.c_double * 32),
+                ("plan_bytes_gen", C.c_uint64 * 32), ("emit_bytes_gen", C.c_uint64 * 32),
+                ("runs_gen", C.c_uint64 * 32)]
 
 
 # reference process environment (nbrm_env) key -> struct field
